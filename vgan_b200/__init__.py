@@ -1,0 +1,9 @@
+"""vgan_b200 — B200-native (sm_100a) squared-MMD forward+backward behind V-GAN's loss interface.
+
+Public surface mirrors the reference (/root/reference/src): ``RBF``, ``MMDLossConstrained``
+(models/Mmd_loss_constrained.py), ``MMDStatistic`` (the torch_two_sample call V-GAN relies on),
+``VGAN`` / ``VGAN_no_kl`` (vgan.py)."""
+from .loss import RBF, MMDLossConstrained, mmd2_eval  # noqa: F401
+from .statistic import MMDStatistic  # noqa: F401
+
+__all__ = ["RBF", "MMDLossConstrained", "MMDStatistic", "mmd2_eval"]

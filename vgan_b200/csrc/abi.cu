@@ -1,0 +1,283 @@
+// C ABI of vgan_b200 (include/vgan_b200.h): argument checking, workspace layout, TMA
+// descriptor creation and kernel launches.  No torch types, no host synchronisation.
+#include <cstdarg>
+#include <cstring>
+
+#include "common.cuh"
+
+namespace vg {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int check_device() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) {
+    set_error("no CUDA device available (vgan_b200 has no CPU fallback)");
+    return VGAN_B200_ERR_DEVICE;
+  }
+  int major = 0;
+  cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev);
+  if (major != 10) {
+    set_error("device compute capability %d.x is not sm_100 (B200); no other backend exists", major);
+    return VGAN_B200_ERR_DEVICE;
+  }
+  return VGAN_B200_OK;
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(ptr);
+  }
+  return fn;
+}
+
+// bf16 [rows, cols] row-major, box = 64 columns x 128 rows, 128-byte swizzle
+int make_tmap_bf16_2d(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) {
+    set_error("cuTensorMapEncodeTiled not available from the driver");
+    return VGAN_B200_ERR_CUDA;
+  }
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {cols * 2};
+  cuuint32_t box[2] = {static_cast<cuuint32_t>(kChunk), static_cast<cuuint32_t>(kTile)};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box,
+                   estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed with CUresult %d", static_cast<int>(r));
+    return VGAN_B200_ERR_CUDA;
+  }
+  return VGAN_B200_OK;
+}
+
+// launchers defined in the kernel files
+int run_prologue(const float*, const float*, const float*, const vgan_b200_layout_t&, int, void*, cudaStream_t);
+int run_scales(const vgan_b200_layout_t&, void*, float*, int, const float*, int, float*, cudaStream_t);
+int run_setup(const vgan_b200_layout_t&, void*, const float*, int, float*, cudaStream_t);
+int run_penalty(const float*, int64_t, int64_t, float, unsigned long long*, float*, float*, int64_t, int64_t,
+                cudaStream_t);
+int run_finalize(const double*, int64_t, int64_t, const float*, float*, cudaStream_t);
+int launch_matrix(const float*, int64_t, int64_t, const float*, int, float, float*, cudaStream_t);
+struct SimtParams;
+int launch_simt_from_abi(const vgan_b200_layout_t& L, void* ws, int64_t row_begin, int64_t row_end, int xx_part,
+                         int xx_nparts, const float* inv_scales, int n_scales, int flags, double* sums,
+                         float* dY, const float* dY_mul, float* dX, cudaStream_t st);
+
+static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+static int fill_layout(int64_t Nx, int64_t Ny, int64_t D, int64_t D_u, int flags, vgan_b200_layout_t* L) {
+  if (!L || Nx < 1 || Ny < 1 || D < 1 || D_u < 0) {
+    set_error("workspace_layout: need Nx, Ny, D >= 1 (got %lld, %lld, %lld)", (long long)Nx, (long long)Ny,
+              (long long)D);
+    return VGAN_B200_ERR_ARG;
+  }
+  if (Nx + Ny > (1ll << 30) || D > (1 << 20)) {
+    set_error("workspace_layout: sizes out of range");
+    return VGAN_B200_ERR_ARG;
+  }
+  memset(L, 0, sizeof(*L));
+  L->Nx = Nx; L->Ny = Ny; L->D = D;
+  L->Dp = (D + kChunk - 1) / kChunk * kChunk;
+  L->Nxp = (Nx + kTile - 1) / kTile * kTile;
+  L->Nyp = (Ny + kTile - 1) / kTile * kTile;
+  const size_t rows = static_cast<size_t>(L->Nxp + L->Nyp);
+  const bool fp32 = (flags & VGAN_B200_PREC_MASK) == VGAN_B200_PREC_FP32;
+  // small buffers first so that their offsets depend on (Nx, Ny, D) only; the operand next;
+  // the penalty scratch (the only part that depends on D_u and precision) last.
+  size_t off = 0;
+  L->off_par = off;   off = align_up(off + kParFloats * 4, 1024);
+  L->off_stats = off; off = align_up(off + (2 + L->Dp) * 8, 1024);
+  L->off_mean = off;  off = align_up(off + L->Dp * 4, 1024);
+  L->off_nrm = off;   off = align_up(off + rows * 4, 1024);
+  L->off_nrms = off;  off = align_up(off + rows * 4, 1024);
+  L->off_zq = off;
+  L->off_zf = off;    off = align_up(off + rows * L->Dp * (fp32 ? 4 : 2), 1024);
+  L->off_cmax = off;  off = align_up(off + static_cast<size_t>(D_u > 0 ? D_u : 1) * 8, 1024);
+  L->total = off;
+  return VGAN_B200_OK;
+}
+
+}  // namespace vg
+
+using namespace vg;
+
+extern "C" {
+
+int vgan_b200_abi_version(void) { return VGAN_B200_ABI_VERSION; }
+const char* vgan_b200_last_error(void) { return g_err; }
+
+int vgan_b200_workspace_layout(int64_t Nx, int64_t Ny, int64_t D, int64_t D_u, int flags,
+                               vgan_b200_layout_t* out) {
+  return fill_layout(Nx, Ny, D, D_u, flags, out);
+}
+
+int vgan_b200_prologue(const float* X, const float* U, const float* Y, int64_t Nx, int64_t Ny, int64_t D,
+                       int flags, void* ws, void* stream) {
+  if (int e = check_device()) return e;
+  vgan_b200_layout_t L;
+  if (int e = fill_layout(Nx, Ny, D, 0, flags, &L)) return e;
+  if (!X || !ws || (!U && !Y)) {
+    set_error("prologue: X, ws and one of U / Y must be non-null");
+    return VGAN_B200_ERR_ARG;
+  }
+  if (!Y && Nx != Ny) {
+    set_error("prologue: masking Y = U*X needs Ny == Nx (got %lld vs %lld)", (long long)Ny, (long long)Nx);
+    return VGAN_B200_ERR_ARG;
+  }
+  if (reinterpret_cast<uintptr_t>(ws) % 1024) {
+    set_error("prologue: workspace must be 1024-byte aligned");
+    return VGAN_B200_ERR_ARG;
+  }
+  return run_prologue(X, U, Y, L, flags, ws, static_cast<cudaStream_t>(stream));
+}
+
+int vgan_b200_scales(void* ws, int64_t Nx, int64_t Ny, int64_t D, float* bandwidth, int frozen,
+                     const float* mults_host, int n_scales, float* inv_scales, void* stream) {
+  if (int e = check_device()) return e;
+  vgan_b200_layout_t L;
+  if (int e = fill_layout(Nx, Ny, D, 0, 0, &L)) return e;
+  if (!ws || !bandwidth || !mults_host || !inv_scales || n_scales < 1 || n_scales > VGAN_B200_MAX_SCALES) {
+    set_error("scales: null pointer or n_scales outside [1, %d]", VGAN_B200_MAX_SCALES);
+    return VGAN_B200_ERR_ARG;
+  }
+  return run_scales(L, ws, bandwidth, frozen, mults_host, n_scales, inv_scales, static_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"
+
+extern "C" {
+
+int vgan_b200_mmd2_fwd_bwd(void* ws, int64_t Nx, int64_t Ny, int64_t D, int64_t row_begin, int64_t row_end,
+                           int xx_part, int xx_nparts, const float* inv_scales, int n_scales, int flags,
+                           double* sums, float* dY, const float* dY_mul, float* dX, void* stream) {
+  if (int e = check_device()) return e;
+  vgan_b200_layout_t L;
+  if (int e = fill_layout(Nx, Ny, D, 0, flags, &L)) return e;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (!ws || !inv_scales || !sums || n_scales < 1 || n_scales > VGAN_B200_MAX_SCALES) {
+    set_error("mmd2_fwd_bwd: null pointer or n_scales outside [1, %d]", VGAN_B200_MAX_SCALES);
+    return VGAN_B200_ERR_ARG;
+  }
+  if (row_begin < 0 || row_begin % kTile || row_end <= row_begin || xx_nparts < 1 || xx_part < 0 ||
+      xx_part >= xx_nparts) {
+    set_error("mmd2_fwd_bwd: bad shard (row_begin %lld must be a multiple of 128, row_end %lld, xx %d/%d)",
+              (long long)row_begin, (long long)row_end, xx_part, xx_nparts);
+    return VGAN_B200_ERR_ARG;
+  }
+  const bool need_dx = (flags & VGAN_B200_NEED_DX) != 0;
+  if (need_dx && !dX) {
+    set_error("mmd2_fwd_bwd: NEED_DX set but dX is null");
+    return VGAN_B200_ERR_ARG;
+  }
+  if ((need_dx || dY_mul) && !dY) {
+    set_error("mmd2_fwd_bwd: dY is null but a gradient output was requested");
+    return VGAN_B200_ERR_ARG;
+  }
+  if ((flags & VGAN_B200_LADDER) && n_scales != 5) {
+    set_error("mmd2_fwd_bwd: LADDER needs exactly 5 scales");
+    return VGAN_B200_ERR_ARG;
+  }
+  uint8_t* base = static_cast<uint8_t*>(ws);
+  if ((flags & VGAN_B200_PREC_MASK) == VGAN_B200_PREC_FP32)
+    return launch_simt_from_abi(L, ws, row_begin, row_end, xx_part, xx_nparts, inv_scales, n_scales, flags,
+                                sums, dY, dY_mul, dX, st);
+
+  float* par = reinterpret_cast<float*>(base + L.off_par);
+  if (int e = run_setup(L, ws, inv_scales, n_scales, par, st)) return e;
+  TcParams p;
+  memset(&p, 0, sizeof(p));
+  p.tiles_x = static_cast<int>(L.Nxp / kTile);
+  p.tiles_y = static_cast<int>(L.Nyp / kTile);
+  p.kchunks = static_cast<int>(L.Dp / kChunk);
+  p.slice_chunks = kSliceMax / kChunk;
+  if (p.slice_chunks > p.kchunks) p.slice_chunks = p.kchunks;
+  p.pv = dY ? 1 : 0;
+  p.nslices = p.pv ? (p.kchunks + p.slice_chunks - 1) / p.slice_chunks : 1;
+  const int64_t ye = row_end < Ny ? row_end : Ny, xe = row_end < Nx ? row_end : Nx;
+  p.gy_begin = static_cast<int>(row_begin / kTile);
+  p.gy_end = ye > row_begin ? static_cast<int>((ye + kTile - 1) / kTile) : p.gy_begin;
+  if (need_dx) {
+    p.gx_begin = static_cast<int>(row_begin / kTile);
+    p.gx_end = xe > row_begin ? static_cast<int>((xe + kTile - 1) / kTile) : p.gx_begin;
+    p.n_xx_units = 0;
+  } else {
+    p.gx_begin = p.gx_end = 0;
+    p.n_xx_units = xx_part < p.tiles_x ? (p.tiles_x - xx_part + xx_nparts - 1) / xx_nparts : 0;
+  }
+  p.xx_part = xx_part; p.xx_nparts = xx_nparts;
+  p.n_scales = n_scales;
+  p.Nx = Nx; p.Ny = Ny; p.D = D; p.Dp = L.Dp;
+  p.row_begin = row_begin; p.row_end = row_end;
+  p.zq = reinterpret_cast<const __nv_bfloat16*>(base + L.off_zq);
+  p.nrms = reinterpret_cast<const float*>(base + L.off_nrms);
+  p.par = par;
+  p.sums = sums; p.dY = dY; p.dY_mul = dY_mul; p.dX = dX;
+  CUtensorMap map;
+  if (int e = make_tmap_bf16_2d(&map, p.zq, static_cast<uint64_t>(L.Nxp + L.Nyp), static_cast<uint64_t>(L.Dp)))
+    return e;
+  return launch_tc(p, map, (flags & VGAN_B200_LADDER) ? 1 : 0, st);
+}
+
+int vgan_b200_colmax_penalty(const float* U, int64_t N, int64_t D_u, float weight, void* scratch,
+                             float* penalty, float* dU, int64_t dU_row_begin, int64_t dU_rows, void* stream) {
+  if (int e = check_device()) return e;
+  if (!U || !scratch || !penalty || N < 1 || D_u < 1) {
+    set_error("colmax_penalty: null pointer or empty U");
+    return VGAN_B200_ERR_ARG;
+  }
+  return run_penalty(U, N, D_u, weight, static_cast<unsigned long long*>(scratch), penalty, dU, dU_row_begin,
+                     dU_rows, static_cast<cudaStream_t>(stream));
+}
+
+int vgan_b200_finalize_loss(const double* sums, int64_t Nx, int64_t Ny, const float* penalty, float* loss,
+                            void* stream) {
+  if (int e = check_device()) return e;
+  if (!sums || !loss || Nx < 1 || Ny < 1) {
+    set_error("finalize_loss: null pointer");
+    return VGAN_B200_ERR_ARG;
+  }
+  return run_finalize(sums, Nx, Ny, penalty, loss, static_cast<cudaStream_t>(stream));
+}
+
+int vgan_b200_mmd2_matrix(const float* Z, int64_t n, int64_t D, const float* inv_scales, int n_scales,
+                          float eps, float* K_out, void* stream) {
+  if (int e = check_device()) return e;
+  if (!Z || !inv_scales || !K_out || n < 1 || D < 1 || n_scales < 1 || n > 65536) {
+    set_error("mmd2_matrix: null pointer or bad size (n <= 65536)");
+    return VGAN_B200_ERR_ARG;
+  }
+  return launch_matrix(Z, n, D, inv_scales, n_scales, eps, K_out, static_cast<cudaStream_t>(stream));
+}
+
+int vgan_b200_umma_probe(const void* A, const void* B, float* S_out, float* O_out, void* stream) {
+  if (int e = check_device()) return e;
+  if (!A || !B || !S_out || !O_out) {
+    set_error("umma_probe: null pointer");
+    return VGAN_B200_ERR_ARG;
+  }
+  CUtensorMap ma, mb;
+  if (int e = make_tmap_bf16_2d(&ma, A, 128, 128)) return e;
+  if (int e = make_tmap_bf16_2d(&mb, B, 128, 128)) return e;
+  return launch_probe(ma, mb, S_out, O_out, static_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"

@@ -1,0 +1,68 @@
+// Shared constants, the parameter block and host helpers of the vgan_b200 kernels.
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <cstdio>
+
+#include "../../include/vgan_b200.h"
+
+namespace vg {
+
+constexpr int kTile = 128;          // rows per tile (TMEM lanes) and columns per step
+constexpr int kChunk = 64;          // bf16 elements per K chunk = one 128-byte swizzle row
+constexpr int kChunkBytes = kTile * kChunk * 2;   // 16 KiB
+constexpr int kSliceMax = 256;      // output features owned by one CTA (TMEM columns of O)
+constexpr float kPadNorm = 1e30f;   // |z|^2 of padding rows: makes every exp underflow to 0
+constexpr float kLog2e = 1.4426950408889634f;
+
+// Device-resident parameter block written by setup_kernel (no host sync needed).
+// par[0] = c0 = log2(e) * inv_s[ref]       par[1] = -2 c0
+// par[2 + m]  = inv_s[m] / inv_s[ref]      (general path exponent ratios)
+// par[10 + m] = cx * inv_s[m]              (P coefficients for X columns, cx = +1/Nx)
+// par[18 + m] = cy * inv_s[m]              (P coefficients for Y columns, cy = -1/Ny)
+constexpr int kParFloats = 32;
+
+struct TcParams {
+  int tiles_x, tiles_y;       // 128-row tiles in the X / Y regions of the stacked operand
+  int kchunks;                // Dp / 64
+  int nslices, slice_chunks;  // output feature slices per row tile, chunks per (full) slice
+  int gx_begin, gx_end;       // X row tiles that need a gradient (NEED_DX), else empty
+  int gy_begin, gy_end;       // Y row tiles of this shard
+  int xx_part, xx_nparts;     // S_xx-only units: X tiles t with t % nparts == part
+  int n_xx_units;
+  int pv;                     // 1: run the gradient GEMM and write dX/dY
+  int n_scales;
+  int64_t Nx, Ny, D, Dp;
+  int64_t row_begin, row_end; // gradient row range (rows of Y, and of X with NEED_DX)
+  const __nv_bfloat16* zq;    // stacked operand (for the final z_i read)
+  const float* nrms;          // scaled norms
+  const float* par;           // parameter block
+  double* sums;
+  float* dY;
+  const float* dY_mul;
+  float* dX;
+};
+
+#define VG_CUDA_CHECK(expr)                                                          \
+  do {                                                                               \
+    cudaError_t _e = (expr);                                                         \
+    if (_e != cudaSuccess) {                                                         \
+      vg::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, \
+                    __LINE__);                                                       \
+      return VGAN_B200_ERR_CUDA;                                                     \
+    }                                                                                \
+  } while (0)
+
+void set_error(const char* fmt, ...);
+int check_device();   // 0 when the current device is compute capability 10.x
+
+// kernels' host launchers (defined in their own .cu files)
+int launch_tc(const TcParams& p, const CUtensorMap& map, int ladder, cudaStream_t st);
+int launch_probe(const CUtensorMap& mapA, const CUtensorMap& mapB, float* S_out, float* O_out,
+                 cudaStream_t st);
+int make_tmap_bf16_2d(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols);
+
+}  // namespace vg

@@ -1,0 +1,382 @@
+// K1 — fused MMD^2 forward+backward on tcgen05 tensor cores (bf16 operands, fp32 TMEM
+// accumulation).  Replaces RBF.forward + MMDLossConstrained.forward + autograd backward
+// (/root/reference/src/models/Mmd_loss_constrained.py:24-26, 42-50).
+//
+// One CTA = one work unit = (row tile I of 128 stacked rows, feature slice p <= 256 wide):
+//   for every column tile J (128 stacked rows):
+//     S   = Z_I Z_J^T                    tcgen05.mma, K streamed in 64-wide TMA chunks
+//     d2  = |z_i|^2 + |z_j|^2 - 2 S      epilogue warps, straight out of TMEM
+//     t   = exp(-d2/s_4); k = t+t^2+t^4+t^8+t^16 ; w = sum_m t^(2^q)/s_m   (x2 ladder)
+//     sums += k (S_xx / S_xy / S_yy by tile type) ; P = c_j w  -> bf16 -> smem
+//     O_I[:, slice p] += P Z_J[:, slice p]          second tcgen05.mma, O stays in TMEM
+//   dZ_I[:, slice p] = 4 c_i (O - rowsum(P) z_i)
+// The pairwise matrix only ever exists as a 128x128 TMEM tile.
+//
+// Warp roles (384 threads): warps 0-7 epilogue (warp%4 = TMEM lane quadrant, warp/4 =
+// column half), warp 8 = TMA producer for the Gram ring, warp 9 = MMA issuer,
+// warp 10 = TMA producer for V slices + column norms, warp 11 = TMEM allocator.
+#include "common.cuh"
+#include "ptx.cuh"
+
+namespace vg {
+
+constexpr int kStages = 3;
+constexpr int kStageBytes = 2 * kChunkBytes;                 // Z_I chunk + Z_J chunk
+constexpr int kVBytes = (kSliceMax / kChunk) * kChunkBytes;  // 64 KiB
+constexpr int kPBytes = 2 * kChunkBytes;                     // 128 x 128 bf16
+constexpr int kNumEpiThreads = 256;
+constexpr int kThreads = 384;
+
+struct __align__(8) TcBarriers {
+  uint64_t ring_full[kStages], ring_empty[kStages];
+  uint64_t s_full[2], s_empty[2];
+  uint64_t nj_full[2];
+  uint64_t p_full[2], p_empty[2];
+  uint64_t v_full, v_empty;
+  uint64_t o_full;
+  uint32_t tmem_base;
+  float red[8][4];
+};
+
+constexpr int kSmemRing = 0;
+constexpr int kSmemV = kSmemRing + kStages * kStageBytes;
+constexpr int kSmemP = kSmemV + kVBytes;
+constexpr int kSmemNj = kSmemP + 2 * kPBytes;
+constexpr int kSmemBar = kSmemNj + 2 * kTile * 4;
+constexpr int kSmemTotal = kSmemBar + static_cast<int>(sizeof(TcBarriers)) + 1024;  // + align slack
+static_assert(kSmemTotal <= 232448, "shared memory budget");
+
+struct Unit {
+  int ti;        // stacked row tile
+  int slice;     // feature slice
+  int j_begin, j_end;
+  int pv;        // gradient GEMM on
+  int row_is_x;  // row tile lies in the X region
+  int sym;       // S_xx-only unit walking the upper triangle: off-diagonal tiles count twice
+};
+
+__device__ __forceinline__ Unit decode_unit(const TcParams& p) {
+  Unit u;
+  const int ngx = p.gx_end - p.gx_begin;
+  const int ngy = p.gy_end - p.gy_begin;
+  const int n_grad_units = (ngx + ngy) * p.nslices;
+  int b = blockIdx.x;
+  if (b < n_grad_units) {
+    int t = b / p.nslices;
+    u.slice = b - t * p.nslices;
+    u.row_is_x = t < ngx;
+    u.ti = u.row_is_x ? p.gx_begin + t : p.tiles_x + p.gy_begin + (t - ngx);
+    u.j_begin = 0;
+    u.j_end = p.tiles_x + p.tiles_y;
+    u.pv = p.pv;
+    u.sym = 0;
+  } else {
+    int x = b - n_grad_units;
+    u.ti = p.xx_part + x * p.xx_nparts;
+    u.slice = 0;
+    u.row_is_x = 1;
+    u.j_begin = u.ti;      // upper triangle of the symmetric X x X block
+    u.j_end = p.tiles_x;
+    u.pv = 0;
+    u.sym = 1;
+  }
+  return u;
+}
+
+template <bool LADDER>
+__global__ void __launch_bounds__(kThreads, 1)
+mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const TcParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  TcBarriers* bar = reinterpret_cast<TcBarriers*>(smem + kSmemBar);
+  float* nj_smem = reinterpret_cast<float*>(smem + kSmemNj);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const Unit u = decode_unit(p);
+  const int n_tiles = u.j_end - u.j_begin;
+  const int slice_chunks =
+      min(p.slice_chunks, p.kchunks - u.slice * p.slice_chunks);  // chunks in this slice
+  const int slice_w = slice_chunks * kChunk;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(&bar->ring_full[s], 1);
+      mbar_init(&bar->ring_empty[s], 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&bar->s_full[b], 1);
+      mbar_init(&bar->s_empty[b], kNumEpiThreads);
+      mbar_init(&bar->nj_full[b], 1);
+      mbar_init(&bar->p_full[b], kNumEpiThreads);
+      mbar_init(&bar->p_empty[b], 1);
+    }
+    mbar_init(&bar->v_full, 1);
+    mbar_init(&bar->v_empty, 1);
+    mbar_init(&bar->o_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 11) {
+    tmem_alloc(&bar->tmem_base, 512);
+    tmem_relinquish();
+  }
+  if (warp == 8 && lane == 0) tma_prefetch_desc(&zmap);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = bar->tmem_base;
+  const uint32_t tmem_o = tmem + 256;
+
+  if (warp == 8) {
+    // ===================== TMA producer: Gram operand ring =====================
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int n = 0; n < n_tiles; ++n) {
+        const int jt = u.j_begin + n;
+        for (int kc = 0; kc < p.kchunks; ++kc, ++it) {
+          const uint32_t s = it % kStages, ph = (it / kStages) & 1;
+          mbar_wait(&bar->ring_empty[s], ph ^ 1);
+          uint8_t* dst = smem + kSmemRing + s * kStageBytes;
+          mbar_arrive_expect_tx(&bar->ring_full[s], kStageBytes);
+          tma_load_2d(dst, &zmap, &bar->ring_full[s], kc * kChunk, u.ti * kTile);
+          tma_load_2d(dst + kChunkBytes, &zmap, &bar->ring_full[s], kc * kChunk, jt * kTile);
+        }
+      }
+    }
+  } else if (warp == 10) {
+    // ===================== TMA producer: column norms + V slice =====================
+    if (lane == 0) {
+      for (int n = 0; n < n_tiles; ++n) {
+        const int jt = u.j_begin + n;
+        const int b = n & 1;
+        mbar_wait(&bar->s_empty[b], ((n >> 1) & 1) ^ 1);   // epilogue done with nj[b]
+        mbar_arrive_expect_tx(&bar->nj_full[b], kTile * 4);
+        bulk_load_1d(nj_smem + b * kTile, p.nrms + static_cast<int64_t>(jt) * kTile, kTile * 4,
+                     &bar->nj_full[b]);
+        if (u.pv) {
+          mbar_wait(&bar->v_empty, (n & 1) ^ 1);           // PV(n-1) finished reading V
+          mbar_arrive_expect_tx(&bar->v_full, slice_chunks * kChunkBytes);
+          for (int c = 0; c < slice_chunks; ++c)
+            tma_load_2d(smem + kSmemV + c * kChunkBytes, &zmap, &bar->v_full,
+                        (u.slice * p.slice_chunks + c) * kChunk, jt * kTile);
+        }
+      }
+    }
+  } else if (warp == 9) {
+    // ===================== MMA issuer (one thread) =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc_gram = make_idesc_bf16(kTile, kTile, 0, 0);
+      const uint32_t idesc_pv = make_idesc_bf16(kTile, slice_w, 0, 1);
+      uint32_t it = 0;
+      for (int n = 0; n <= n_tiles; ++n) {
+        if (n < n_tiles) {
+          // ---- Gram(n): S[b] = Z_I Z_J^T over all K chunks
+          const int b = n & 1;
+          mbar_wait(&bar->s_empty[b], ((n >> 1) & 1) ^ 1);
+          tc_fence_after();
+          const uint32_t d_tmem = tmem + b * kTile;
+          for (int kc = 0; kc < p.kchunks; ++kc, ++it) {
+            const uint32_t s = it % kStages, ph = (it / kStages) & 1;
+            mbar_wait(&bar->ring_full[s], ph);
+            tc_fence_after();
+            const uint32_t a_addr = smem_u32(smem + kSmemRing + s * kStageBytes);
+            const uint32_t b_addr = a_addr + kChunkBytes;
+#pragma unroll
+            for (int kk = 0; kk < kChunk / 16; ++kk) {
+              umma_bf16_ss(d_tmem, make_sdesc(a_addr + kk * 32, 0, 1024),
+                           make_sdesc(b_addr + kk * 32, 0, 1024), idesc_gram,
+                           (kc | kk) != 0);
+            }
+            umma_commit(&bar->ring_empty[s]);
+          }
+          umma_commit(&bar->s_full[b]);
+        }
+        if (u.pv && n >= 1) {
+          // ---- PV(n-1): O += P Z_J[:, slice]
+          const int m = n - 1, pb = m & 1;
+          mbar_wait(&bar->p_full[pb], (m >> 1) & 1);
+          mbar_wait(&bar->v_full, m & 1);
+          tc_fence_after();
+          const uint32_t p_addr = smem_u32(smem + kSmemP + pb * kPBytes);
+          const uint32_t v_addr = smem_u32(smem + kSmemV);
+#pragma unroll
+          for (int kk = 0; kk < kTile / 16; ++kk) {
+            const uint64_t adesc =
+                make_sdesc(p_addr + (kk >> 2) * kChunkBytes + (kk & 3) * 32, 0, 1024);
+            const uint64_t bdesc = make_sdesc(v_addr + kk * 2048, kChunkBytes, 1024);
+            umma_bf16_ss(tmem_o, adesc, bdesc, idesc_pv, (m | kk) != 0);
+          }
+          umma_commit(&bar->p_empty[pb]);
+          umma_commit(&bar->v_empty);
+        }
+      }
+      if (u.pv) umma_commit(&bar->o_full);
+    }
+  } else if (warp < 8) {
+    // ===================== epilogue warps =====================
+    const int q = warp & 3, g = warp >> 2;
+    const int row = q * 32 + lane;
+    const uint32_t lane_addr = static_cast<uint32_t>(q * 32) << 16;
+    const float c0 = p.par[0], m2c0 = p.par[1];
+    const float ni = p.nrms[static_cast<int64_t>(u.ti) * kTile + row];
+    float coef_x[VGAN_B200_MAX_SCALES], coef_y[VGAN_B200_MAX_SCALES], ratio[VGAN_B200_MAX_SCALES];
+#pragma unroll
+    for (int m = 0; m < VGAN_B200_MAX_SCALES; ++m) {
+      ratio[m] = p.par[2 + m];
+      coef_x[m] = p.par[10 + m];
+      coef_y[m] = p.par[18 + m];
+    }
+    (void)c0;
+    float acc_x = 0.f, acc_y = 0.f;   // sum of k over X / Y columns (weighted by symmetry)
+    float rsum = 0.f;                 // sum_j P_ij over this thread's column half
+
+    for (int n = 0; n < n_tiles; ++n) {
+      const int jt = u.j_begin + n;
+      const int b = n & 1;
+      const bool col_is_x = jt < p.tiles_x;
+      const float fac = (u.sym && jt != u.ti) ? 2.f : 1.f;
+      float cf[VGAN_B200_MAX_SCALES];
+#pragma unroll
+      for (int m = 0; m < VGAN_B200_MAX_SCALES; ++m) cf[m] = col_is_x ? coef_x[m] : coef_y[m];
+      mbar_wait(&bar->nj_full[b], (n >> 1) & 1);
+      mbar_wait(&bar->s_full[b], (n >> 1) & 1);
+      tc_fence_after();
+      if (u.pv) mbar_wait(&bar->p_empty[b], ((n >> 1) & 1) ^ 1);   // PV(n-2) done with P[b]
+      uint8_t* p_row = smem + kSmemP + b * kPBytes + g * kChunkBytes + row * 128;
+      const float* njp = nj_smem + b * kTile + g * 64;
+      float ksum = 0.f;
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        uint32_t v[32];
+        tmem_ld_32x32(tmem + lane_addr + b * kTile + g * 64 + half * 32, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {   // 8 columns -> one 16-byte chunk of 8 bf16
+          const float4 nja = *reinterpret_cast<const float4*>(njp + half * 32 + c * 8);
+          const float4 njb = *reinterpret_cast<const float4*>(njp + half * 32 + c * 8 + 4);
+          const float njv[8] = {nja.x, nja.y, nja.z, nja.w, njb.x, njb.y, njb.z, njb.w};
+          float w[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            float uarg = fmaf(__uint_as_float(v[c * 8 + e]), m2c0, ni + njv[e]);
+            uarg = fmaxf(uarg, 0.f);
+            if (LADDER) {
+              const float t1 = ex2_approx(-uarg);
+              const float t2 = t1 * t1, t4 = t2 * t2, t8 = t4 * t4, t16 = t8 * t8;
+              ksum += (t1 + t2) + (t4 + t8) + t16;
+              // scale index 4 is the widest kernel (t1), index 0 the narrowest (t16)
+              w[e] = fmaf(t16, cf[0],
+                          fmaf(t8, cf[1], fmaf(t4, cf[2], fmaf(t2, cf[3], t1 * cf[4]))));
+            } else {
+              float kk = 0.f, ww = 0.f;
+              for (int m = 0; m < p.n_scales; ++m) {
+                const float em = ex2_approx(-uarg * ratio[m]);
+                kk += em;
+                ww = fmaf(em, cf[m], ww);
+              }
+              ksum += kk;
+              w[e] = ww;
+            }
+            rsum += w[e];
+          }
+          if (u.pv) {
+            uint4 pk;
+            pk.x = pack_bf16x2(w[0], w[1]);
+            pk.y = pack_bf16x2(w[2], w[3]);
+            pk.z = pack_bf16x2(w[4], w[5]);
+            pk.w = pack_bf16x2(w[6], w[7]);
+            const int chunk16 = half * 4 + c;   // 128B-swizzled K-major A operand
+            *reinterpret_cast<uint4*>(p_row + ((chunk16 ^ (row & 7)) << 4)) = pk;
+          }
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(&bar->s_empty[b]);
+      if (u.pv) {
+        fence_proxy_async_smem();
+        mbar_arrive(&bar->p_full[b]);
+      }
+      if (col_is_x) acc_x = fmaf(ksum, fac, acc_x); else acc_y += ksum;
+    }
+
+    // ---- block sums (only slice 0 owns them)
+    acc_x = warp_sum(acc_x);
+    acc_y = warp_sum(acc_y);
+    if (lane == 0) {
+      bar->red[warp][0] = acc_x;
+      bar->red[warp][1] = acc_y;
+    }
+    nj_smem[g * kTile + row] = rsum;   // norms are dead by now: reuse as the row-sum exchange
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    if (threadIdx.x == 0 && u.slice == 0) {
+      double sx = 0.0, sy = 0.0;
+      for (int wv = 0; wv < 8; ++wv) {
+        sx += bar->red[wv][0];
+        sy += bar->red[wv][1];
+      }
+      if (u.row_is_x) {
+        atomicAdd(&p.sums[0], sx);            // X rows x X cols -> S_xx (x Y cols is S_xy again)
+      } else {
+        atomicAdd(&p.sums[1], sx);            // Y rows x X cols -> S_xy
+        atomicAdd(&p.sums[2], sy);            // Y rows x Y cols -> S_yy
+      }
+    }
+
+    // ---- gradient rows: dZ_i[slice] = 4 c_i (O_i - rowsum(P)_i z_i)  (x dY_mul)
+    if (u.pv) {
+      const float rtot = nj_smem[row] + nj_smem[kTile + row];
+      const int64_t region_row = static_cast<int64_t>(u.row_is_x ? u.ti : u.ti - p.tiles_x) * kTile + row;
+      const int64_t n_region = u.row_is_x ? p.Nx : p.Ny;
+      const bool row_ok = region_row < n_region && region_row >= p.row_begin && region_row < p.row_end;
+      const float ci4 = 4.f * (u.row_is_x ? 1.f / static_cast<float>(p.Nx) : -1.f / static_cast<float>(p.Ny));
+      float* out = (u.row_is_x ? p.dX : p.dY) + (region_row - p.row_begin) * p.D;
+      const float* mul = (!u.row_is_x && p.dY_mul) ? p.dY_mul + (region_row - p.row_begin) * p.D : nullptr;
+      const __nv_bfloat16* zrow = p.zq + (static_cast<int64_t>(u.ti) * kTile + row) * p.Dp;
+      const int f_slice = u.slice * p.slice_chunks * kChunk;
+      mbar_wait(&bar->o_full, 0);
+      tc_fence_after();
+      for (int cc = 0; cc < slice_chunks; ++cc) {
+        const int col = g * (slice_w / 2) + cc * 32;
+        uint32_t v[32];
+        tmem_ld_32x32(tmem_o + lane_addr + col, v);
+        tmem_ld_wait();
+        if (row_ok) {
+          const uint4* z4 = reinterpret_cast<const uint4*>(zrow + f_slice + col);
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            const uint4 zz = z4[c];
+            const uint32_t zw[4] = {zz.x, zz.y, zz.z, zz.w};
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              const float z = __uint_as_float((e & 1) ? (zw[e >> 1] & 0xffff0000u) : (zw[e >> 1] << 16));
+              const int f = f_slice + col + c * 8 + e;
+              if (f < p.D) {
+                float gval = ci4 * (__uint_as_float(v[c * 8 + e]) - rtot * z);
+                if (mul) gval *= mul[f];
+                out[f] = gval;
+              }
+            }
+          }
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 11) tmem_dealloc(tmem, 512);
+}
+
+int launch_tc(const TcParams& p, const CUtensorMap& map, int ladder, cudaStream_t st) {
+  const int ngrad = (p.gx_end - p.gx_begin) + (p.gy_end - p.gy_begin);
+  const int grid = ngrad * p.nslices + p.n_xx_units;
+  if (grid <= 0) return VGAN_B200_OK;
+  auto kern = ladder ? mmd2_tc_kernel<true> : mmd2_tc_kernel<false>;
+  VG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
+  kern<<<grid, kThreads, kSmemTotal, st>>>(map, p);
+  VG_CUDA_CHECK(cudaGetLastError());
+  return VGAN_B200_OK;
+}
+
+}  // namespace vg

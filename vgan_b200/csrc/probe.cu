@@ -1,0 +1,111 @@
+// Debug aid (vgan_b200_umma_probe): one Gram tile and one gradient tile through exactly
+// the descriptors K1 uses — K-major SW128 A/B for S = A B^T, then bf16(S) written to shared
+// memory in the swizzled K-major A layout and B re-read as an MN-major operand spanning two
+// 64-column blocks (LBO) for O = bf16(S) B.  Raw S and O are returned so a test can tell
+// which descriptor is wrong.  A, B: bf16 [128,128] row-major.
+#include "common.cuh"
+#include "ptx.cuh"
+
+namespace vg {
+
+constexpr int kProbeSmem = 4 * kChunkBytes /*A0 A1 B0 B1*/ + 2 * kChunkBytes /*P*/ + 1024 + 256;
+
+__global__ void __launch_bounds__(128, 1)
+umma_probe_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
+                  float* __restrict__ S_out, float* __restrict__ O_out) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  uint8_t* sA = smem;                       // 2 chunks [128 x 64]
+  uint8_t* sB = smem + 2 * kChunkBytes;     // 2 chunks [128 x 64]
+  uint8_t* sP = smem + 4 * kChunkBytes;     // 2 K-major atoms [128 x 64]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 6 * kChunkBytes);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 4);
+  const int warp = threadIdx.x >> 5;
+
+  if (threadIdx.x == 0) {
+    mbar_init(&bars[0], 1);
+    mbar_init(&bars[1], 1);
+    mbar_init(&bars[2], 1);
+    fence_barrier_init();
+  }
+  if (warp == 0) {
+    tmem_alloc(tmem_slot, 256);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  if (threadIdx.x == 0) {
+    mbar_arrive_expect_tx(&bars[0], 4 * kChunkBytes);
+    for (int c = 0; c < 2; ++c) {
+      tma_load_2d(sA + c * kChunkBytes, &mapA, &bars[0], c * kChunk, 0);
+      tma_load_2d(sB + c * kChunkBytes, &mapB, &bars[0], c * kChunk, 0);
+    }
+    mbar_wait(&bars[0], 0);
+    tc_fence_after();
+    constexpr uint32_t idesc = make_idesc_bf16(128, 128, 0, 0);
+    for (int c = 0; c < 2; ++c)
+      for (int kk = 0; kk < 4; ++kk)
+        umma_bf16_ss(tmem, make_sdesc(smem_u32(sA) + c * kChunkBytes + kk * 32, 0, 1024),
+                     make_sdesc(smem_u32(sB) + c * kChunkBytes + kk * 32, 0, 1024), idesc,
+                     (c | kk) != 0);
+    umma_commit(&bars[1]);
+  }
+  mbar_wait(&bars[1], 0);
+  tc_fence_after();
+  const int row = threadIdx.x;
+  const uint32_t lane_addr = static_cast<uint32_t>(warp * 32) << 16;
+  for (int cc = 0; cc < 4; ++cc) {
+    uint32_t v[32];
+    tmem_ld_32x32(tmem + lane_addr + cc * 32, v);
+    tmem_ld_wait();
+    for (int e = 0; e < 32; ++e) S_out[row * 128 + cc * 32 + e] = __uint_as_float(v[e]);
+    for (int c = 0; c < 4; ++c) {
+      uint4 pk;
+      pk.x = pack_bf16x2(__uint_as_float(v[c * 8 + 0]), __uint_as_float(v[c * 8 + 1]));
+      pk.y = pack_bf16x2(__uint_as_float(v[c * 8 + 2]), __uint_as_float(v[c * 8 + 3]));
+      pk.z = pack_bf16x2(__uint_as_float(v[c * 8 + 4]), __uint_as_float(v[c * 8 + 5]));
+      pk.w = pack_bf16x2(__uint_as_float(v[c * 8 + 6]), __uint_as_float(v[c * 8 + 7]));
+      const int j = cc * 32 + c * 8;             // first column of this 16-byte chunk
+      const int atom = j >> 6, chunk16 = (j & 63) >> 3;
+      *reinterpret_cast<uint4*>(sP + atom * kChunkBytes + row * 128 + ((chunk16 ^ (row & 7)) << 4)) = pk;
+    }
+  }
+  tc_fence_before();
+  fence_proxy_async_smem();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    tc_fence_after();
+    constexpr uint32_t idesc_pv = make_idesc_bf16(128, 128, 0, 1);
+    for (int kk = 0; kk < 8; ++kk)
+      umma_bf16_ss(tmem + 128,
+                   make_sdesc(smem_u32(sP) + (kk >> 2) * kChunkBytes + (kk & 3) * 32, 0, 1024),
+                   make_sdesc(smem_u32(sB) + kk * 2048, kChunkBytes, 1024), idesc_pv, kk != 0);
+    umma_commit(&bars[2]);
+  }
+  mbar_wait(&bars[2], 0);
+  tc_fence_after();
+  for (int cc = 0; cc < 4; ++cc) {
+    uint32_t v[32];
+    tmem_ld_32x32(tmem + 128 + lane_addr + cc * 32, v);
+    tmem_ld_wait();
+    for (int e = 0; e < 32; ++e) O_out[row * 128 + cc * 32 + e] = __uint_as_float(v[e]);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem, 256);
+}
+
+int launch_probe(const CUtensorMap& mapA, const CUtensorMap& mapB, float* S_out, float* O_out,
+                 cudaStream_t st) {
+  VG_CUDA_CHECK(cudaFuncSetAttribute(umma_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     kProbeSmem));
+  umma_probe_kernel<<<1, 128, kProbeSmem, st>>>(mapA, mapB, S_out, O_out);
+  VG_CUDA_CHECK(cudaGetLastError());
+  return VGAN_B200_OK;
+}
+
+}  // namespace vg

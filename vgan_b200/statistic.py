@@ -1,0 +1,74 @@
+"""``MMDStatistic`` with the call convention of torch_two_sample (josipd/torch-two-sample,
+unpinned and absent in the reference environment) as V-GAN uses it in ``check_if_myopic``
+(/root/reference/src/vgan.py:419-428, 696-705):
+
+    mmd = MMDStatistic(n_1, n_2)
+    value, K = mmd(sample_1, sample_2, alphas=[a], ret_matrix=True)
+    p = mmd.pval(K, n_permutations=1000)
+
+Unbiased (diagonal-removed) MMD^2 with k = sum_a exp(-a (d2 + 1e-5)).  The kernel matrix comes
+from the CUDA ``mmd2_matrix`` kernel; the permutation test evaluates all relabelings as one
+batched quadratic form on the device instead of the upstream Cython O(n_perm n^2) loop.
+Parity for this class is UNPINNED (no upstream source or vectors available): it is checked
+against the restatement in oracle/mmd_oracle.py only."""
+from __future__ import annotations
+
+import torch
+
+from . import _lib
+from .loss import _as_input, _ptr, _stream
+
+
+class MMDStatistic:
+    def __init__(self, n_1, n_2):
+        self.n_1 = n_1
+        self.n_2 = n_2
+        self.a00 = 1. / (n_1 * (n_1 - 1))
+        self.a11 = 1. / (n_2 * (n_2 - 1))
+        self.a01 = - 1. / (n_1 * n_2)
+
+    def _statistic(self, K, member_1):
+        """member_1: [P, n] {0,1} float rows marking sample 1; returns [P] statistics."""
+        KA = member_1 @ K
+        aKa = (KA * member_1).sum(1)
+        aK1 = KA.sum(1)
+        total = K.sum()
+        diag = torch.diagonal(K)
+        d1 = member_1 @ diag
+        d2 = diag.sum() - d1
+        aKb = aK1 - aKa
+        bKb = total - 2.0 * aK1 + aKa
+        return self.a00 * (aKa - d1) + self.a11 * (bKb - d2) + 2.0 * self.a01 * aKb
+
+    def __call__(self, sample_1, sample_2, alphas, ret_matrix=False):
+        if sample_1.device.type != "cuda":
+            raise RuntimeError("vgan_b200.MMDStatistic needs CUDA tensors on an sm_100 device")
+        dev = sample_1.device
+        Z = torch.cat([_as_input(sample_1, dev), _as_input(sample_2, dev)], 0).contiguous()
+        n, D = Z.shape
+        if n != self.n_1 + self.n_2:
+            raise RuntimeError("MMDStatistic: sample sizes do not match n_1, n_2")
+        inv = torch.tensor([float(a) for a in alphas], dtype=torch.float32, device=dev)
+        if inv.numel() < 1 or inv.numel() > _lib.MAX_SCALES:
+            raise RuntimeError(f"MMDStatistic: between 1 and {_lib.MAX_SCALES} alphas are supported")
+        K = torch.empty((n, n), dtype=torch.float32, device=dev)
+        _lib.check(_lib.lib().vgan_b200_mmd2_matrix(_ptr(Z), n, D, _ptr(inv), inv.numel(), 1e-5, _ptr(K),
+                                                    _stream()), "mmd2_matrix")
+        member = torch.zeros(1, n, dtype=torch.float64, device=dev)
+        member[0, :self.n_1] = 1
+        mmd = self._statistic(K.double(), member)[0].float()
+        if ret_matrix:
+            return mmd, K
+        return mmd
+
+    def pval(self, distances, n_permutations=1000):
+        """Fraction of random relabelings whose statistic is >= the observed one."""
+        K = distances.double()
+        n = K.shape[0]
+        dev = K.device
+        member = torch.zeros(n_permutations + 1, n, dtype=torch.float64, device=dev)
+        member[0, :self.n_1] = 1
+        order = torch.rand(n_permutations, n, device=dev).argsort(1)
+        member[1:].scatter_(1, order[:, :self.n_1], 1.0)
+        st = self._statistic(K, member)
+        return float((st[1:] >= st[0]).double().mean().item())
