@@ -1,0 +1,53 @@
+"""Row-tile sharding of one MMD^2 evaluation across the GPUs of a node.
+
+The pairwise matrix is split by row tiles: rank g computes the gradient rows
+[g*N/G, (g+1)*N/G) of Y = U*X against ALL columns (complete dL/dU rows, no reduction needed),
+the partial sums S_xy, S_yy of those rows and the S_xx tiles t = g (mod G).  The only exchange
+is ONE all-reduce per step of [S_xx, S_xy, S_yy | colsum_i dL/dU[i,:]] (3 + D doubles) over
+NCCL/NVLink.  Inputs are replicated (the generator MLP is tiny and data-parallel replicas
+produce the same U from the same noise)."""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+
+from .loss import default_precision, mmd2_eval
+
+
+def shard_rows(N: int, rank: int, world: int, tile: int = 128):
+    """Contiguous, tile-aligned row range of rank `rank` (the last rank takes the remainder)."""
+    tiles = (N + tile - 1) // tile
+    per = (tiles + world - 1) // world
+    b = min(rank * per * tile, N)
+    e = min((rank + 1) * per * tile, N)
+    return b, e
+
+
+def sharded_masked_step(loss_fn, X, U, rank: int = 0, world: int = 1, group=None, time_k1: bool = True):
+    """loss(X, U*X, U) and dL/dU rows of this rank; returns dict(loss, dU, rows, dU_colsum, k1_events).
+
+    With world == 1 this is exactly ``loss_fn.forward_masked(X, U)`` + backward, without autograd."""
+    N, D = X.shape
+    kernel = loss_fn.kernel
+    bw, frozen = kernel._bw_state(X.device)
+    prec = loss_fn.precision or default_precision(D)
+    b, e = shard_rows(N, rank, world)
+    ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) if time_k1 else None
+    if e <= b:      # more ranks than row tiles: this rank only joins the all-reduce
+        raise RuntimeError("sharded_masked_step: fewer 128-row tiles than ranks")
+    out = mmd2_eval(X, None, U, weight=float(loss_fn.weight), bw_dev=bw, frozen=frozen, mults=kernel._mults,
+                    precision=prec, need_dX=False, need_dY=True, masked=True, penalty_grad=True,
+                    row_begin=b, row_end=e, xx_part=rank, xx_nparts=world, center=loss_fn.center,
+                    finalize=(world == 1), k1_events=ev)
+    kernel._freeze()
+    dU = out["dY"]
+    colsum = dU.sum(0, dtype=torch.float64)
+    if world > 1:
+        packed = torch.cat([out["sums"][:3], colsum])
+        dist.all_reduce(packed, group=group)
+        sums, colsum = packed[:3], packed[3:]
+        # the penalty (column max over ALL rows of the replicated U) is identical on every rank
+        loss = (sums[0] / (N * N) - 2.0 * sums[1] / (N * N) + sums[2] / (N * N)).float() + out["penalty"][0]
+    else:
+        loss = out["loss"][0]
+    return dict(loss=loss, dU=dU, rows=(b, e), dU_colsum=colsum.float(), k1_events=ev, sums=out["sums"])

@@ -74,14 +74,15 @@ def _workspace(Nx, Ny, D, D_u, flags, device) -> _Workspace:
 def default_precision(D: int) -> str:
     """bf16 tensor-core path by default; tiny feature widths (the VGAN encodings,
     latent = D//16) go to the fp32 CUDA-core path where a 64-wide K chunk would be padding."""
-    return "fp32" if D < 16 else "bf16"
+    return "fp32" if D < 32 else "bf16"
 
 
 def mmd2_eval(X: torch.Tensor, Y: Optional[torch.Tensor], U: Optional[torch.Tensor], *,
               weight: float, bw_dev: torch.Tensor, frozen: bool, mults, precision: str = "bf16",
               need_dX: bool = False, need_dY: bool = True, masked: bool = False,
               penalty_grad: bool = True, row_begin: int = 0, row_end: Optional[int] = None,
-              xx_part: int = 0, xx_nparts: int = 1, center: bool = True, finalize: bool = True):
+              xx_part: int = 0, xx_nparts: int = 1, center: bool = True, finalize: bool = True,
+              k1_events=None):
     """Run prologue -> scales -> fused fwd+bwd -> penalty -> finalize on the current stream.
 
     ``masked=True``: Y is formed as U*X inside the prologue and the returned ``dY`` is already
@@ -117,9 +118,13 @@ def mmd2_eval(X: torch.Tensor, Y: Optional[torch.Tensor], U: Optional[torch.Tens
     dY = torch.empty((min(row_end, Ny) - row_begin, D), dtype=torch.float32, device=dev) if want_grad else None
     dX = torch.empty((min(row_end, Nx) - row_begin, D), dtype=torch.float32, device=dev) if need_dX else None
     mul = X[row_begin:] if (masked and want_grad) else None
+    if k1_events is not None:
+        k1_events[0].record()
     _lib.check(L.vgan_b200_mmd2_fwd_bwd(ws.ptr, Nx, Ny, D, row_begin, row_end, xx_part, xx_nparts,
                                         _ptr(ws.inv_scales), len(mults), flags, _ptr(ws.sums), _ptr(dY),
                                         _ptr(mul), _ptr(dX), st), "mmd2_fwd_bwd")
+    if k1_events is not None:
+        k1_events[1].record()
     dU_pen = None
     if U is not None and weight != 0:
         tgt = None
