@@ -121,7 +121,7 @@ def main():
     ap.add_argument("--n", type=int, default=N_DEFAULT)
     ap.add_argument("--d", type=int, default=D_DEFAULT)
     ap.add_argument("--precision", default="bf16")
-    ap.add_argument("--cpu-rows", type=int, default=128)
+    ap.add_argument("--cpu-rows", type=int, default=4096)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     args = ap.parse_args()

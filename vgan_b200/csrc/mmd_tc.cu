@@ -20,9 +20,8 @@
 
 namespace vg {
 
-constexpr int kStages = 3;
-constexpr int kStageBytes = 2 * kChunkBytes;                 // Z_I chunk + Z_J chunk
-constexpr int kVBytes = (kSliceMax / kChunk) * kChunkBytes;  // 64 KiB
+constexpr int kStages = 5;
+constexpr int kStageBytes = 2 * kChunkBytes;   // Gram: Z_I chunk + Z_J chunk;  PV: two V chunks (128 features)
 constexpr int kPBytes = 2 * kChunkBytes;                     // 128 x 128 bf16
 constexpr int kNumEpiThreads = 256;
 constexpr int kThreads = 384;
@@ -32,18 +31,16 @@ struct __align__(8) TcBarriers {
   uint64_t s_full[2], s_empty[2];
   uint64_t nj_full[2];
   uint64_t p_full[2], p_empty[2];
-  uint64_t v_full, v_empty;
   uint64_t o_full;
   uint32_t tmem_base;
   float red[8][4];
 };
 
 constexpr int kSmemRing = 0;
-constexpr int kSmemV = kSmemRing + kStages * kStageBytes;
-constexpr int kSmemP = kSmemV + kVBytes;
+constexpr int kSmemP = kSmemRing + kStages * kStageBytes;
 constexpr int kSmemNj = kSmemP + 2 * kPBytes;
 constexpr int kSmemBar = kSmemNj + 2 * kTile * 4;
-constexpr int kSmemTotal = kSmemBar + static_cast<int>(sizeof(TcBarriers)) + 1024;  // + align slack
+constexpr int kSmemTotal = kSmemBar + static_cast<int>(sizeof(TcBarriers));
 static_assert(kSmemTotal <= 232448, "shared memory budget");
 
 struct Unit {
@@ -86,9 +83,8 @@ __device__ __forceinline__ Unit decode_unit(const TcParams& p) {
 template <bool LADDER>
 __global__ void __launch_bounds__(kThreads, 1)
 mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const TcParams p) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                             ~static_cast<uintptr_t>(1023));
+  extern __shared__ __align__(1024) uint8_t smem[];   // SWIZZLE_128B tiles need 1024-byte alignment
+  if ((smem_u32(smem) & 1023u) != 0) __trap();
   TcBarriers* bar = reinterpret_cast<TcBarriers*>(smem + kSmemBar);
   float* nj_smem = reinterpret_cast<float*>(smem + kSmemNj);
 
@@ -112,8 +108,6 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const TcParams p) {
       mbar_init(&bar->p_full[b], kNumEpiThreads);
       mbar_init(&bar->p_empty[b], 1);
     }
-    mbar_init(&bar->v_full, 1);
-    mbar_init(&bar->v_empty, 1);
     mbar_init(&bar->o_full, 1);
     fence_barrier_init();
   }
@@ -129,23 +123,41 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const TcParams p) {
   const uint32_t tmem_o = tmem + 256;
 
   if (warp == 8) {
-    // ===================== TMA producer: Gram operand ring =====================
+    // ===================== TMA producer: one ring for Gram operands and V slices ==========
+    // Stages are issued in exactly the order the MMA thread consumes them:
+    //   Gram(0), Gram(1), PV(0), Gram(2), PV(1), ...
     if (lane == 0) {
       uint32_t it = 0;
-      for (int n = 0; n < n_tiles; ++n) {
-        const int jt = u.j_begin + n;
-        for (int kc = 0; kc < p.kchunks; ++kc, ++it) {
-          const uint32_t s = it % kStages, ph = (it / kStages) & 1;
-          mbar_wait(&bar->ring_empty[s], ph ^ 1);
-          uint8_t* dst = smem + kSmemRing + s * kStageBytes;
-          mbar_arrive_expect_tx(&bar->ring_full[s], kStageBytes);
-          tma_load_2d(dst, &zmap, &bar->ring_full[s], kc * kChunk, u.ti * kTile);
-          tma_load_2d(dst + kChunkBytes, &zmap, &bar->ring_full[s], kc * kChunk, jt * kTile);
+      const int pv_stages = (slice_chunks + 1) >> 1;
+      for (int n = 0; n <= n_tiles; ++n) {
+        if (n < n_tiles) {
+          const int jt = u.j_begin + n;
+          for (int kc = 0; kc < p.kchunks; ++kc, ++it) {
+            const uint32_t s = it % kStages, ph = (it / kStages) & 1;
+            mbar_wait(&bar->ring_empty[s], ph ^ 1);
+            uint8_t* dst = smem + kSmemRing + s * kStageBytes;
+            mbar_arrive_expect_tx(&bar->ring_full[s], kStageBytes);
+            tma_load_2d(dst, &zmap, &bar->ring_full[s], kc * kChunk, u.ti * kTile);
+            tma_load_2d(dst + kChunkBytes, &zmap, &bar->ring_full[s], kc * kChunk, jt * kTile);
+          }
+        }
+        if (u.pv && n >= 1) {
+          const int jt = u.j_begin + n - 1;
+          for (int h = 0; h < pv_stages; ++h, ++it) {
+            const uint32_t s = it % kStages, ph = (it / kStages) & 1;
+            const int nch = min(2, slice_chunks - 2 * h);
+            mbar_wait(&bar->ring_empty[s], ph ^ 1);
+            uint8_t* dst = smem + kSmemRing + s * kStageBytes;
+            mbar_arrive_expect_tx(&bar->ring_full[s], nch * kChunkBytes);
+            for (int c = 0; c < nch; ++c)
+              tma_load_2d(dst + c * kChunkBytes, &zmap, &bar->ring_full[s],
+                          (u.slice * p.slice_chunks + 2 * h + c) * kChunk, jt * kTile);
+          }
         }
       }
     }
   } else if (warp == 10) {
-    // ===================== TMA producer: column norms + V slice =====================
+    // ===================== bulk-copy producer: scaled column norms =====================
     if (lane == 0) {
       for (int n = 0; n < n_tiles; ++n) {
         const int jt = u.j_begin + n;
@@ -154,20 +166,12 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const TcParams p) {
         mbar_arrive_expect_tx(&bar->nj_full[b], kTile * 4);
         bulk_load_1d(nj_smem + b * kTile, p.nrms + static_cast<int64_t>(jt) * kTile, kTile * 4,
                      &bar->nj_full[b]);
-        if (u.pv) {
-          mbar_wait(&bar->v_empty, (n & 1) ^ 1);           // PV(n-1) finished reading V
-          mbar_arrive_expect_tx(&bar->v_full, slice_chunks * kChunkBytes);
-          for (int c = 0; c < slice_chunks; ++c)
-            tma_load_2d(smem + kSmemV + c * kChunkBytes, &zmap, &bar->v_full,
-                        (u.slice * p.slice_chunks + c) * kChunk, jt * kTile);
-        }
       }
     }
   } else if (warp == 9) {
     // ===================== MMA issuer (one thread) =====================
     if (lane == 0) {
       constexpr uint32_t idesc_gram = make_idesc_bf16(kTile, kTile, 0, 0);
-      const uint32_t idesc_pv = make_idesc_bf16(kTile, slice_w, 0, 1);
       uint32_t it = 0;
       for (int n = 0; n <= n_tiles; ++n) {
         if (n < n_tiles) {
@@ -196,19 +200,26 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const TcParams p) {
           // ---- PV(n-1): O += P Z_J[:, slice]
           const int m = n - 1, pb = m & 1;
           mbar_wait(&bar->p_full[pb], (m >> 1) & 1);
-          mbar_wait(&bar->v_full, m & 1);
           tc_fence_after();
           const uint32_t p_addr = smem_u32(smem + kSmemP + pb * kPBytes);
-          const uint32_t v_addr = smem_u32(smem + kSmemV);
+          const int pv_stages = (slice_chunks + 1) >> 1;
+          for (int h = 0; h < pv_stages; ++h, ++it) {
+            const uint32_t s = it % kStages, ph = (it / kStages) & 1;
+            const int nch = min(2, slice_chunks - 2 * h);
+            const uint32_t idesc_pv = make_idesc_bf16(kTile, nch * kChunk, 0, 1);
+            mbar_wait(&bar->ring_full[s], ph);
+            tc_fence_after();
+            const uint32_t v_addr = smem_u32(smem + kSmemRing + s * kStageBytes);
 #pragma unroll
-          for (int kk = 0; kk < kTile / 16; ++kk) {
-            const uint64_t adesc =
-                make_sdesc(p_addr + (kk >> 2) * kChunkBytes + (kk & 3) * 32, 0, 1024);
-            const uint64_t bdesc = make_sdesc(v_addr + kk * 2048, kChunkBytes, 1024);
-            umma_bf16_ss(tmem_o, adesc, bdesc, idesc_pv, (m | kk) != 0);
+            for (int kk = 0; kk < kTile / 16; ++kk) {
+              const uint64_t adesc =
+                  make_sdesc(p_addr + (kk >> 2) * kChunkBytes + (kk & 3) * 32, 0, 1024);
+              const uint64_t bdesc = make_sdesc(v_addr + kk * 2048, kChunkBytes, 1024);
+              umma_bf16_ss(tmem_o + h * 2 * kChunk, adesc, bdesc, idesc_pv, (m | kk) != 0);
+            }
+            umma_commit(&bar->ring_empty[s]);
           }
           umma_commit(&bar->p_empty[pb]);
-          umma_commit(&bar->v_empty);
         }
       }
       if (u.pv) umma_commit(&bar->o_full);
