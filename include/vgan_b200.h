@@ -121,6 +121,10 @@ int vgan_b200_mmd2_matrix(const float* Z, int64_t n, int64_t D, const float* inv
 /* Debug aid: one Gram tile and one gradient tile through the tcgen05 pipeline with raw
  * outputs, used by tests to localise descriptor/layout errors. A,B bf16 [128,128] row-major;
  * S_out float [128,128] = A B^T;  O_out float [128,128] = bf16(S) B. */
+/* Debug aid: when buf != NULL, the next bf16 mmd2_fwd_bwd calls add the kernel sum of every
+ * (work unit, column tile) to buf[unit * stride + tile] (device floats).  NULL switches it off. */
+int vgan_b200_debug_tile_sums(float* buf, int stride);
+
 int vgan_b200_umma_probe(const void* A, const void* B, float* S_out, float* O_out, void* stream);
 
 #ifdef __cplusplus

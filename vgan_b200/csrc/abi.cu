@@ -82,6 +82,9 @@ int launch_simt_from_abi(const vgan_b200_layout_t& L, void* ws, int64_t row_begi
                          int xx_nparts, const float* inv_scales, int n_scales, int flags, double* sums,
                          float* dY, const float* dY_mul, float* dX, cudaStream_t st);
 
+static float* g_dbg = nullptr;
+static int g_dbg_stride = 0;
+
 static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 static int fill_layout(int64_t Nx, int64_t Ny, int64_t D, int64_t D_u, int flags, vgan_b200_layout_t* L) {
@@ -231,6 +234,7 @@ int vgan_b200_mmd2_fwd_bwd(void* ws, int64_t Nx, int64_t Ny, int64_t D, int64_t 
   p.nrms = reinterpret_cast<const float*>(base + L.off_nrms);
   p.par = par;
   p.sums = sums; p.dY = dY; p.dY_mul = dY_mul; p.dX = dX;
+  p.dbg = g_dbg; p.dbg_stride = g_dbg_stride;
   CUtensorMap map;
   if (int e = make_tmap_bf16_2d(&map, p.zq, static_cast<uint64_t>(L.Nxp + L.Nyp), static_cast<uint64_t>(L.Dp)))
     return e;
@@ -266,6 +270,12 @@ int vgan_b200_mmd2_matrix(const float* Z, int64_t n, int64_t D, const float* inv
     return VGAN_B200_ERR_ARG;
   }
   return launch_matrix(Z, n, D, inv_scales, n_scales, eps, K_out, static_cast<cudaStream_t>(stream));
+}
+
+int vgan_b200_debug_tile_sums(float* buf, int stride) {
+  g_dbg = buf;
+  g_dbg_stride = stride;
+  return VGAN_B200_OK;
 }
 
 int vgan_b200_umma_probe(const void* A, const void* B, float* S_out, float* O_out, void* stream) {

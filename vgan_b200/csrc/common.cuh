@@ -44,6 +44,8 @@ struct TcParams {
   float* dY;
   const float* dY_mul;
   float* dX;
+  float* dbg;                 // debug: per-(unit, tile) kernel sums, or nullptr
+  int dbg_stride;
 };
 
 #define VG_CUDA_CHECK(expr)                                                          \

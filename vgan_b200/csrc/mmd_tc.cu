@@ -127,24 +127,23 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const TcParams p) {
     // Stages are issued in exactly the order the MMA thread consumes them:
     //   Gram(0), Gram(1), PV(0), Gram(2), PV(1), ...
     if (lane == 0) {
-      uint32_t it = 0;
+      uint32_t s = 0, ph = 0;
       const int pv_stages = (slice_chunks + 1) >> 1;
       for (int n = 0; n <= n_tiles; ++n) {
         if (n < n_tiles) {
           const int jt = u.j_begin + n;
-          for (int kc = 0; kc < p.kchunks; ++kc, ++it) {
-            const uint32_t s = it % kStages, ph = (it / kStages) & 1;
+          for (int kc = 0; kc < p.kchunks; ++kc) {
             mbar_wait(&bar->ring_empty[s], ph ^ 1);
             uint8_t* dst = smem + kSmemRing + s * kStageBytes;
             mbar_arrive_expect_tx(&bar->ring_full[s], kStageBytes);
             tma_load_2d(dst, &zmap, &bar->ring_full[s], kc * kChunk, u.ti * kTile);
             tma_load_2d(dst + kChunkBytes, &zmap, &bar->ring_full[s], kc * kChunk, jt * kTile);
+            if (++s == kStages) { s = 0; ph ^= 1; }
           }
         }
         if (u.pv && n >= 1) {
           const int jt = u.j_begin + n - 1;
-          for (int h = 0; h < pv_stages; ++h, ++it) {
-            const uint32_t s = it % kStages, ph = (it / kStages) & 1;
+          for (int h = 0; h < pv_stages; ++h) {
             const int nch = min(2, slice_chunks - 2 * h);
             mbar_wait(&bar->ring_empty[s], ph ^ 1);
             uint8_t* dst = smem + kSmemRing + s * kStageBytes;
@@ -152,6 +151,7 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const TcParams p) {
             for (int c = 0; c < nch; ++c)
               tma_load_2d(dst + c * kChunkBytes, &zmap, &bar->ring_full[s],
                           (u.slice * p.slice_chunks + 2 * h + c) * kChunk, jt * kTile);
+            if (++s == kStages) { s = 0; ph ^= 1; }
           }
         }
       }
@@ -169,61 +169,75 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const TcParams p) {
       }
     }
   } else if (warp == 9) {
-    // ===================== MMA issuer (one thread) =====================
-    if (lane == 0) {
-      constexpr uint32_t idesc_gram = make_idesc_bf16(kTile, kTile, 0, 0);
-      uint32_t it = 0;
-      for (int n = 0; n <= n_tiles; ++n) {
-        if (n < n_tiles) {
-          // ---- Gram(n): S[b] = Z_I Z_J^T over all K chunks
-          const int b = n & 1;
-          mbar_wait(&bar->s_empty[b], ((n >> 1) & 1) ^ 1);
+    // ===================== MMA issuer =====================
+    // The whole warp runs the (warp-uniform) control flow so that addresses and descriptors live
+    // in uniform registers; one elected lane issues the tcgen05 instructions.
+    constexpr uint32_t idesc_gram = make_idesc_bf16(kTile, kTile, 0, 0);
+    // descriptor high word: SBO = 1024 B, version 1, SWIZZLE_128B; low word: address and LBO
+    constexpr uint32_t desc_hi = (1024u >> 4) | (1u << 14) | (2u << 29);
+    constexpr uint32_t lbo_v = (static_cast<uint32_t>(kChunkBytes) >> 4) << 16;   // MN-major V: next 64 features
+    const uint32_t ring_lo = (smem_u32(smem + kSmemRing) & 0x3FFFFu) >> 4;
+    const uint32_t p_lo0 = (smem_u32(smem + kSmemP) & 0x3FFFFu) >> 4;
+    const int pv_stages = (slice_chunks + 1) >> 1;
+    uint32_t s = 0, ph = 0;
+    for (int n = 0; n <= n_tiles; ++n) {
+      if (n < n_tiles) {
+        // ---- Gram(n): S[b] = Z_I Z_J^T over all K chunks
+        const int b = n & 1;
+        mbar_wait(&bar->s_empty[b], ((n >> 1) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem + b * kTile;
+        for (int kc = 0; kc < p.kchunks; ++kc) {
+          mbar_wait(&bar->ring_full[s], ph);
           tc_fence_after();
-          const uint32_t d_tmem = tmem + b * kTile;
-          for (int kc = 0; kc < p.kchunks; ++kc, ++it) {
-            const uint32_t s = it % kStages, ph = (it / kStages) & 1;
-            mbar_wait(&bar->ring_full[s], ph);
-            tc_fence_after();
-            const uint32_t a_addr = smem_u32(smem + kSmemRing + s * kStageBytes);
-            const uint32_t b_addr = a_addr + kChunkBytes;
+          const uint32_t a_lo = ring_lo + s * (kStageBytes >> 4);
+          const uint32_t b_lo = a_lo + (kChunkBytes >> 4);
+          if (elect_one()) {
 #pragma unroll
             for (int kk = 0; kk < kChunk / 16; ++kk) {
-              umma_bf16_ss(d_tmem, make_sdesc(a_addr + kk * 32, 0, 1024),
-                           make_sdesc(b_addr + kk * 32, 0, 1024), idesc_gram,
-                           (kc | kk) != 0);
+              const uint64_t adesc = (static_cast<uint64_t>(desc_hi) << 32) | (a_lo + kk * 2);
+              const uint64_t bdesc = (static_cast<uint64_t>(desc_hi) << 32) | (b_lo + kk * 2);
+              umma_bf16_ss(d_tmem, adesc, bdesc, idesc_gram, (kc | kk) != 0);
             }
             umma_commit(&bar->ring_empty[s]);
           }
-          umma_commit(&bar->s_full[b]);
+          __syncwarp();
+          if (++s == kStages) { s = 0; ph ^= 1; }
         }
-        if (u.pv && n >= 1) {
-          // ---- PV(n-1): O += P Z_J[:, slice]
-          const int m = n - 1, pb = m & 1;
-          mbar_wait(&bar->p_full[pb], (m >> 1) & 1);
+        if (elect_one()) umma_commit(&bar->s_full[b]);
+        __syncwarp();
+      }
+      if (u.pv && n >= 1) {
+        // ---- PV(n-1): O += P Z_J[:, slice]   (two 64-feature chunks = 128 columns of O per stage)
+        const int m = n - 1, pb = m & 1;
+        mbar_wait(&bar->p_full[pb], (m >> 1) & 1);
+        tc_fence_after();
+        const uint32_t p_lo = p_lo0 + pb * (kPBytes >> 4);
+        for (int h = 0; h < pv_stages; ++h) {
+          const int nch = min(2, slice_chunks - 2 * h);
+          const uint32_t idesc_pv = make_idesc_bf16(kTile, nch * kChunk, 0, 1);
+          mbar_wait(&bar->ring_full[s], ph);
           tc_fence_after();
-          const uint32_t p_addr = smem_u32(smem + kSmemP + pb * kPBytes);
-          const int pv_stages = (slice_chunks + 1) >> 1;
-          for (int h = 0; h < pv_stages; ++h, ++it) {
-            const uint32_t s = it % kStages, ph = (it / kStages) & 1;
-            const int nch = min(2, slice_chunks - 2 * h);
-            const uint32_t idesc_pv = make_idesc_bf16(kTile, nch * kChunk, 0, 1);
-            mbar_wait(&bar->ring_full[s], ph);
-            tc_fence_after();
-            const uint32_t v_addr = smem_u32(smem + kSmemRing + s * kStageBytes);
+          const uint32_t v_lo = ring_lo + s * (kStageBytes >> 4);
+          if (elect_one()) {
 #pragma unroll
             for (int kk = 0; kk < kTile / 16; ++kk) {
-              const uint64_t adesc =
-                  make_sdesc(p_addr + (kk >> 2) * kChunkBytes + (kk & 3) * 32, 0, 1024);
-              const uint64_t bdesc = make_sdesc(v_addr + kk * 2048, kChunkBytes, 1024);
+              const uint64_t adesc = (static_cast<uint64_t>(desc_hi) << 32) |
+                                     (p_lo + (kk >> 2) * (kChunkBytes >> 4) + (kk & 3) * 2);
+              const uint64_t bdesc = (static_cast<uint64_t>(desc_hi) << 32) | (v_lo + kk * (2048 >> 4)) | lbo_v;
               umma_bf16_ss(tmem_o + h * 2 * kChunk, adesc, bdesc, idesc_pv, (m | kk) != 0);
             }
             umma_commit(&bar->ring_empty[s]);
           }
-          umma_commit(&bar->p_empty[pb]);
+          __syncwarp();
+          if (++s == kStages) { s = 0; ph ^= 1; }
         }
+        if (elect_one()) umma_commit(&bar->p_empty[pb]);
+        __syncwarp();
       }
-      if (u.pv) umma_commit(&bar->o_full);
     }
+    if (u.pv && elect_one()) umma_commit(&bar->o_full);
+    __syncwarp();
   } else if (warp < 8) {
     // ===================== epilogue warps =====================
     const int q = warp & 3, g = warp >> 2;
@@ -309,6 +323,7 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const TcParams p) {
         mbar_arrive(&bar->p_full[b]);
       }
       if (col_is_x) acc_x = fmaf(ksum, fac, acc_x); else acc_y += ksum;
+      if (p.dbg) atomicAdd(&p.dbg[static_cast<int64_t>(blockIdx.x) * p.dbg_stride + n], ksum);
     }
 
     // ---- block sums (only slice 0 owns them)
@@ -318,7 +333,8 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const TcParams p) {
       bar->red[warp][0] = acc_x;
       bar->red[warp][1] = acc_y;
     }
-    nj_smem[g * kTile + row] = rsum;   // norms are dead by now: reuse as the row-sum exchange
+    asm volatile("bar.sync 1, 256;" ::: "memory");   // every epilogue warp is done reading the norms
+    nj_smem[g * kTile + row] = rsum;                  // ... so their buffer can carry the row-sum exchange
     asm volatile("bar.sync 1, 256;" ::: "memory");
     if (threadIdx.x == 0 && u.slice == 0) {
       double sx = 0.0, sy = 0.0;
