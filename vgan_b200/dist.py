@@ -23,6 +23,16 @@ def shard_rows(N: int, rank: int, world: int, tile: int = 128):
     return b, e
 
 
+def combine_shards(sums, dU_colsum, penalty, Nx: int, Ny: int, group=None):
+    """The one exchange of the sharded path: all-reduce [S_xx, S_xy, S_yy | colsum dU] (float64)
+    and finish the loss.  Works on any backend (NCCL on the GPUs, gloo in the CPU tests)."""
+    packed = torch.cat([sums[:3].double(), dU_colsum.double()])
+    dist.all_reduce(packed, group=group)
+    s = packed[:3]
+    loss = (s[0] / (Nx * Nx) - 2.0 * s[1] / (Nx * Ny) + s[2] / (Ny * Ny)).float() + penalty
+    return loss, s, packed[3:]
+
+
 def sharded_masked_step(loss_fn, X, U, rank: int = 0, world: int = 1, group=None, time_k1: bool = True):
     """loss(X, U*X, U) and dL/dU rows of this rank; returns dict(loss, dU, rows, dU_colsum, k1_events).
 
@@ -43,11 +53,8 @@ def sharded_masked_step(loss_fn, X, U, rank: int = 0, world: int = 1, group=None
     dU = out["dY"]
     colsum = dU.sum(0, dtype=torch.float64)
     if world > 1:
-        packed = torch.cat([out["sums"][:3], colsum])
-        dist.all_reduce(packed, group=group)
-        sums, colsum = packed[:3], packed[3:]
         # the penalty (column max over ALL rows of the replicated U) is identical on every rank
-        loss = (sums[0] / (N * N) - 2.0 * sums[1] / (N * N) + sums[2] / (N * N)).float() + out["penalty"][0]
+        loss, _, colsum = combine_shards(out["sums"], colsum, out["penalty"][0], N, N, group)
     else:
         loss = out["loss"][0]
     return dict(loss=loss, dU=dU, rows=(b, e), dU_colsum=colsum.float(), k1_events=ev, sums=out["sums"])
