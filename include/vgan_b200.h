@@ -43,7 +43,8 @@ enum {
   VGAN_B200_PREC_MASK = 1,
   VGAN_B200_CENTER    = 2,      /* subtract the stacked column mean (distance invariant) */
   VGAN_B200_NEED_DX   = 4,      /* also produce dL/dX (VGAN.fit, vgan.py:283)           */
-  VGAN_B200_LADDER    = 8       /* scales are s, s/2, s/4, s/8, s/16: 1 ex2 + 4 squarings */
+  VGAN_B200_LADDER    = 8,      /* scales are s, s/2, s/4, s/8, s/16: 1 ex2 + 4 squarings */
+  VGAN_B200_NO_CLUSTER = 16     /* D > 256: independent slice CTAs (Gram recomputed) instead of the cluster kernel */
 };
 
 /* Layout of the caller-provided workspace (all offsets in bytes from `ws`).

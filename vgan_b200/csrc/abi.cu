@@ -238,7 +238,19 @@ int vgan_b200_mmd2_fwd_bwd(void* ws, int64_t Nx, int64_t Ny, int64_t D, int64_t 
   CUtensorMap map;
   if (int e = make_tmap_bf16_2d(&map, p.zq, static_cast<uint64_t>(L.Nxp + L.Nyp), static_cast<uint64_t>(L.Dp)))
     return e;
-  return launch_tc(p, map, (flags & VGAN_B200_LADDER) ? 1 : 0, st);
+  const int ladder = (flags & VGAN_B200_LADDER) ? 1 : 0;
+  if (p.pv && p.nslices >= 2 && !(flags & VGAN_B200_NO_CLUSTER)) {
+    // D_p > 256: the slice CTAs of a row tile run as one thread-block cluster sharing P over DSMEM;
+    // the S_xx-only units (no gradient GEMM, one slice) stay on the plain kernel.
+    if (int e = launch_tc_cluster(p, map, ladder, st)) return e;
+    if (p.n_xx_units == 0) return VGAN_B200_OK;
+    TcParams q = p;
+    q.gx_begin = q.gx_end = q.gy_begin = q.gy_end = 0;
+    q.pv = 0;
+    q.nslices = 1;
+    return launch_tc(q, map, ladder, st);
+  }
+  return launch_tc(p, map, ladder, st);
 }
 
 int vgan_b200_colmax_penalty(const float* U, int64_t N, int64_t D_u, float weight, void* scratch,

@@ -18,6 +18,7 @@ gradients by ``grad_output``).  There is no CPU implementation here.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Optional
 
 import torch
@@ -102,6 +103,8 @@ def mmd2_eval(X: torch.Tensor, Y: Optional[torch.Tensor], U: Optional[torch.Tens
         flags |= _lib.NEED_DX
     if precision != "fp32" and _is_ladder(mults):
         flags |= _lib.LADDER
+    if os.environ.get("VGAN_B200_NO_CLUSTER"):
+        flags |= _lib.NO_CLUSTER
     ws = _workspace(Nx, Ny, D, D_u, flags, dev)
     st = _stream()
     row_end = max(Nx, Ny) if row_end is None else row_end
