@@ -242,13 +242,27 @@ int vgan_b200_mmd2_fwd_bwd(void* ws, int64_t Nx, int64_t Ny, int64_t D, int64_t 
   if (p.pv && p.nslices >= 2 && !(flags & VGAN_B200_NO_CLUSTER)) {
     // D_p > 256: the slice CTAs of a row tile run as one thread-block cluster sharing P over DSMEM;
     // the S_xx-only units (no gradient GEMM, one slice) stay on the plain kernel.
+    // The S_xx units run concurrently on a side stream: clusters of 4 can only occupy 132 of the
+    // 148 SMs (GPC granularity), and the S_xx work (~1/9 of the total) fills the stranded ones.
+    static cudaStream_t side = nullptr;
+    static cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    if (p.n_xx_units > 0 && !side) {
+      VG_CUDA_CHECK(cudaStreamCreateWithFlags(&side, cudaStreamNonBlocking));
+      VG_CUDA_CHECK(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
+      VG_CUDA_CHECK(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
+    }
+    if (p.n_xx_units > 0) VG_CUDA_CHECK(cudaEventRecord(ev_fork, st));
     if (int e = launch_tc_cluster(p, map, ladder, st)) return e;
     if (p.n_xx_units == 0) return VGAN_B200_OK;
     TcParams q = p;
     q.gx_begin = q.gx_end = q.gy_begin = q.gy_end = 0;
     q.pv = 0;
     q.nslices = 1;
-    return launch_tc(q, map, ladder, st);
+    VG_CUDA_CHECK(cudaStreamWaitEvent(side, ev_fork, 0));
+    if (int e = launch_tc(q, map, ladder, side)) return e;
+    VG_CUDA_CHECK(cudaEventRecord(ev_join, side));
+    VG_CUDA_CHECK(cudaStreamWaitEvent(st, ev_join, 0));
+    return VGAN_B200_OK;
   }
   return launch_tc(p, map, ladder, st);
 }

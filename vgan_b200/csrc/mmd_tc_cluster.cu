@@ -152,15 +152,23 @@ mmd2_tc_cluster_kernel(const __grid_constant__ CUtensorMap zmap, const TcParams 
     const uint32_t ring_lo = (smem_u32(smem + kCSmemRing) & 0x3FFFFu) >> 4;
     const uint32_t p_lo0 = (smem_u32(smem + kCSmemP) & 0x3FFFFu) >> 4;
     uint32_t s = 0, ph = 0, pf_mask = 0;
+    long long t_pf = 0, t_ring = 0, t_se = 0;
+    const long long t_begin = clock64();
     auto gram = [&](int k, int kc0, int kc1) {
       const int b = k & 1;
       const uint32_t d_tmem = tmem + b * kTile;
       for (int kc = kc0; kc < kc1; ++kc) {
         if (kc == 0) {
+          const long long t0 = clock64();
           mbar_wait(&bar->s_empty[b], ((k >> 1) & 1) ^ 1);
+          t_se += clock64() - t0;
           tc_fence_after();
         }
-        mbar_wait(&bar->ring_full[s], ph);
+        {
+          const long long t0 = clock64();
+          mbar_wait(&bar->ring_full[s], ph);
+          t_ring += clock64() - t0;
+        }
         tc_fence_after();
         const uint32_t a_lo = ring_lo + s * (kCStageBytes >> 4);
         const uint32_t b_lo = a_lo + (kChunkBytes >> 4);
@@ -180,14 +188,22 @@ mmd2_tc_cluster_kernel(const __grid_constant__ CUtensorMap zmap, const TcParams 
     };
     auto pv = [&](int t) {
       const int slot = t % kPSlots;
-      mbar_wait(&bar->p_full[slot], (pf_mask >> slot) & 1);
+      {
+        const long long t0 = clock64();
+        mbar_wait(&bar->p_full[slot], (pf_mask >> slot) & 1);
+        t_pf += clock64() - t0;
+      }
       pf_mask ^= 1u << slot;
       tc_fence_after();
       const uint32_t p_lo = p_lo0 + slot * (kCPBytes >> 4);
       for (int h = 0; h < pv_stages; ++h) {
         const int nch = min(2, slice_chunks - 2 * h);
         const uint32_t idesc_pv = make_idesc_bf16(kTile, nch * kChunk, 0, 1);
-        mbar_wait(&bar->ring_full[s], ph);
+        {
+          const long long t0 = clock64();
+          mbar_wait(&bar->ring_full[s], ph);
+          t_ring += clock64() - t0;
+        }
         tc_fence_after();
         const uint32_t v_lo = ring_lo + s * (kCStageBytes >> 4);
         if (elect_one()) {
@@ -217,6 +233,13 @@ mmd2_tc_cluster_kernel(const __grid_constant__ CUtensorMap zmap, const TcParams 
     }
     if (elect_one()) umma_commit(&bar->o_full);
     __syncwarp();
+    if (p.dbg && lane == 0) {
+      float* d = p.dbg + static_cast<int64_t>(blockIdx.x) * p.dbg_stride;
+      d[0] = static_cast<float>(clock64() - t_begin);
+      d[1] = static_cast<float>(t_pf);
+      d[2] = static_cast<float>(t_ring);
+      d[3] = static_cast<float>(t_se);
+    }
   } else if (warp < 8) {
     // ===================== epilogue warps: this CTA's own column tiles =====================
     const int q = warp & 3, g = warp >> 2;
@@ -233,6 +256,7 @@ mmd2_tc_cluster_kernel(const __grid_constant__ CUtensorMap zmap, const TcParams 
     }
     float acc_x = 0.f, acc_y = 0.f, rsum = 0.f;
     uint32_t sf_mask = 0;
+    long long e_sfull = 0, e_comp = 0, e_slot = 0, e_pub = 0;
     for (int k = 0; k < K; ++k) {
       const int t = CS * k + c;
       const bool valid = t < T;
@@ -242,8 +266,10 @@ mmd2_tc_cluster_kernel(const __grid_constant__ CUtensorMap zmap, const TcParams 
       float cf[VGAN_B200_MAX_SCALES];
 #pragma unroll
       for (int m = 0; m < VGAN_B200_MAX_SCALES; ++m) cf[m] = valid ? (col_is_x ? coef_x[m] : coef_y[m]) : 0.f;
+      long long tq = clock64();
       mbar_wait(&bar->nj_full[b], (k >> 1) & 1);
       mbar_wait(&bar->s_full[b], (k >> 1) & 1);
+      e_sfull += clock64() - tq; tq = clock64();
       tc_fence_after();
       const float* njp = nj_smem + b * kTile + g * 64;
       float ksum = 0.f;
@@ -262,10 +288,12 @@ mmd2_tc_cluster_kernel(const __grid_constant__ CUtensorMap zmap, const TcParams 
       if (valid) { if (col_is_x) acc_x += ksum; else acc_y += ksum; }
       // ---- publish the P tile: own slot first, then a bulk copy into the same slot of every peer
       const int slot = t % kPSlots;
+      e_comp += clock64() - tq; tq = clock64();
       if (t >= kPSlots) {
         mbar_wait(&bar->slot_free[slot], (sf_mask >> slot) & 1);   // every CTA finished PV(t - kPSlots)
         sf_mask ^= 1u << slot;
       }
+      e_slot += clock64() - tq; tq = clock64();
       uint8_t* p_slot = smem + kCSmemP + slot * kCPBytes;
       uint8_t* p_row = p_slot + g * kChunkBytes + row * 128;
 #pragma unroll
@@ -283,6 +311,14 @@ mmd2_tc_cluster_kernel(const __grid_constant__ CUtensorMap zmap, const TcParams 
           bulk_copy_to_peer(mapa_u32(src, d), src, kCPBytes, rbar);
         }
       }
+      e_pub += clock64() - tq;
+    }
+    if (p.dbg && threadIdx.x == 0) {
+      float* d = p.dbg + static_cast<int64_t>(blockIdx.x) * p.dbg_stride;
+      d[4] = static_cast<float>(e_sfull);
+      d[5] = static_cast<float>(e_comp);
+      d[6] = static_cast<float>(e_slot);
+      d[7] = static_cast<float>(e_pub);
     }
     // ---- partial sums of this CTA's tiles
     acc_x = warp_sum(acc_x);
