@@ -126,6 +126,9 @@ int vgan_b200_mmd2_matrix(const float* Z, int64_t n, int64_t D, const float* inv
  * (work unit, column tile) to buf[unit * stride + tile] (device floats).  NULL switches it off. */
 int vgan_b200_debug_tile_sums(float* buf, int stride);
 
+/* Debug aid: SM cycles for iters x 4 tcgen05.mma (M=128, N=n, K=16) on resident operands. */
+int vgan_b200_umma_rate_probe(int n, int iters, int b_mn, long long* cycles_out, void* stream);
+
 int vgan_b200_umma_probe(const void* A, const void* B, float* S_out, float* O_out, void* stream);
 
 #ifdef __cplusplus

@@ -1,0 +1,58 @@
+"""Config 2/3/5 sweep on one B200: fused fwd+bwd evaluations/s of vgan_b200 (bf16 and fp32 paths)
+next to torch-eager running the reference formula on the same GPU (where its [5,2N,2N] tensor
+fits).  Prints one JSON line per (N, D)."""
+import json, os, sys, time
+import torch
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from vgan_b200 import MMDLossConstrained, RBF
+from oracle import torch_eager
+
+def timeit(fn, reps):
+    for _ in range(2): fn()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(reps): fn()
+    b.record(); torch.cuda.synchronize()
+    return a.elapsed_time(b) / reps
+
+def main():
+    shapes = [(4096, 784), (4096, 49), (16384, 32), (16384, 128), (16384, 512), (4096, 16), (4096, 64), (4096, 256),
+              (4096, 1024), (4096, 4096), (16384, 1024), (65536, 64), (65536, 256), (65536, 1024), (131072, 128)]
+    for N, D in shapes:
+        g = torch.Generator(device="cuda").manual_seed(0)
+        X = torch.randn(N, D, device="cuda", generator=g)
+        p = torch.softmax(torch.randn(N, D, device="cuda", generator=g), 1)
+        U0 = torch.where(p < 1.0 / D, p, torch.ones_like(p))
+        row = {"N": N, "D": D}
+        for prec in ("bf16", "fp32"):
+            if prec == "fp32" and N * N * D > 16384 * 16384 * 512: continue
+            loss_fn = MMDLossConstrained(10.0, kernel=RBF(), precision=prec)
+            U = U0.clone().requires_grad_()
+            def step():
+                U.grad = None
+                loss_fn.forward_masked(X, U).backward()
+            reps = 20 if N * N * D < 1e12 else 5
+            ms = timeit(step, reps)
+            row[f"{prec}_ms"] = round(ms, 4)
+            row[f"{prec}_evals_per_s"] = round(1e3 / ms, 2)
+            if prec == "bf16":
+                row["bf16_tflops_alg"] = round(8.0 * N * N * D / (ms * 1e-3) / 1e12, 1)
+        if 5 * (2 * N) ** 2 * 4 * 4 < 150e9:      # [5,2N,2N] fp32 + autograd copies must fit
+            try:
+                ref = torch_eager.MMDLossConstrained(10.0)
+                U = U0.clone().requires_grad_()
+                def rstep():
+                    U.grad = None
+                    ref(X, U * X, U).backward()
+                ms = timeit(rstep, 3)
+                row["torch_eager_ms"] = round(ms, 3)
+                row["speedup_vs_torch_eager_bf16"] = round(ms / row["bf16_ms"], 1)
+                del ref
+            except torch.OutOfMemoryError:
+                row["torch_eager_ms"] = "oom"
+            torch.cuda.empty_cache()
+        print(json.dumps(row), flush=True)
+
+if __name__ == "__main__":
+    main()

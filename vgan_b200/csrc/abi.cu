@@ -78,6 +78,7 @@ int run_penalty(const float*, int64_t, int64_t, float, unsigned long long*, floa
 int run_finalize(const double*, int64_t, int64_t, const float*, float*, cudaStream_t);
 int launch_matrix(const float*, int64_t, int64_t, const float*, int, float, float*, cudaStream_t);
 struct SimtParams;
+int launch_rate_probe(int n, int iters, int b_mn, long long* out, cudaStream_t st);
 int launch_simt_from_abi(const vgan_b200_layout_t& L, void* ws, int64_t row_begin, int64_t row_end, int xx_part,
                          int xx_nparts, const float* inv_scales, int n_scales, int flags, double* sums,
                          float* dY, const float* dY_mul, float* dX, cudaStream_t st);
@@ -239,6 +240,8 @@ int vgan_b200_mmd2_fwd_bwd(void* ws, int64_t Nx, int64_t Ny, int64_t D, int64_t 
   if (int e = make_tmap_bf16_2d(&map, p.zq, static_cast<uint64_t>(L.Nxp + L.Nyp), static_cast<uint64_t>(L.Dp)))
     return e;
   const int ladder = (flags & VGAN_B200_LADDER) ? 1 : 0;
+  p.cs = p.nslices < 4 ? p.nslices : 4;
+  p.ngroups = (p.nslices + p.cs - 1) / p.cs;
   if (p.pv && p.nslices >= 2 && !(flags & VGAN_B200_NO_CLUSTER)) {
     // D_p > 256: the slice CTAs of a row tile run as one thread-block cluster sharing P over DSMEM;
     // the S_xx-only units (no gradient GEMM, one slice) stay on the plain kernel.
@@ -302,6 +305,11 @@ int vgan_b200_debug_tile_sums(float* buf, int stride) {
   g_dbg = buf;
   g_dbg_stride = stride;
   return VGAN_B200_OK;
+}
+
+int vgan_b200_umma_rate_probe(int n, int iters, int b_mn, long long* cycles_out, void* stream) {
+  if (int e = check_device()) return e;
+  return launch_rate_probe(n, iters, b_mn, cycles_out, static_cast<cudaStream_t>(stream));
 }
 
 int vgan_b200_umma_probe(const void* A, const void* B, float* S_out, float* O_out, void* stream) {

@@ -29,6 +29,7 @@ struct TcParams {
   int tiles_x, tiles_y;       // 128-row tiles in the X / Y regions of the stacked operand
   int kchunks;                // Dp / 64
   int nslices, slice_chunks;  // output feature slices per row tile, chunks per (full) slice
+  int cs, ngroups;            // cluster kernel: CTAs per cluster, slice groups (clusters) per row tile
   int gx_begin, gx_end;       // X row tiles that need a gradient (NEED_DX), else empty
   int gy_begin, gy_end;       // Y row tiles of this shard
   int xx_part, xx_nparts;     // S_xx-only units: X tiles t with t % nparts == part

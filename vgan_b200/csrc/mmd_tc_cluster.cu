@@ -55,17 +55,19 @@ mmd2_tc_cluster_kernel(const __grid_constant__ CUtensorMap zmap, const TcParams 
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int CS = p.nslices;                            // cluster size = number of feature slices
-  const int c = static_cast<int>(cluster_ctarank());   // this CTA's slice
+  const int CS = p.cs;                                 // cluster size (<= 4 feature slices per cluster)
+  const int c = static_cast<int>(cluster_ctarank());
+  const int grp = (blockIdx.x / CS) % p.ngroups;       // D_p > 1024: several clusters per row tile
+  const int slice = grp * CS + c;                      // this CTA's feature slice (may be past the end)
   // ---- unit decode: one cluster per gradient row tile
   const int ngx = p.gx_end - p.gx_begin;
-  const int unit = blockIdx.x / CS;
+  const int unit = blockIdx.x / (CS * p.ngroups);
   const int row_is_x = unit < ngx;
   const int ti = row_is_x ? p.gx_begin + unit : p.tiles_x + p.gy_begin + (unit - ngx);
   const int T = p.tiles_x + p.tiles_y;                 // column tiles
   const int K = (T + CS - 1) / CS;                     // Gram tiles per CTA (the tail is padded)
   const int TT = K * CS;                               // padded tile count; tiles >= T carry P = 0
-  const int slice_chunks = min(p.slice_chunks, p.kchunks - c * p.slice_chunks);
+  const int slice_chunks = max(0, min(p.slice_chunks, p.kchunks - slice * p.slice_chunks));
   const int pv_stages = (slice_chunks + 1) >> 1;
 
   if (threadIdx.x == 0) {
@@ -120,7 +122,7 @@ mmd2_tc_cluster_kernel(const __grid_constant__ CUtensorMap zmap, const TcParams 
           mbar_arrive_expect_tx(&bar->ring_full[s], nch * kChunkBytes);
           for (int cc = 0; cc < nch; ++cc)
             tma_load_2d(dst + cc * kChunkBytes, &zmap, &bar->ring_full[s],
-                        (c * p.slice_chunks + 2 * h + cc) * kChunk, jt * kTile);
+                        (slice * p.slice_chunks + 2 * h + cc) * kChunk, jt * kTile);
           if (++s == kCStages) { s = 0; ph ^= 1; }
         }
       };
@@ -326,7 +328,7 @@ mmd2_tc_cluster_kernel(const __grid_constant__ CUtensorMap zmap, const TcParams 
     if (lane == 0) { bar->red[warp][0] = acc_x; bar->red[warp][1] = acc_y; }
     asm volatile("bar.sync 1, 256;" ::: "memory");   // all epilogue warps are done with the norms
     nj_smem[g * kTile + row] = rsum;
-    if (threadIdx.x == 0) {
+    if (threadIdx.x == 0 && grp == 0) {
       double sx = 0.0, sy = 0.0;
       for (int wv = 0; wv < 8; ++wv) { sx += bar->red[wv][0]; sy += bar->red[wv][1]; }
       if (row_is_x) {
@@ -357,7 +359,7 @@ mmd2_tc_cluster_kernel(const __grid_constant__ CUtensorMap zmap, const TcParams 
     float rtot = 0.f;
     for (int d = 0; d < CS; ++d) rtot += rsx[d * kTile + row];
     tc_fence_after();
-    write_grad_rows(p, tmem_o, static_cast<uint32_t>(q * 32) << 16, g, row, ti, row_is_x, c, slice_chunks, rtot);
+    write_grad_rows(p, tmem_o, static_cast<uint32_t>(q * 32) << 16, g, row, ti, row_is_x, slice, slice_chunks, rtot);
   }
   tc_fence_before();
   __syncthreads();
@@ -370,13 +372,13 @@ int launch_tc_cluster(const TcParams& p, const CUtensorMap& map, int ladder, cud
   auto kern = ladder ? mmd2_tc_cluster_kernel<true> : mmd2_tc_cluster_kernel<false>;
   VG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kCSmemTotal));
   cudaLaunchConfig_t cfg{};
-  cfg.gridDim = dim3(static_cast<unsigned>(ngrad * p.nslices));
+  cfg.gridDim = dim3(static_cast<unsigned>(ngrad * p.cs * p.ngroups));
   cfg.blockDim = dim3(kCThreads);
   cfg.dynamicSmemBytes = kCSmemTotal;
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = static_cast<unsigned>(p.nslices);
+  attr[0].val.clusterDim.x = static_cast<unsigned>(p.cs);
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;

@@ -109,3 +109,55 @@ int launch_probe(const CUtensorMap& mapA, const CUtensorMap& mapB, float* S_out,
 }
 
 }  // namespace vg
+
+// ------------------------------------------------------------------ MMA issue-rate probe
+// Issues `iters` x 4 tcgen05.mma (M=128, N=n, K=16) on resident shared-memory operands (no TMA
+// traffic) and returns the elapsed SM cycles: the achievable tensor rate for SS operands.
+namespace vg {
+__global__ void __launch_bounds__(128, 1) umma_rate_kernel(int n, int iters, int b_mn, long long* out) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  __shared__ uint64_t bar;
+  __shared__ uint32_t tmem_slot;
+  const int warp = threadIdx.x >> 5;
+  for (int i = threadIdx.x; i < 6 * kChunkBytes / 4; i += 128) reinterpret_cast<uint32_t*>(smem)[i] = 0x3c003c00u;
+  if (threadIdx.x == 0) { mbar_init(&bar, 1); fence_barrier_init(); }
+  if (warp == 0) { tmem_alloc(&tmem_slot, 512); tmem_relinquish(); }
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = tmem_slot;
+  if (warp == 0) {
+    const uint32_t idesc = make_idesc_bf16(128, n, 0, b_mn);
+    const uint32_t a0 = smem_u32(smem), b0 = smem_u32(smem) + 2 * kChunkBytes;
+    const long long t0 = clock64();
+    for (int it = 0; it < iters; ++it) {
+      if (elect_one()) {
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) {
+          const uint64_t ad = make_sdesc(a0 + (it & 1) * kChunkBytes + kk * 32, 0, 1024);
+          const uint64_t bd = b_mn ? make_sdesc(b0 + kk * 2048, kChunkBytes, 1024)
+                                   : make_sdesc(b0 + kk * 32, 0, 1024);
+          umma_bf16_ss(tmem + (it & 1) * 256, ad, bd, idesc, 1);
+        }
+      }
+      __syncwarp();
+    }
+    if (elect_one()) umma_commit(&bar);
+    __syncwarp();
+    mbar_wait(&bar, 0);
+    if (threadIdx.x == 0) out[0] = clock64() - t0;
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem, 512);
+}
+
+int launch_rate_probe(int n, int iters, int b_mn, long long* out, cudaStream_t st) {
+  const int bytes = 6 * kChunkBytes;
+  VG_CUDA_CHECK(cudaFuncSetAttribute(umma_rate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+  umma_rate_kernel<<<1, 128, bytes, st>>>(n, iters, b_mn, out);
+  VG_CUDA_CHECK(cudaGetLastError());
+  return VGAN_B200_OK;
+}
+}  // namespace vg
