@@ -126,6 +126,11 @@ int vgan_b200_mmd2_matrix(const float* Z, int64_t n, int64_t D, const float* inv
  * (work unit, column tile) to buf[unit * stride + tile] (device floats).  NULL switches it off. */
 int vgan_b200_debug_tile_sums(float* buf, int stride);
 
+/* Debug aid: cta_group::2 Gram + gradient tile on one CTA pair. A0,A1,B bf16 [128,128], V bf16 [128,256];
+ * S_out float [2,128,128] = A_h B^T;  O_out float [2,128,256] = bf16(S_h) V. */
+int vgan_b200_pair_probe(const void* A0, const void* A1, const void* B, const void* V, float* S_out, float* O_out,
+                         void* stream);
+
 /* Debug aid: SM cycles for iters x 4 tcgen05.mma (M=128, N=n, K=16) on resident operands. */
 int vgan_b200_umma_rate_probe(int n, int iters, int b_mn, long long* cycles_out, void* stream);
 

@@ -21,7 +21,7 @@ EXPORTS = [
     "vgan_b200_abi_version", "vgan_b200_last_error", "vgan_b200_workspace_layout",
     "vgan_b200_prologue", "vgan_b200_scales", "vgan_b200_mmd2_fwd_bwd",
     "vgan_b200_colmax_penalty", "vgan_b200_finalize_loss", "vgan_b200_mmd2_matrix",
-    "vgan_b200_umma_probe", "vgan_b200_debug_tile_sums", "vgan_b200_umma_rate_probe",
+    "vgan_b200_umma_probe", "vgan_b200_debug_tile_sums", "vgan_b200_umma_rate_probe", "vgan_b200_pair_probe",
 ]
 
 
@@ -72,6 +72,7 @@ def lib() -> C.CDLL:
             L.vgan_b200_umma_probe.argtypes = [p, p, p, p, p]
             L.vgan_b200_debug_tile_sums.argtypes = [p, i]
             L.vgan_b200_umma_rate_probe.argtypes = [i, i, i, p, p]
+            L.vgan_b200_pair_probe.argtypes = [p, p, p, p, p, p, p]
             for name in EXPORTS:
                 if name not in ("vgan_b200_last_error",):
                     getattr(L, name).restype = i

@@ -49,7 +49,7 @@ static EncodeTiledFn get_encode() {
 }
 
 // bf16 [rows, cols] row-major, box = 64 columns x 128 rows, 128-byte swizzle
-int make_tmap_bf16_2d(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols) {
+int make_tmap_bf16_2d(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint32_t box_rows) {
   EncodeTiledFn enc = get_encode();
   if (!enc) {
     set_error("cuTensorMapEncodeTiled not available from the driver");
@@ -57,7 +57,7 @@ int make_tmap_bf16_2d(CUtensorMap* map, const void* base, uint64_t rows, uint64_
   }
   cuuint64_t dims[2] = {cols, rows};
   cuuint64_t strides[1] = {cols * 2};
-  cuuint32_t box[2] = {static_cast<cuuint32_t>(kChunk), static_cast<cuuint32_t>(kTile)};
+  cuuint32_t box[2] = {static_cast<cuuint32_t>(kChunk), static_cast<cuuint32_t>(box_rows)};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box,
                    estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
@@ -79,6 +79,8 @@ int run_finalize(const double*, int64_t, int64_t, const float*, float*, cudaStre
 int launch_matrix(const float*, int64_t, int64_t, const float*, int, float, float*, cudaStream_t);
 struct SimtParams;
 int launch_rate_probe(int n, int iters, int b_mn, long long* out, cudaStream_t st);
+int launch_pair_probe(const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, float*, float*,
+                      cudaStream_t);
 int launch_simt_from_abi(const vgan_b200_layout_t& L, void* ws, int64_t row_begin, int64_t row_end, int xx_part,
                          int xx_nparts, const float* inv_scales, int n_scales, int flags, double* sums,
                          float* dY, const float* dY_mul, float* dX, cudaStream_t st);
@@ -305,6 +307,17 @@ int vgan_b200_debug_tile_sums(float* buf, int stride) {
   g_dbg = buf;
   g_dbg_stride = stride;
   return VGAN_B200_OK;
+}
+
+int vgan_b200_pair_probe(const void* A0, const void* A1, const void* B, const void* V, float* S_out, float* O_out,
+                         void* stream) {
+  if (int e = check_device()) return e;
+  CUtensorMap a0, a1, bh, v;
+  if (int e = make_tmap_bf16_2d(&a0, A0, 128, 128)) return e;
+  if (int e = make_tmap_bf16_2d(&a1, A1, 128, 128)) return e;
+  if (int e = make_tmap_bf16_2d(&bh, B, 128, 128, 64)) return e;
+  if (int e = make_tmap_bf16_2d(&v, V, 128, 256)) return e;
+  return launch_pair_probe(a0, a1, bh, v, S_out, O_out, static_cast<cudaStream_t>(stream));
 }
 
 int vgan_b200_umma_rate_probe(int n, int iters, int b_mn, long long* cycles_out, void* stream) {
