@@ -44,6 +44,7 @@ enum {
   VGAN_B200_CENTER    = 2,      /* subtract the stacked column mean (distance invariant) */
   VGAN_B200_NEED_DX   = 4,      /* also produce dL/dX (VGAN.fit, vgan.py:283)           */
   VGAN_B200_LADDER    = 8,      /* scales are s, s/2, s/4, s/8, s/16: 1 ex2 + 4 squarings */
+  VGAN_B200_NO_PAIR   = 32,     /* D > 256: 1-CTA cluster kernel instead of the cta_group::2 pair kernel */
   VGAN_B200_NO_CLUSTER = 16     /* D > 256: independent slice CTAs (Gram recomputed) instead of the cluster kernel */
 };
 

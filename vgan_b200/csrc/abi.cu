@@ -257,7 +257,17 @@ int vgan_b200_mmd2_fwd_bwd(void* ws, int64_t Nx, int64_t Ny, int64_t D, int64_t 
       VG_CUDA_CHECK(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
     }
     if (p.n_xx_units > 0) VG_CUDA_CHECK(cudaEventRecord(ev_fork, st));
-    if (int e = launch_tc_cluster(p, map, ladder, st)) return e;
+    // full 128/256-wide slices: CTA pairs (cta_group::2) halve the shared-memory operand traffic
+    const bool pair_ok = (p.kchunks % 4 == 0 || p.kchunks % 4 == 2) && !(flags & VGAN_B200_NO_PAIR);
+    if (pair_ok) {
+      CUtensorMap map64;
+      if (int e = make_tmap_bf16_2d(&map64, p.zq, static_cast<uint64_t>(L.Nxp + L.Nyp),
+                                    static_cast<uint64_t>(L.Dp), 64))
+        return e;
+      if (int e = launch_tc_pair(p, map, map64, ladder, st)) return e;
+    } else {
+      if (int e = launch_tc_cluster(p, map, ladder, st)) return e;
+    }
     if (p.n_xx_units == 0) return VGAN_B200_OK;
     TcParams q = p;
     q.gx_begin = q.gx_end = q.gy_begin = q.gy_end = 0;

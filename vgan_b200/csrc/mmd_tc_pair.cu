@@ -1,0 +1,410 @@
+// K1, CTA-pair variant (cta_group::2) of the cluster kernel, for D_p = 2 or 4 chunks per slice.
+// Cluster = 2 row tiles x CS feature slices.  CTAs 2c (leader) and 2c+1 form the tcgen05 pair of
+// slice c; they own DIFFERENT row tiles (I0, I1) and share every B operand:
+//   Gram  M=256 = [Z_I0 ; Z_I1] chunks (each CTA loads its own 16 KiB), B = Z_J chunk, each CTA
+//         loads only HALF of its 128 rows (8 KiB)   -> 6 KiB instead of 8 KiB smem read per MMA
+//   PV    M=256 = [P(I0,t) ; P(I1,t)], B = Z_Jt[:, slice c], each CTA holds half of the features
+//         (N = 256 per MMA)                            -> 8 KiB instead of 16 KiB per 256 features
+// Shared-memory traffic is what bounds the 1-CTA cluster kernel (mmd_tc_cluster.cu: an N=128 SS MMA
+// needs the full 128 B/clk of shared-memory bandwidth by itself); pairing cuts it by ~1/3.
+// P tiles are exchanged among the CTAs of the SAME row tile exactly as in mmd_tc_cluster.cu.
+// Only the leader issues MMAs; extra signalling: the peer's epilogue arrives on the leader's
+// s_empty, the peer's (otherwise idle) MMA warp forwards its p_full to the leader (p_pair),
+// and every tcgen05.commit is multicast to both CTAs of the pair.
+#include "common.cuh"
+#include "ptx.cuh"
+#include "tc_epi.cuh"
+
+namespace vg {
+
+constexpr int kQStages = 4;                       // 4 x 32 KiB operand ring
+constexpr int kQStageBytes = 2 * kChunkBytes;
+constexpr int kQSlots = 3;                        // 3 x 32 KiB P tiles
+constexpr int kQPBytes = 2 * kChunkBytes;
+constexpr int kQLag = 1;                           // PV(t) is issued kQLag periods after tile t's turn
+constexpr int kQThreads = 384;
+
+struct __align__(8) PairBarriers {
+  uint64_t ring_full[kQStages], ring_empty[kQStages];
+  uint64_t s_full[2], s_empty[2];
+  uint64_t nj_full[2];
+  uint64_t p_full[kQSlots], slot_free[kQSlots], p_pair[kQSlots];
+  uint64_t o_full;
+  uint32_t tmem_base;
+  float red[8][4];
+};
+
+constexpr int kQSmemRing = 0;
+constexpr int kQSmemP = kQSmemRing + kQStages * kQStageBytes;
+constexpr int kQSmemNj = kQSmemP + kQSlots * kQPBytes;
+constexpr int kQSmemBar = kQSmemNj + 2 * kTile * 4;
+constexpr int kQSmemTotal = kQSmemBar + static_cast<int>(sizeof(PairBarriers));
+static_assert(kQSmemTotal <= 232448, "shared memory budget");
+
+template <bool LADDER>
+__global__ void __launch_bounds__(kQThreads, 1)
+mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__ CUtensorMap zmap64,
+                    const TcParams p) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  if ((smem_u32(smem) & 1023u) != 0) __trap();
+  PairBarriers* bar = reinterpret_cast<PairBarriers*>(smem + kQSmemBar);
+  float* nj_smem = reinterpret_cast<float*>(smem + kQSmemNj);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int CS = p.cs;                                 // feature slices per cluster; cluster size = 2 CS
+  const int rank = static_cast<int>(cluster_ctarank());
+  const int c = rank >> 1;                             // pair index = slice within the group
+  const int hh = rank & 1;                             // 0: leader (row tile I0), 1: peer (row tile I1)
+  const int csz = 2 * CS;
+  const int grp = (blockIdx.x / csz) % p.ngroups;
+  const int slice = grp * CS + c;
+  // ---- unit decode: one cluster per PAIR of gradient row tiles
+  const int ngx = p.gx_end - p.gx_begin;
+  const int ngrad = ngx + (p.gy_end - p.gy_begin);
+  int unit = 2 * static_cast<int>(blockIdx.x / (csz * p.ngroups)) + hh;
+  const bool dup = unit >= ngrad;                      // odd tile count: the peer repeats I0, output dropped
+  if (dup) unit = ngrad - 1;
+  const int row_is_x = unit < ngx;
+  const int ti = row_is_x ? p.gx_begin + unit : p.tiles_x + p.gy_begin + (unit - ngx);
+  const uint16_t pair_mask = static_cast<uint16_t>(3u << (2 * c));
+  const int T = p.tiles_x + p.tiles_y;                 // column tiles
+  const int K = (T + CS - 1) / CS;                     // Gram tiles per CTA (the tail is padded)
+  const int TT = K * CS;                               // padded tile count; tiles >= T carry P = 0
+  const int slice_chunks = max(0, min(p.slice_chunks, p.kchunks - slice * p.slice_chunks));
+  const int pv_stages = slice_chunks > 0 ? 1 : 0;     // one stage per tile: this CTA's half of the slice
+  const int my_chunks = slice_chunks >> 1;             // 64-feature chunks of the slice held by this CTA
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kQStages; ++s) {
+      mbar_init(&bar->ring_full[s], 1);
+      mbar_init(&bar->ring_empty[s], 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&bar->s_full[b], 1);
+      mbar_init(&bar->s_empty[b], hh == 0 ? 512 : 256);   // leader: both epilogues
+      mbar_init(&bar->nj_full[b], 1);
+    }
+    for (int s = 0; s < kQSlots; ++s) {
+      mbar_init(&bar->p_full[s], 1);
+      mbar_init(&bar->slot_free[s], CS);
+      mbar_init(&bar->p_pair[s], 1);
+    }
+    mbar_init(&bar->o_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 11) {
+    tmem_alloc_2cta(&bar->tmem_base, 512);
+    tmem_relinquish_2cta();
+  }
+  if (warp == 8 && lane == 0) tma_prefetch_desc(&zmap);
+  tc_fence_before();
+  cluster_sync_all();          // peers' barriers are initialised before any remote arrive / copy
+  tc_fence_after();
+  const uint32_t tmem = bar->tmem_base;
+  const uint32_t tmem_o = tmem + 256;
+
+  if (warp == 8) {
+    // ===================== TMA producer (mirrors the MMA stream order exactly) =====================
+    if (lane == 0) {
+      uint32_t s = 0, ph = 0;
+      auto gram_stages = [&](int k, int kc0, int kc1) {
+        const int jt = min(CS * k + c, T - 1);
+        for (int kc = kc0; kc < kc1; ++kc) {
+          mbar_wait(&bar->ring_empty[s], ph ^ 1);
+          uint8_t* dst = smem + kQSmemRing + s * kQStageBytes;
+          if (hh == 0) mbar_arrive_expect_tx(&bar->ring_full[s], 2 * (kChunkBytes + kChunkBytes / 2));
+          tma_load_2d_2cta(dst, &zmap, &bar->ring_full[s], kc * kChunk, ti * kTile);
+          tma_load_2d_2cta(dst + kChunkBytes, &zmap64, &bar->ring_full[s], kc * kChunk, jt * kTile + 64 * hh);
+          if (++s == kQStages) { s = 0; ph ^= 1; }
+        }
+      };
+      auto pv_stages_load = [&](int t) {
+        const int jt = min(t, T - 1);
+        for (int h = 0; h < pv_stages; ++h) {
+          mbar_wait(&bar->ring_empty[s], ph ^ 1);
+          uint8_t* dst = smem + kQSmemRing + s * kQStageBytes;
+          if (hh == 0) mbar_arrive_expect_tx(&bar->ring_full[s], slice_chunks * kChunkBytes);
+          for (int cc = 0; cc < my_chunks; ++cc)
+            tma_load_2d_2cta(dst + cc * kChunkBytes, &zmap, &bar->ring_full[s],
+                             (slice * p.slice_chunks + hh * my_chunks + cc) * kChunk, jt * kTile);
+          if (++s == kQStages) { s = 0; ph ^= 1; }
+        }
+      };
+      gram_stages(0, 0, p.kchunks);
+      for (int m = 0; m < TT + kQLag; ++m) {
+        const int kn = 1 + m / CS, q = m % CS;
+        if (kn < K) gram_stages(kn, (q * p.kchunks) / CS, ((q + 1) * p.kchunks) / CS);
+        const int tc = m - kQLag;
+        if (tc >= 0 && tc < TT) pv_stages_load(tc);
+      }
+    }
+  } else if (warp == 10) {
+    // ===================== bulk-copy producer: scaled column norms of this CTA's tiles ============
+    if (lane == 0) {
+      for (int k = 0; k < K; ++k) {
+        const int jt = min(CS * k + c, T - 1);
+        const int b = k & 1;
+        mbar_wait(&bar->s_empty[b], ((k >> 1) & 1) ^ 1);
+        mbar_arrive_expect_tx(&bar->nj_full[b], kTile * 4);
+        bulk_load_1d(nj_smem + b * kTile, p.nrms + static_cast<int64_t>(jt) * kTile, kTile * 4,
+                     &bar->nj_full[b]);
+      }
+    }
+  } else if (warp == 9 && hh == 1) {
+    // ===================== peer CTA: forward "my P tile t is in place" to the leader's MMA warp =========
+    uint32_t pf_mask = 0;
+    const uint32_t pp0 = mapa_u32(smem_u32(&bar->p_pair[0]), static_cast<uint32_t>(rank - 1));
+    for (int t = 0; t < TT; ++t) {
+      const int slot = t % kQSlots;
+      mbar_wait(&bar->p_full[slot], (pf_mask >> slot) & 1);
+      pf_mask ^= 1u << slot;
+      if (lane == 0) mbar_remote_arrive(pp0 + slot * 8);
+      __syncwarp();
+    }
+  } else if (warp == 9) {
+    // ===================== leader CTA: MMA issuer for the pair (warp-uniform; one lane issues) ==========
+    constexpr uint32_t idesc_gram = make_idesc_bf16(2 * kTile, kTile, 0, 0);
+    constexpr uint32_t desc_hi = (1024u >> 4) | (1u << 14) | (2u << 29);
+    constexpr uint32_t lbo_v = (static_cast<uint32_t>(kChunkBytes) >> 4) << 16;
+    const uint32_t idesc_pv = make_idesc_bf16(2 * kTile, slice_chunks * kChunk, 0, 1);
+    const uint32_t ring_lo = (smem_u32(smem + kQSmemRing) & 0x3FFFFu) >> 4;
+    const uint32_t p_lo0 = (smem_u32(smem + kQSmemP) & 0x3FFFFu) >> 4;
+    uint32_t s = 0, ph = 0, pf_mask = 0;
+    long long t_pf = 0, t_ring = 0, t_se = 0;
+    const long long t_begin = clock64();
+    auto gram = [&](int k, int kc0, int kc1) {
+      const int b = k & 1;
+      const uint32_t d_tmem = tmem + b * kTile;
+      for (int kc = kc0; kc < kc1; ++kc) {
+        if (kc == 0) {
+          const long long t0 = clock64();
+          mbar_wait(&bar->s_empty[b], ((k >> 1) & 1) ^ 1);     // both CTAs' epilogues released S[b]
+          t_se += clock64() - t0;
+          tc_fence_after();
+        }
+        {
+          const long long t0 = clock64();
+          mbar_wait(&bar->ring_full[s], ph);
+          t_ring += clock64() - t0;
+        }
+        tc_fence_after();
+        const uint32_t a_lo = ring_lo + s * (kQStageBytes >> 4);
+        const uint32_t b_lo = a_lo + (kChunkBytes >> 4);
+        if (elect_one()) {
+#pragma unroll
+          for (int kk = 0; kk < kChunk / 16; ++kk) {
+            const uint64_t adesc = (static_cast<uint64_t>(desc_hi) << 32) | (a_lo + kk * 2);
+            const uint64_t bdesc = (static_cast<uint64_t>(desc_hi) << 32) | (b_lo + kk * 2);
+            umma_bf16_ss_2cta(d_tmem, adesc, bdesc, idesc_gram, (kc | kk) != 0);
+          }
+          umma_commit_2cta_mc(&bar->ring_empty[s], pair_mask);
+          if (kc == p.kchunks - 1) umma_commit_2cta_mc(&bar->s_full[b], pair_mask);
+        }
+        __syncwarp();
+        if (++s == kQStages) { s = 0; ph ^= 1; }
+      }
+    };
+    auto pv = [&](int t) {
+      const int slot = t % kQSlots;
+      {
+        const long long t0 = clock64();
+        mbar_wait(&bar->p_full[slot], (pf_mask >> slot) & 1);   // my P(I0, t)
+        mbar_wait(&bar->p_pair[slot], (pf_mask >> slot) & 1);   // the peer's P(I1, t)
+        t_pf += clock64() - t0;
+      }
+      pf_mask ^= 1u << slot;
+      tc_fence_after();
+      const uint32_t p_lo = p_lo0 + slot * (kQPBytes >> 4);
+      if (pv_stages) {
+        {
+          const long long t0 = clock64();
+          mbar_wait(&bar->ring_full[s], ph);
+          t_ring += clock64() - t0;
+        }
+        tc_fence_after();
+        const uint32_t v_lo = ring_lo + s * (kQStageBytes >> 4);
+        if (elect_one()) {
+#pragma unroll
+          for (int kk = 0; kk < kTile / 16; ++kk) {
+            const uint64_t adesc = (static_cast<uint64_t>(desc_hi) << 32) |
+                                   (p_lo + (kk >> 2) * (kChunkBytes >> 4) + (kk & 3) * 2);
+            const uint64_t bdesc = (static_cast<uint64_t>(desc_hi) << 32) | (v_lo + kk * (2048 >> 4)) | lbo_v;
+            umma_bf16_ss_2cta(tmem_o, adesc, bdesc, idesc_pv, (t | kk) != 0);
+          }
+          umma_commit_2cta_mc(&bar->ring_empty[s], pair_mask);
+        }
+        __syncwarp();
+        if (++s == kQStages) { s = 0; ph ^= 1; }
+      }
+      // both CTAs of the pair are done with slot: tell the two writers (rows I0 and I1) of tile t + kQSlots
+      if (t + kQSlots < TT && elect_one())
+        umma_commit_2cta_mc(&bar->slot_free[slot], static_cast<uint16_t>(3u << (2 * ((t + kQSlots) % CS))));
+      __syncwarp();
+    };
+    gram(0, 0, p.kchunks);
+    for (int m = 0; m < TT + kQLag; ++m) {
+      const int kn = 1 + m / CS, q = m % CS;
+      if (kn < K) gram(kn, (q * p.kchunks) / CS, ((q + 1) * p.kchunks) / CS);
+      const int tc = m - kQLag;
+      if (tc >= 0 && tc < TT) pv(tc);
+    }
+    if (elect_one()) umma_commit_2cta_mc(&bar->o_full, pair_mask);
+    __syncwarp();
+    if (p.dbg && lane == 0) {
+      float* d = p.dbg + static_cast<int64_t>(blockIdx.x) * p.dbg_stride;
+      d[0] = static_cast<float>(clock64() - t_begin);
+      d[1] = static_cast<float>(t_pf);
+      d[2] = static_cast<float>(t_ring);
+      d[3] = static_cast<float>(t_se);
+    }
+  } else if (warp < 8) {
+    // ===================== epilogue warps: this CTA's own column tiles =====================
+    const int q = warp & 3, g = warp >> 2;
+    const int row = q * 32 + lane;
+    const uint32_t lane_addr = static_cast<uint32_t>(q * 32) << 16;
+    const float m2c0 = p.par[1];
+    const float ni = p.nrms[static_cast<int64_t>(ti) * kTile + row];
+    float coef_x[VGAN_B200_MAX_SCALES], coef_y[VGAN_B200_MAX_SCALES], ratio[VGAN_B200_MAX_SCALES];
+#pragma unroll
+    for (int m = 0; m < VGAN_B200_MAX_SCALES; ++m) {
+      ratio[m] = p.par[2 + m];
+      coef_x[m] = p.par[10 + m];
+      coef_y[m] = p.par[18 + m];
+    }
+    float acc_x = 0.f, acc_y = 0.f, rsum = 0.f;
+    uint32_t sf_mask = 0;
+    long long e_sfull = 0, e_comp = 0, e_slot = 0, e_pub = 0;
+    for (int k = 0; k < K; ++k) {
+      const int t = CS * k + c;
+      const bool valid = t < T;
+      const int jt = min(t, T - 1);
+      const int b = k & 1;
+      const bool col_is_x = jt < p.tiles_x;
+      float cf[VGAN_B200_MAX_SCALES];
+#pragma unroll
+      for (int m = 0; m < VGAN_B200_MAX_SCALES; ++m) cf[m] = valid ? (col_is_x ? coef_x[m] : coef_y[m]) : 0.f;
+      long long tq = clock64();
+      mbar_wait(&bar->nj_full[b], (k >> 1) & 1);
+      mbar_wait(&bar->s_full[b], (k >> 1) & 1);
+      e_sfull += clock64() - tq; tq = clock64();
+      tc_fence_after();
+      const float* njp = nj_smem + b * kTile + g * 64;
+      float ksum = 0.f;
+      uint4 pk[8];
+      {
+        uint4 h0[4], h1[4];
+        epi_half_tile<LADDER>(tmem + lane_addr + b * kTile + g * 64, njp, ni, m2c0, cf, ratio, p.n_scales,
+                              ksum, rsum, h0);
+        epi_half_tile<LADDER>(tmem + lane_addr + b * kTile + g * 64 + 32, njp + 32, ni, m2c0, cf, ratio,
+                              p.n_scales, ksum, rsum, h1);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { pk[i] = h0[i]; pk[4 + i] = h1[i]; }
+      }
+      tc_fence_before();
+      mbar_arrive(&bar->s_empty[b]);          // S and the norms are free; P is parked in registers
+      if (hh == 1) mbar_remote_arrive(mapa_u32(smem_u32(&bar->s_empty[b]), static_cast<uint32_t>(rank - 1)));
+      if (valid) { if (col_is_x) acc_x += ksum; else acc_y += ksum; }
+      // ---- publish the P tile: own slot first, then a bulk copy into the same slot of every peer
+      const int slot = t % kQSlots;
+      e_comp += clock64() - tq; tq = clock64();
+      if (t >= kQSlots) {
+        mbar_wait(&bar->slot_free[slot], (sf_mask >> slot) & 1);   // every CTA finished PV(t - kQSlots)
+        sf_mask ^= 1u << slot;
+      }
+      e_slot += clock64() - tq; tq = clock64();
+      uint8_t* p_slot = smem + kQSmemP + slot * kQPBytes;
+      uint8_t* p_row = p_slot + g * kChunkBytes + row * 128;
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        *reinterpret_cast<uint4*>(p_row + ((i ^ (row & 7)) << 4)) = pk[i];
+      fence_proxy_async_smem();
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (threadIdx.x == 0) {
+        mbar_arrive(&bar->p_full[slot]);
+        const uint32_t src = smem_u32(p_slot), fb = smem_u32(&bar->p_full[slot]);
+        for (int d = 0; d < CS; ++d) {          // the other slices of MY row tile
+          if (d == c) continue;
+          const uint32_t peer = static_cast<uint32_t>(2 * d + hh);
+          const uint32_t rbar = mapa_u32(fb, peer);
+          mbar_remote_arrive_expect_tx(rbar, kQPBytes);
+          bulk_copy_to_peer(mapa_u32(src, peer), src, kQPBytes, rbar);
+        }
+      }
+      e_pub += clock64() - tq;
+    }
+    if (p.dbg && threadIdx.x == 0) {
+      float* d = p.dbg + static_cast<int64_t>(blockIdx.x) * p.dbg_stride;
+      d[4] = static_cast<float>(e_sfull);
+      d[5] = static_cast<float>(e_comp);
+      d[6] = static_cast<float>(e_slot);
+      d[7] = static_cast<float>(e_pub);
+    }
+    // ---- partial sums of this CTA's tiles
+    acc_x = warp_sum(acc_x);
+    acc_y = warp_sum(acc_y);
+    if (lane == 0) { bar->red[warp][0] = acc_x; bar->red[warp][1] = acc_y; }
+    asm volatile("bar.sync 1, 256;" ::: "memory");   // all epilogue warps are done with the norms
+    nj_smem[g * kTile + row] = rsum;
+    if (threadIdx.x == 0 && grp == 0 && !dup) {
+      double sx = 0.0, sy = 0.0;
+      for (int wv = 0; wv < 8; ++wv) { sx += bar->red[wv][0]; sy += bar->red[wv][1]; }
+      if (row_is_x) {
+        atomicAdd(&p.sums[0], sx);
+      } else {
+        atomicAdd(&p.sums[1], sx);
+        atomicAdd(&p.sums[2], sy);
+      }
+    }
+    mbar_wait(&bar->o_full, 0);      // every PV of this CTA has completed: its P slots are dead
+    tc_fence_after();
+  }
+
+  // ===================== cluster-wide row sums of P, then the gradient rows =====================
+  float* rsx = reinterpret_cast<float*>(smem + kQSmemP);       // [CS][128], reuses P slot 0
+  tc_fence_before();
+  cluster_sync_all();      // #1: no CTA of the cluster reads a P slot any more
+  if (warp < 4) {
+    const int row = warp * 32 + lane;
+    const float tot = nj_smem[row] + nj_smem[kTile + row];     // both column halves of this CTA's tiles
+    const uint32_t a = smem_u32(rsx + c * kTile + row);
+    for (int d = 0; d < CS; ++d) st_cluster_f32(mapa_u32(a, static_cast<uint32_t>(2 * d + hh)), tot);
+  }
+  cluster_sync_all();      // #2: all partial row sums have arrived
+  if (warp < 8) {
+    const int q = warp & 3, g = warp >> 2;
+    const int row = q * 32 + lane;
+    float rtot = 0.f;
+    for (int d = 0; d < CS; ++d) rtot += rsx[d * kTile + row];
+    tc_fence_after();
+    if (!dup)
+      write_grad_rows(p, tmem_o, static_cast<uint32_t>(q * 32) << 16, g, row, ti, row_is_x, slice, slice_chunks, rtot);
+  }
+  tc_fence_before();
+  cluster_sync_all();      // both CTAs of every pair are done with tensor memory
+  if (warp == 11) tmem_dealloc_2cta(tmem, 512);
+}
+
+int launch_tc_pair(const TcParams& p, const CUtensorMap& map, const CUtensorMap& map64, int ladder,
+                   cudaStream_t st) {
+  const int ngrad = (p.gx_end - p.gx_begin) + (p.gy_end - p.gy_begin);
+  if (ngrad <= 0) return VGAN_B200_OK;
+  auto kern = ladder ? mmd2_tc_pair_kernel<true> : mmd2_tc_pair_kernel<false>;
+  VG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kQSmemTotal));
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(static_cast<unsigned>(((ngrad + 1) / 2) * p.ngroups * 2 * p.cs));
+  cfg.blockDim = dim3(kQThreads);
+  cfg.dynamicSmemBytes = kQSmemTotal;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = static_cast<unsigned>(2 * p.cs);
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  VG_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, map, map64, p));
+  return VGAN_B200_OK;
+}
+
+}  // namespace vg

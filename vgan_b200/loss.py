@@ -105,6 +105,8 @@ def mmd2_eval(X: torch.Tensor, Y: Optional[torch.Tensor], U: Optional[torch.Tens
         flags |= _lib.LADDER
     if os.environ.get("VGAN_B200_NO_CLUSTER"):
         flags |= _lib.NO_CLUSTER
+    if os.environ.get("VGAN_B200_NO_PAIR"):
+        flags |= _lib.NO_PAIR
     ws = _workspace(Nx, Ny, D, D_u, flags, dev)
     st = _stream()
     row_end = max(Nx, Ny) if row_end is None else row_end
