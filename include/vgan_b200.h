@@ -127,13 +127,27 @@ int vgan_b200_mmd2_matrix(const float* Z, int64_t n, int64_t D, const float* inv
  * (work unit, column tile) to buf[unit * stride + tile] (device floats).  NULL switches it off. */
 int vgan_b200_debug_tile_sums(float* buf, int stride);
 
+/* Tuning aid: selects the pipeline shape (operand-ring stages, P slots, PV lag) of the CTA-pair kernel;
+ * 0 = default.  Results do not depend on it. */
+int vgan_b200_debug_variant(int v);
+
 /* Debug aid: cta_group::2 Gram + gradient tile on one CTA pair. A0,A1,B bf16 [128,128], V bf16 [128,256];
  * S_out float [2,128,128] = A_h B^T;  O_out float [2,128,256] = bf16(S_h) V. */
 int vgan_b200_pair_probe(const void* A0, const void* A1, const void* B, const void* V, float* S_out, float* O_out,
                          void* stream);
 
-/* Debug aid: SM cycles for iters x 4 tcgen05.mma (M=128, N=n, K=16) on resident operands. */
-int vgan_b200_umma_rate_probe(int n, int iters, int b_mn, long long* cycles_out, void* stream);
+/* Measurement aid: L2 -> shared TMA throughput with `stages` x `loads` boxes ([box_rows x 64] bf16) in flight per
+ * CTA, `grid` CTAs, `nprod` producer (and consumer) threads; mode 0 = all CTAs stream the same tiles, 1 = each re-reads its own tile, 2 = one of each per
+ * stage.  Z bf16 [rows, cols]; cycles_out[grid] = SM cycles of each CTA for `iters` stages. */
+int vgan_b200_tma_rate_probe(const void* Z, int64_t rows, int64_t cols, int stages, int loads, int box_rows,
+                             int iters, int mode, int grid, int nprod, long long* cycles_out, void* stream);
+
+/* Measurement aid: SM cycles for iters x 4 tcgen05.mma (M=128, N=n, K=16) on resident operands in each of `grid`
+ * CTAs while `tma_warps` warps per CTA stream 16 KiB TMA boxes of Z (bf16 [rows,1024]) into spare shared memory:
+ * out[2b] = cycles of CTA b, out[2b+1] = boxes it loaded meanwhile.  Shows how operand reads and TMA fills
+ * share the shared-memory bandwidth. */
+int vgan_b200_umma_rate_probe(int n, int iters, int b_mn, const void* Z, int64_t rows, int tma_warps, int grid,
+                              long long* out, void* stream);
 
 int vgan_b200_umma_probe(const void* A, const void* B, float* S_out, float* O_out, void* stream);
 

@@ -17,7 +17,14 @@ for it in range(2):
     torch.cuda.synchronize()
     k._freeze()
 L.vgan_b200_debug_tile_sums(None, 0)
-d = dbg[:units, :8].cpu().numpy()
+d = dbg[:units, :16].cpu().numpy()
+if not os.environ.get("VGAN_B200_NO_PAIR"):
+    d = d[256:]          # the S_xx side kernel writes its tile sums into the first rows of the same buffer
+    lead = d[d[:, 0] > 0]
+    R = 2 * N // 128 / 4
+    print("pair leaders, per round: mma_total %.0f  wait_pfull %.0f  wait_ring_gram %.0f  wait_ring_pv %.0f  wait_sempty %.0f" % tuple(lead[:, i].mean() / R for i in (0, 1, 2, 11, 3)))
+    print("  producers(4 warps summed) wait_empty/round %.0f ; commit->reissue mean %.0f clk (n/round %.1f)" % (lead[:, 8].mean() / R, lead[:, 9].sum() / max(lead[:, 10].sum(), 1), lead[:, 10].mean() / R))
+    print("  issue->full-observed when MMA waited: gram %.0f clk (n/round %.1f), pv %.0f clk (n/round %.1f)" % (lead[:, 12].sum() / max(lead[:, 13].sum(), 1), lead[:, 13].mean() / R, lead[:, 14].sum() / max(lead[:, 15].sum(), 1), lead[:, 15].mean() / R))
 names = ["mma_total", "mma_wait_pfull", "mma_wait_ring", "mma_wait_sempty", "epi_wait_sfull", "epi_compute", "epi_wait_slot", "epi_publish"]
 tiles = 2 * N // 128
 print(f"N={N} tiles={tiles} rounds={tiles//4}; cycles per ROUND (4 tiles), mean over CTAs:")

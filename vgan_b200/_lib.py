@@ -22,6 +22,7 @@ EXPORTS = [
     "vgan_b200_prologue", "vgan_b200_scales", "vgan_b200_mmd2_fwd_bwd",
     "vgan_b200_colmax_penalty", "vgan_b200_finalize_loss", "vgan_b200_mmd2_matrix",
     "vgan_b200_umma_probe", "vgan_b200_debug_tile_sums", "vgan_b200_umma_rate_probe", "vgan_b200_pair_probe",
+    "vgan_b200_debug_variant", "vgan_b200_tma_rate_probe",
 ]
 
 
@@ -71,11 +72,15 @@ def lib() -> C.CDLL:
             L.vgan_b200_mmd2_matrix.argtypes = [p, i64, i64, p, i, f, p, p]
             L.vgan_b200_umma_probe.argtypes = [p, p, p, p, p]
             L.vgan_b200_debug_tile_sums.argtypes = [p, i]
-            L.vgan_b200_umma_rate_probe.argtypes = [i, i, i, p, p]
+            L.vgan_b200_umma_rate_probe.argtypes = [i, i, i, p, i64, i, i, p, p]
             L.vgan_b200_pair_probe.argtypes = [p, p, p, p, p, p, p]
+            L.vgan_b200_debug_variant.argtypes = [i]
+            L.vgan_b200_tma_rate_probe.argtypes = [p, i64, i64, i, i, i, i, i, i, i, p, p]
             for name in EXPORTS:
                 if name not in ("vgan_b200_last_error",):
                     getattr(L, name).restype = i
+            if os.environ.get("VGAN_B200_VARIANT"):
+                L.vgan_b200_debug_variant(int(os.environ["VGAN_B200_VARIANT"]))
             _lib = L
         return _lib
 

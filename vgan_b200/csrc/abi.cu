@@ -78,13 +78,17 @@ int run_penalty(const float*, int64_t, int64_t, float, unsigned long long*, floa
 int run_finalize(const double*, int64_t, int64_t, const float*, float*, cudaStream_t);
 int launch_matrix(const float*, int64_t, int64_t, const float*, int, float, float*, cudaStream_t);
 struct SimtParams;
-int launch_rate_probe(int n, int iters, int b_mn, long long* out, cudaStream_t st);
+int launch_rate_probe(const CUtensorMap& zmap, int n, int iters, int b_mn, int tma_warps, int tma_tiles, int grid,
+                      long long* out, cudaStream_t st);
+int launch_tma_rate(const CUtensorMap& map, int tiles, int kchunks, int stages, int loads, int box_rows, int iters,
+                    int mode, int grid, int nprod, long long* cycles, cudaStream_t st);
 int launch_pair_probe(const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, const CUtensorMap&, float*, float*,
                       cudaStream_t);
 int launch_simt_from_abi(const vgan_b200_layout_t& L, void* ws, int64_t row_begin, int64_t row_end, int xx_part,
                          int xx_nparts, const float* inv_scales, int n_scales, int flags, double* sums,
                          float* dY, const float* dY_mul, float* dX, cudaStream_t st);
 
+extern int g_pair_variant;
 static float* g_dbg = nullptr;
 static int g_dbg_stride = 0;
 
@@ -238,6 +242,7 @@ int vgan_b200_mmd2_fwd_bwd(void* ws, int64_t Nx, int64_t Ny, int64_t D, int64_t 
   p.par = par;
   p.sums = sums; p.dY = dY; p.dY_mul = dY_mul; p.dX = dX;
   p.dbg = g_dbg; p.dbg_stride = g_dbg_stride;
+  p.dbg_flags = g_pair_variant >> 8;
   CUtensorMap map;
   if (int e = make_tmap_bf16_2d(&map, p.zq, static_cast<uint64_t>(L.Nxp + L.Nyp), static_cast<uint64_t>(L.Dp)))
     return e;
@@ -319,6 +324,11 @@ int vgan_b200_debug_tile_sums(float* buf, int stride) {
   return VGAN_B200_OK;
 }
 
+int vgan_b200_debug_variant(int v) {
+  g_pair_variant = v;
+  return VGAN_B200_OK;
+}
+
 int vgan_b200_pair_probe(const void* A0, const void* A1, const void* B, const void* V, float* S_out, float* O_out,
                          void* stream) {
   if (int e = check_device()) return e;
@@ -330,9 +340,31 @@ int vgan_b200_pair_probe(const void* A0, const void* A1, const void* B, const vo
   return launch_pair_probe(a0, a1, bh, v, S_out, O_out, static_cast<cudaStream_t>(stream));
 }
 
-int vgan_b200_umma_rate_probe(int n, int iters, int b_mn, long long* cycles_out, void* stream) {
+int vgan_b200_tma_rate_probe(const void* Z, int64_t rows, int64_t cols, int stages, int loads, int box_rows,
+                             int iters, int mode, int grid, int nprod, long long* cycles_out, void* stream) {
   if (int e = check_device()) return e;
-  return launch_rate_probe(n, iters, b_mn, cycles_out, static_cast<cudaStream_t>(stream));
+  if (!Z || !cycles_out || rows % kTile || cols % kChunk || (box_rows != 64 && box_rows != 128)) {
+    set_error("tma_rate_probe: bad arguments");
+    return VGAN_B200_ERR_ARG;
+  }
+  CUtensorMap map;
+  if (int e = make_tmap_bf16_2d(&map, Z, static_cast<uint64_t>(rows), static_cast<uint64_t>(cols), box_rows)) return e;
+  return launch_tma_rate(map, static_cast<int>(rows / kTile), static_cast<int>(cols / kChunk), stages, loads, box_rows,
+                         iters, mode, grid, nprod < 1 ? 1 : (nprod > 8 ? 8 : nprod), cycles_out,
+                         static_cast<cudaStream_t>(stream));
+}
+
+int vgan_b200_umma_rate_probe(int n, int iters, int b_mn, const void* Z, int64_t rows, int tma_warps, int grid,
+                              long long* out, void* stream) {
+  if (int e = check_device()) return e;
+  if (!Z || rows % kTile || tma_warps < 0 || tma_warps > 8 || grid < 1 || !out) {
+    set_error("umma_rate_probe: bad arguments");
+    return VGAN_B200_ERR_ARG;
+  }
+  CUtensorMap map;
+  if (int e = make_tmap_bf16_2d(&map, Z, static_cast<uint64_t>(rows), 1024)) return e;
+  return launch_rate_probe(map, n, iters, b_mn, tma_warps, static_cast<int>(rows / kTile), grid, out,
+                           static_cast<cudaStream_t>(stream));
 }
 
 int vgan_b200_umma_probe(const void* A, const void* B, float* S_out, float* O_out, void* stream) {

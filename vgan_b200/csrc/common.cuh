@@ -47,6 +47,7 @@ struct TcParams {
   float* dX;
   float* dbg;                 // debug: per-(unit, tile) kernel sums, or nullptr
   int dbg_stride;
+  int dbg_flags;              // measurement only: bit 0 = exchange 16 bytes per P tile instead of 32 KiB (wrong results)
 };
 
 #define VG_CUDA_CHECK(expr)                                                          \

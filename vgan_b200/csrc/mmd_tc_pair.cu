@@ -17,34 +17,41 @@
 
 namespace vg {
 
-constexpr int kQStages = 4;                       // 4 x 32 KiB operand ring
+// Pipeline shape = template parameters <STAGES, SLOTS, LAG>: STAGES x 32 KiB operand ring, SLOTS x 32 KiB
+// P tiles (STAGES + SLOTS <= 7 fits the 227 KiB of shared memory), PV(t) issued LAG periods after
+// tile t's turn.  The exchange latency (epilogue + DSMEM copy) must fit inside LAG periods.
 constexpr int kQStageBytes = 2 * kChunkBytes;
-constexpr int kQSlots = 3;                        // 3 x 32 KiB P tiles
 constexpr int kQPBytes = 2 * kChunkBytes;
-constexpr int kQLag = 1;                           // PV(t) is issued kQLag periods after tile t's turn
-constexpr int kQThreads = 384;
+constexpr int kQThreads = 480;                     // 8 epilogue + MMA + norms + 4 TMA producer warps + P publisher
+constexpr int kQProducers = 4;                    // warps 8, 11, 12, 13
+constexpr int kQMaxStages = 6, kQMaxSlots = 6;
 
 struct __align__(8) PairBarriers {
-  uint64_t ring_full[kQStages], ring_empty[kQStages];
+  uint64_t ring_full[kQMaxStages], ring_empty[kQMaxStages];
   uint64_t s_full[2], s_empty[2];
   uint64_t nj_full[2];
-  uint64_t p_full[kQSlots], slot_free[kQSlots], p_pair[kQSlots];
+  uint64_t p_full[kQMaxSlots], slot_free[kQMaxSlots], p_pair[kQMaxSlots], pub_full[kQMaxSlots];
   uint64_t o_full;
   uint32_t tmem_base;
   float red[8][4];
+  long long ts_issue[kQMaxStages], ts_commit[kQMaxStages];   // debug timers (p.dbg)
 };
 
 constexpr int kQSmemRing = 0;
-constexpr int kQSmemP = kQSmemRing + kQStages * kQStageBytes;
-constexpr int kQSmemNj = kQSmemP + kQSlots * kQPBytes;
-constexpr int kQSmemBar = kQSmemNj + 2 * kTile * 4;
-constexpr int kQSmemTotal = kQSmemBar + static_cast<int>(sizeof(PairBarriers));
-static_assert(kQSmemTotal <= 232448, "shared memory budget");
+__host__ __device__ constexpr int q_smem_total(int stages, int slots) {
+  return stages * kQStageBytes + slots * kQPBytes + 2 * kTile * 4 + static_cast<int>(sizeof(PairBarriers));
+}
 
-template <bool LADDER>
+template <bool LADDER, int STAGES, int SLOTS, int LAG>
 __global__ void __launch_bounds__(kQThreads, 1)
 mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__ CUtensorMap zmap64,
                     const TcParams p) {
+  constexpr int kQStages = STAGES, kQSlots = SLOTS, kQLag = LAG;
+  constexpr int kQSmemP = kQSmemRing + kQStages * kQStageBytes;
+  constexpr int kQSmemNj = kQSmemP + kQSlots * kQPBytes;
+  constexpr int kQSmemBar = kQSmemNj + 2 * kTile * 4;
+  static_assert(q_smem_total(STAGES, SLOTS) <= 232448, "shared memory budget");
+  static_assert(STAGES % kQProducers == 0, "each producer warp owns fixed ring stages");
   extern __shared__ __align__(1024) uint8_t smem[];
   if ((smem_u32(smem) & 1023u) != 0) __trap();
   PairBarriers* bar = reinterpret_cast<PairBarriers*>(smem + kQSmemBar);
@@ -75,6 +82,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
   const int pv_stages = slice_chunks > 0 ? 1 : 0;     // one stage per tile: this CTA's half of the slice
   const int my_chunks = slice_chunks >> 1;             // 64-feature chunks of the slice held by this CTA
 
+  const uint32_t pbytes = (p.dbg_flags & 1) ? 16u : static_cast<uint32_t>(kQPBytes);
   if (threadIdx.x == 0) {
     for (int s = 0; s < kQStages; ++s) {
       mbar_init(&bar->ring_full[s], 1);
@@ -89,9 +97,14 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
       mbar_init(&bar->p_full[s], 1);
       mbar_init(&bar->slot_free[s], CS);
       mbar_init(&bar->p_pair[s], 1);
+      mbar_init(&bar->pub_full[s], 1);
     }
     mbar_init(&bar->o_full, 1);
     fence_barrier_init();
+    // P tiles written by a peer land by bulk copy: the RECEIVER arms its own barrier (no remote arrive);
+    // the first kQSlots tiles here, tile t + kQSlots right after the wait for tile t (warp 9)
+    for (int t = 0; t < kQSlots && t < TT; ++t)
+      if (t % CS != c) mbar_arrive_expect_tx(&bar->p_full[t % kQSlots], pbytes);
   }
   if (warp == 11) {
     tmem_alloc_2cta(&bar->tmem_base, 512);
@@ -104,40 +117,84 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
   const uint32_t tmem = bar->tmem_base;
   const uint32_t tmem_o = tmem + 256;
 
-  if (warp == 8) {
-    // ===================== TMA producer (mirrors the MMA stream order exactly) =====================
-    if (lane == 0) {
-      uint32_t s = 0, ph = 0;
-      auto gram_stages = [&](int k, int kc0, int kc1) {
-        const int jt = min(CS * k + c, T - 1);
-        for (int kc = kc0; kc < kc1; ++kc) {
+  if (warp == 8 || (warp >= 11 && warp <= 13)) {
+    // ===================== TMA producers (mirror the MMA stream order exactly) =====================
+    // One thread issuing wait -> expect_tx -> 2 loads per stage sustains only ~1 stage / 800 cycles
+    // (tools/gpu_tma_rate.py: the loop is latency-bound, not L2-bound), three times slower than the MMAs
+    // drain a Gram stage.  kQProducers warps therefore walk the same stage sequence and each issues every
+    // kQProducers-th stage; within a stage the two boxes are issued by two lanes.
+    const int pj = warp == 8 ? 0 : warp - 10;            // producer index 0..kQProducers-1
+    uint32_t s = 0, ph = 0;
+    int r = 0;                                           // stage-use counter modulo kQProducers
+    long long pw_empty = 0, rel_sum = 0;
+    int rel_n = 0, n_use = 0;
+    auto advance = [&]() {
+      ++n_use;
+      if (++r == kQProducers) r = 0;
+      if (++s == kQStages) { s = 0; ph ^= 1; }
+    };
+    auto gram_stages = [&](int k, int kc0, int kc1) {
+      const int jt = min(CS * k + c, T - 1);
+      for (int kc = kc0; kc < kc1; ++kc) {
+        if (r == pj) {
+          const long long tw0 = clock64();
           mbar_wait(&bar->ring_empty[s], ph ^ 1);
+          if (p.dbg && lane == 0) {
+            const long long now = clock64();
+            pw_empty += now - tw0;
+            if (n_use >= kQStages) { rel_sum += now - *(volatile long long*)&bar->ts_commit[s]; ++rel_n; }
+            *(volatile long long*)&bar->ts_issue[s] = now;
+          }
           uint8_t* dst = smem + kQSmemRing + s * kQStageBytes;
-          if (hh == 0) mbar_arrive_expect_tx(&bar->ring_full[s], 2 * (kChunkBytes + kChunkBytes / 2));
-          tma_load_2d_2cta(dst, &zmap, &bar->ring_full[s], kc * kChunk, ti * kTile);
-          tma_load_2d_2cta(dst + kChunkBytes, &zmap64, &bar->ring_full[s], kc * kChunk, jt * kTile + 64 * hh);
-          if (++s == kQStages) { s = 0; ph ^= 1; }
+          if (p.dbg_flags & 2) {            // measurement only: no operand loads
+            if (lane == 0 && hh == 0) mbar_arrive(&bar->ring_full[s]);
+          } else if (lane == 0) {
+            if (hh == 0) mbar_arrive_expect_tx(&bar->ring_full[s], 2 * (kChunkBytes + kChunkBytes / 2));
+            tma_load_2d_2cta(dst, &zmap, &bar->ring_full[s], kc * kChunk, ti * kTile);
+          } else if (lane == 1) {
+            tma_load_2d_2cta(dst + kChunkBytes, &zmap64, &bar->ring_full[s], kc * kChunk, jt * kTile + 64 * hh);
+          }
+          __syncwarp();
         }
-      };
-      auto pv_stages_load = [&](int t) {
-        const int jt = min(t, T - 1);
-        for (int h = 0; h < pv_stages; ++h) {
-          mbar_wait(&bar->ring_empty[s], ph ^ 1);
-          uint8_t* dst = smem + kQSmemRing + s * kQStageBytes;
-          if (hh == 0) mbar_arrive_expect_tx(&bar->ring_full[s], slice_chunks * kChunkBytes);
-          for (int cc = 0; cc < my_chunks; ++cc)
-            tma_load_2d_2cta(dst + cc * kChunkBytes, &zmap, &bar->ring_full[s],
-                             (slice * p.slice_chunks + hh * my_chunks + cc) * kChunk, jt * kTile);
-          if (++s == kQStages) { s = 0; ph ^= 1; }
-        }
-      };
-      gram_stages(0, 0, p.kchunks);
-      for (int m = 0; m < TT + kQLag; ++m) {
-        const int kn = 1 + m / CS, q = m % CS;
-        if (kn < K) gram_stages(kn, (q * p.kchunks) / CS, ((q + 1) * p.kchunks) / CS);
-        const int tc = m - kQLag;
-        if (tc >= 0 && tc < TT) pv_stages_load(tc);
+        advance();
       }
+    };
+    auto pv_stages_load = [&](int t) {
+      const int jt = min(t, T - 1);
+      for (int h = 0; h < pv_stages; ++h) {
+        if (r == pj) {
+          const long long tw0 = clock64();
+          mbar_wait(&bar->ring_empty[s], ph ^ 1);
+          if (p.dbg && lane == 0) {
+            const long long now = clock64();
+            pw_empty += now - tw0;
+            if (n_use >= kQStages) { rel_sum += now - *(volatile long long*)&bar->ts_commit[s]; ++rel_n; }
+            *(volatile long long*)&bar->ts_issue[s] = now;
+          }
+          uint8_t* dst = smem + kQSmemRing + s * kQStageBytes;
+          if (p.dbg_flags & 4) {            // measurement only: no V loads
+            if (lane == 0 && hh == 0) mbar_arrive(&bar->ring_full[s]);
+          } else if (lane == 0 && hh == 0) mbar_arrive_expect_tx(&bar->ring_full[s], slice_chunks * kChunkBytes);
+          if (!(p.dbg_flags & 4) && lane < my_chunks)
+            tma_load_2d_2cta(dst + lane * kChunkBytes, &zmap, &bar->ring_full[s],
+                             (slice * p.slice_chunks + hh * my_chunks + lane) * kChunk, jt * kTile);
+          __syncwarp();
+        }
+        advance();
+      }
+    };
+    gram_stages(0, 0, p.kchunks);
+    for (int m = 0; m < TT + kQLag; ++m) {
+      const int kn = 1 + m / CS, q = m % CS;
+      if (kn < K) gram_stages(kn, (q * p.kchunks) / CS, ((q + 1) * p.kchunks) / CS);
+      const int tc = m - kQLag;
+      if (tc >= 0 && tc < TT) pv_stages_load(tc);
+    }
+    if (p.dbg && lane == 0 && hh == 0) {
+      float* d = p.dbg + static_cast<int64_t>(blockIdx.x) * p.dbg_stride;
+      atomicAdd(&d[8], static_cast<float>(pw_empty));
+      atomicAdd(&d[9], static_cast<float>(rel_sum));
+      atomicAdd(&d[10], static_cast<float>(rel_n));
     }
   } else if (warp == 10) {
     // ===================== bulk-copy producer: scaled column norms of this CTA's tiles ============
@@ -151,6 +208,24 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
                      &bar->nj_full[b]);
       }
     }
+  } else if (warp == 14) {
+    // ===================== publisher: bulk-copies this CTA's P tiles to the other slices of its row tile =======
+    // (kept off the epilogue warps: the DSMEM copies of one tile take longer than the epilogue of the next)
+    // pub_full[slot] counts only this CTA's own tiles (waiting on p_full would alias: it advances through
+    // the peers' tiles in between, and a parity wait cannot tell phases two apart)
+    uint32_t pub_mask = 0;
+    for (int k = 0; k < K; ++k) {
+      const int t = CS * k + c;
+      const int slot = t % kQSlots;
+      mbar_wait(&bar->pub_full[slot], (pub_mask >> slot) & 1);
+      pub_mask ^= 1u << slot;
+      if (lane < CS && lane != c) {
+        const uint32_t peer = static_cast<uint32_t>(2 * lane + hh);
+        const uint32_t src = smem_u32(smem + kQSmemP + slot * kQPBytes);
+        bulk_copy_to_peer(mapa_u32(src, peer), src, pbytes, mapa_u32(smem_u32(&bar->p_full[slot]), peer));
+      }
+      __syncwarp();
+    }
   } else if (warp == 9 && hh == 1) {
     // ===================== peer CTA: forward "my P tile t is in place" to the leader's MMA warp =========
     uint32_t pf_mask = 0;
@@ -159,7 +234,10 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
       const int slot = t % kQSlots;
       mbar_wait(&bar->p_full[slot], (pf_mask >> slot) & 1);
       pf_mask ^= 1u << slot;
-      if (lane == 0) mbar_remote_arrive(pp0 + slot * 8);
+      if (lane == 0) {
+        if (t + kQSlots < TT && (t + kQSlots) % CS != c) mbar_arrive_expect_tx(&bar->p_full[slot], pbytes);
+        mbar_remote_arrive(pp0 + slot * 8);
+      }
       __syncwarp();
     }
   } else if (warp == 9) {
@@ -171,7 +249,8 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     const uint32_t ring_lo = (smem_u32(smem + kQSmemRing) & 0x3FFFFu) >> 4;
     const uint32_t p_lo0 = (smem_u32(smem + kQSmemP) & 0x3FFFFu) >> 4;
     uint32_t s = 0, ph = 0, pf_mask = 0;
-    long long t_pf = 0, t_ring = 0, t_se = 0;
+    long long t_pf = 0, t_ring = 0, t_se = 0, t_ring_pv = 0, lat_g = 0, lat_p = 0;
+    int lat_gn = 0, lat_pn = 0;
     const long long t_begin = clock64();
     auto gram = [&](int k, int kc0, int kc1) {
       const int b = k & 1;
@@ -186,7 +265,9 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
         {
           const long long t0 = clock64();
           mbar_wait(&bar->ring_full[s], ph);
-          t_ring += clock64() - t0;
+          const long long now = clock64();
+          t_ring += now - t0;
+          if (p.dbg && now - t0 > 100) { lat_g += now - *(volatile long long*)&bar->ts_issue[s]; ++lat_gn; }
         }
         tc_fence_after();
         const uint32_t a_lo = ring_lo + s * (kQStageBytes >> 4);
@@ -199,6 +280,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
             umma_bf16_ss_2cta(d_tmem, adesc, bdesc, idesc_gram, (kc | kk) != 0);
           }
           umma_commit_2cta_mc(&bar->ring_empty[s], pair_mask);
+          if (p.dbg) *(volatile long long*)&bar->ts_commit[s] = clock64();
           if (kc == p.kchunks - 1) umma_commit_2cta_mc(&bar->s_full[b], pair_mask);
         }
         __syncwarp();
@@ -210,6 +292,8 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
       {
         const long long t0 = clock64();
         mbar_wait(&bar->p_full[slot], (pf_mask >> slot) & 1);   // my P(I0, t)
+        if (lane == 0 && t + kQSlots < TT && (t + kQSlots) % CS != c)
+          mbar_arrive_expect_tx(&bar->p_full[slot], pbytes);  // arm the slot for its next (remote) tile
         mbar_wait(&bar->p_pair[slot], (pf_mask >> slot) & 1);   // the peer's P(I1, t)
         t_pf += clock64() - t0;
       }
@@ -220,7 +304,9 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
         {
           const long long t0 = clock64();
           mbar_wait(&bar->ring_full[s], ph);
-          t_ring += clock64() - t0;
+          const long long now = clock64();
+          t_ring_pv += now - t0;
+          if (p.dbg && now - t0 > 100) { lat_p += now - *(volatile long long*)&bar->ts_issue[s]; ++lat_pn; }
         }
         tc_fence_after();
         const uint32_t v_lo = ring_lo + s * (kQStageBytes >> 4);
@@ -233,6 +319,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
             umma_bf16_ss_2cta(tmem_o, adesc, bdesc, idesc_pv, (t | kk) != 0);
           }
           umma_commit_2cta_mc(&bar->ring_empty[s], pair_mask);
+          if (p.dbg) *(volatile long long*)&bar->ts_commit[s] = clock64();
         }
         __syncwarp();
         if (++s == kQStages) { s = 0; ph ^= 1; }
@@ -257,6 +344,11 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
       d[1] = static_cast<float>(t_pf);
       d[2] = static_cast<float>(t_ring);
       d[3] = static_cast<float>(t_se);
+      d[11] = static_cast<float>(t_ring_pv);
+      d[12] = static_cast<float>(lat_g);
+      d[13] = static_cast<float>(lat_gn);
+      d[14] = static_cast<float>(lat_p);
+      d[15] = static_cast<float>(lat_pn);
     }
   } else if (warp < 8) {
     // ===================== epilogue warps: this CTA's own column tiles =====================
@@ -321,15 +413,8 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
       fence_proxy_async_smem();
       asm volatile("bar.sync 1, 256;" ::: "memory");
       if (threadIdx.x == 0) {
-        mbar_arrive(&bar->p_full[slot]);
-        const uint32_t src = smem_u32(p_slot), fb = smem_u32(&bar->p_full[slot]);
-        for (int d = 0; d < CS; ++d) {          // the other slices of MY row tile
-          if (d == c) continue;
-          const uint32_t peer = static_cast<uint32_t>(2 * d + hh);
-          const uint32_t rbar = mapa_u32(fb, peer);
-          mbar_remote_arrive_expect_tx(rbar, kQPBytes);
-          bulk_copy_to_peer(mapa_u32(src, peer), src, kQPBytes, rbar);
-        }
+        mbar_arrive(&bar->p_full[slot]);     // own MMA warp
+        mbar_arrive(&bar->pub_full[slot]);   // publisher warp
       }
       e_pub += clock64() - tq;
     }
@@ -385,16 +470,17 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
   if (warp == 11) tmem_dealloc_2cta(tmem, 512);
 }
 
-int launch_tc_pair(const TcParams& p, const CUtensorMap& map, const CUtensorMap& map64, int ladder,
-                   cudaStream_t st) {
+template <int STAGES, int SLOTS, int LAG>
+static int launch_pair_variant(const TcParams& p, const CUtensorMap& map, const CUtensorMap& map64, int ladder,
+                               cudaStream_t st) {
   const int ngrad = (p.gx_end - p.gx_begin) + (p.gy_end - p.gy_begin);
-  if (ngrad <= 0) return VGAN_B200_OK;
-  auto kern = ladder ? mmd2_tc_pair_kernel<true> : mmd2_tc_pair_kernel<false>;
-  VG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kQSmemTotal));
+  auto kern = ladder ? mmd2_tc_pair_kernel<true, STAGES, SLOTS, LAG> : mmd2_tc_pair_kernel<false, STAGES, SLOTS, LAG>;
+  constexpr int smem = q_smem_total(STAGES, SLOTS);
+  VG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(static_cast<unsigned>(((ngrad + 1) / 2) * p.ngroups * 2 * p.cs));
   cfg.blockDim = dim3(kQThreads);
-  cfg.dynamicSmemBytes = kQSmemTotal;
+  cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -405,6 +491,20 @@ int launch_tc_pair(const TcParams& p, const CUtensorMap& map, const CUtensorMap&
   cfg.numAttrs = 1;
   VG_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, map, map64, p));
   return VGAN_B200_OK;
+}
+
+int g_pair_variant = 0;   // debug/tuning: vgan_b200_debug_variant()
+
+int launch_tc_pair(const TcParams& p, const CUtensorMap& map, const CUtensorMap& map64, int ladder,
+                   cudaStream_t st) {
+  const int ngrad = (p.gx_end - p.gx_begin) + (p.gy_end - p.gy_begin);
+  if (ngrad <= 0) return VGAN_B200_OK;
+  // STAGES must be a multiple of kQProducers (each producer warp owns fixed ring stages)
+  switch (g_pair_variant & 255) {
+    case 1: return launch_pair_variant<4, 3, 2>(p, map, map64, ladder, st);
+    case 2: return launch_pair_variant<4, 3, 3>(p, map, map64, ladder, st);
+    default: return launch_pair_variant<4, 3, 1>(p, map, map64, ladder, st);
+  }
 }
 
 }  // namespace vg

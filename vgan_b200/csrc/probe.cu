@@ -114,13 +114,21 @@ int launch_probe(const CUtensorMap& mapA, const CUtensorMap& mapB, float* S_out,
 // Issues `iters` x 4 tcgen05.mma (M=128, N=n, K=16) on resident shared-memory operands (no TMA
 // traffic) and returns the elapsed SM cycles: the achievable tensor rate for SS operands.
 namespace vg {
-__global__ void __launch_bounds__(128, 1) umma_rate_kernel(int n, int iters, int b_mn, long long* out) {
+__global__ void __launch_bounds__(384, 1)
+umma_rate_kernel(const __grid_constant__ CUtensorMap zmap, int n, int iters, int b_mn, int tma_warps, int tma_tiles,
+                 long long* out) {
   extern __shared__ __align__(1024) uint8_t smem[];
-  __shared__ uint64_t bar;
+  __shared__ uint64_t bar, tbar[8];
   __shared__ uint32_t tmem_slot;
+  __shared__ volatile int done;
   const int warp = threadIdx.x >> 5;
-  for (int i = threadIdx.x; i < 6 * kChunkBytes / 4; i += 128) reinterpret_cast<uint32_t*>(smem)[i] = 0x3c003c00u;
-  if (threadIdx.x == 0) { mbar_init(&bar, 1); fence_barrier_init(); }
+  for (int i = threadIdx.x; i < 6 * kChunkBytes / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0x3c003c00u;
+  if (threadIdx.x == 0) {
+    mbar_init(&bar, 1);
+    for (int i = 0; i < 8; ++i) mbar_init(&tbar[i], 1);
+    done = 0;
+    fence_barrier_init();
+  }
   if (warp == 0) { tmem_alloc(&tmem_slot, 512); tmem_relinquish(); }
   fence_proxy_async_smem();
   tc_fence_before();
@@ -146,17 +154,36 @@ __global__ void __launch_bounds__(128, 1) umma_rate_kernel(int n, int iters, int
     if (elect_one()) umma_commit(&bar);
     __syncwarp();
     mbar_wait(&bar, 0);
-    if (threadIdx.x == 0) out[0] = clock64() - t0;
+    if (threadIdx.x == 0) { out[2 * blockIdx.x] = clock64() - t0; done = 1; }
+  } else if (warp >= 4 && warp < 4 + tma_warps && (threadIdx.x & 31) == 0) {
+    // concurrent TMA traffic into spare shared memory (beyond the 6 operand chunks): each warp keeps one
+    // 16 KiB box in flight and re-issues it as soon as it lands, until the MMA loop is finished
+    const int w = warp - 4;
+    uint8_t* dst = smem + (6 + w) * kChunkBytes;
+    long long n_loads = 0;
+    uint32_t ph = 0;
+    int tile = (blockIdx.x * 7 + w) % tma_tiles, kc = w;
+    while (!done) {
+      mbar_arrive_expect_tx(&tbar[w], kChunkBytes);
+      tma_load_2d(dst, &zmap, &tbar[w], (kc & 15) * kChunk, tile * kTile);
+      mbar_wait(&tbar[w], ph);
+      ph ^= 1;
+      ++n_loads; ++kc;
+      if ((kc & 15) == 0) tile = (tile + 1) % tma_tiles;
+    }
+    atomicAdd(reinterpret_cast<unsigned long long*>(&out[2 * blockIdx.x + 1]), static_cast<unsigned long long>(n_loads));
   }
   tc_fence_before();
   __syncthreads();
   if (warp == 0) tmem_dealloc(tmem, 512);
 }
 
-int launch_rate_probe(int n, int iters, int b_mn, long long* out, cudaStream_t st) {
-  const int bytes = 6 * kChunkBytes;
+int launch_rate_probe(const CUtensorMap& zmap, int n, int iters, int b_mn, int tma_warps, int tma_tiles, int grid,
+                      long long* out, cudaStream_t st) {
+  const int bytes = (6 + 8) * kChunkBytes;
   VG_CUDA_CHECK(cudaFuncSetAttribute(umma_rate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
-  umma_rate_kernel<<<1, 128, bytes, st>>>(n, iters, b_mn, out);
+  VG_CUDA_CHECK(cudaMemsetAsync(out, 0, sizeof(long long) * 2 * grid, st));
+  umma_rate_kernel<<<grid, 384, bytes, st>>>(zmap, n, iters, b_mn, tma_warps, tma_tiles, out);
   VG_CUDA_CHECK(cudaGetLastError());
   return VGAN_B200_OK;
 }
