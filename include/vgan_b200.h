@@ -63,6 +63,7 @@ typedef struct {
   size_t off_stats;   /* double[2+Dp] sum|z|^2, spare, column sums of the stored fp32 rows   */
   size_t off_cmax;    /* uint64[D_u]  packed (value,row) column maxima of U                   */
   size_t off_par;     /* float[32]    device parameter block of K1 (exp2 scale, coefficients) */
+  size_t off_xchg;    /* bytes: P-tile exchange scratch of the D_p > 256 kernels (L2 resident), else empty  */
   size_t total;       /* bytes to allocate                                                   */
 } vgan_b200_layout_t;
 

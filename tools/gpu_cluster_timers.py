@@ -22,9 +22,9 @@ if not os.environ.get("VGAN_B200_NO_PAIR"):
     d = d[256:]          # the S_xx side kernel writes its tile sums into the first rows of the same buffer
     lead = d[d[:, 0] > 0]
     R = 2 * N // 128 / 4
-    print("pair leaders, per round: mma_total %.0f  wait_pfull %.0f  wait_ring_gram %.0f  wait_ring_pv %.0f  wait_sempty %.0f" % tuple(lead[:, i].mean() / R for i in (0, 1, 2, 11, 3)))
-    print("  producers(4 warps summed) wait_empty/round %.0f ; commit->reissue mean %.0f clk (n/round %.1f)" % (lead[:, 8].mean() / R, lead[:, 9].sum() / max(lead[:, 10].sum(), 1), lead[:, 10].mean() / R))
-    print("  issue->full-observed when MMA waited: gram %.0f clk (n/round %.1f), pv %.0f clk (n/round %.1f)" % (lead[:, 12].sum() / max(lead[:, 13].sum(), 1), lead[:, 13].mean() / R, lead[:, 14].sum() / max(lead[:, 15].sum(), 1), lead[:, 15].mean() / R))
+    print("pair leaders, cycles per round (4 tiles):")
+    print("  Gram warp: total %.0f  wait_g_ring %.0f  wait_s_empty %.0f" % tuple(lead[:, i].mean() / R for i in (0, 2, 3)))
+    print("  PV warp:   total %.0f  wait_p %.0f  wait_v_ring %.0f" % tuple(lead[:, i].mean() / R for i in (8, 1, 9)))
 names = ["mma_total", "mma_wait_pfull", "mma_wait_ring", "mma_wait_sempty", "epi_wait_sfull", "epi_compute", "epi_wait_slot", "epi_publish"]
 tiles = 2 * N // 128
 print(f"N={N} tiles={tiles} rounds={tiles//4}; cycles per ROUND (4 tiles), mean over CTAs:")

@@ -29,7 +29,7 @@ EXPORTS = [
 class Layout(C.Structure):
     _fields_ = [(n, C.c_int64) for n in ("Nx", "Ny", "D", "Dp", "Nxp", "Nyp")] + \
                [(n, C.c_size_t) for n in ("off_zq", "off_zf", "off_nrm", "off_nrms", "off_mean",
-                                          "off_stats", "off_cmax", "off_par", "total")]
+                                          "off_stats", "off_cmax", "off_par", "off_xchg", "total")]
 
 
 def build(force: bool = False) -> str:

@@ -119,9 +119,12 @@ static int fill_layout(int64_t Nx, int64_t Ny, int64_t D, int64_t D_u, int flags
   L->off_mean = off;  off = align_up(off + L->Dp * 4, 1024);
   L->off_nrm = off;   off = align_up(off + rows * 4, 1024);
   L->off_nrms = off;  off = align_up(off + rows * 4, 1024);
+  L->off_xchg = off;  // before the operand: must not depend on D_u (callers pass D_u = 0 to recompute offsets)
+  if (!fp32 && L->Dp > kSliceMax) off = align_up(off + static_cast<size_t>(kXchgSms) * kXchgBytesPerSm, 1024);
   L->off_zq = off;
   L->off_zf = off;    off = align_up(off + rows * L->Dp * (fp32 ? 4 : 2), 1024);
   L->off_cmax = off;  off = align_up(off + static_cast<size_t>(D_u > 0 ? D_u : 1) * 8, 1024);
+
   L->total = off;
   return VGAN_B200_OK;
 }
@@ -241,6 +244,7 @@ int vgan_b200_mmd2_fwd_bwd(void* ws, int64_t Nx, int64_t Ny, int64_t D, int64_t 
   p.nrms = reinterpret_cast<const float*>(base + L.off_nrms);
   p.par = par;
   p.sums = sums; p.dY = dY; p.dY_mul = dY_mul; p.dX = dX;
+  p.xchg = L.Dp > kSliceMax ? base + L.off_xchg : nullptr;
   p.dbg = g_dbg; p.dbg_stride = g_dbg_stride;
   p.dbg_flags = g_pair_variant >> 8;
   CUtensorMap map;

@@ -24,6 +24,10 @@ constexpr float kLog2e = 1.4426950408889634f;
 // par[10 + m] = cx * inv_s[m]              (P coefficients for X columns, cx = +1/Nx)
 // par[18 + m] = cy * inv_s[m]              (P coefficients for Y columns, cy = -1/Ny)
 constexpr int kParFloats = 32;
+// P-tile exchange scratch (pair kernel): 3 slots of one bf16 [128,128] tile per SM, indexed by %smid so that a
+// region is only ever rewritten by the CTA resident on that SM (stays in L2, never streams to HBM)
+constexpr int kXchgSms = 256;
+constexpr int kXchgBytesPerSm = 3 * 2 * kChunkBytes;
 
 struct TcParams {
   int tiles_x, tiles_y;       // 128-row tiles in the X / Y regions of the stacked operand
@@ -45,6 +49,7 @@ struct TcParams {
   float* dY;
   const float* dY_mul;
   float* dX;
+  uint8_t* xchg;              // P-tile exchange scratch, kXchgSms x kXchgBytesPerSm (cluster kernels), L2 resident
   float* dbg;                 // debug: per-(unit, tile) kernel sums, or nullptr
   int dbg_stride;
   int dbg_flags;              // measurement only: bit 0 = exchange 16 bytes per P tile instead of 32 KiB (wrong results)

@@ -2,56 +2,63 @@
 // Cluster = 2 row tiles x CS feature slices.  CTAs 2c (leader) and 2c+1 form the tcgen05 pair of
 // slice c; they own DIFFERENT row tiles (I0, I1) and share every B operand:
 //   Gram  M=256 = [Z_I0 ; Z_I1] chunks (each CTA loads its own 16 KiB), B = Z_J chunk, each CTA
-//         loads only HALF of its 128 rows (8 KiB)   -> 6 KiB instead of 8 KiB smem read per MMA
+//         loads only HALF of its 128 rows (8 KiB)
 //   PV    M=256 = [P(I0,t) ; P(I1,t)], B = Z_Jt[:, slice c], each CTA holds half of the features
-//         (N = 256 per MMA)                            -> 8 KiB instead of 16 KiB per 256 features
-// Shared-memory traffic is what bounds the 1-CTA cluster kernel (mmd_tc_cluster.cu: an N=128 SS MMA
-// needs the full 128 B/clk of shared-memory bandwidth by itself); pairing cuts it by ~1/3.
 // P tiles are exchanged among the CTAs of the SAME row tile exactly as in mmd_tc_cluster.cu.
-// Only the leader issues MMAs; extra signalling: the peer's epilogue arrives on the leader's
-// s_empty, the peer's (otherwise idle) MMA warp forwards its p_full to the leader (p_pair),
-// and every tcgen05.commit is multicast to both CTAs of the pair.
+//
+// What bounds this kernel is not the tensor pipe, L2 or shared memory but the ISSUE stream of the
+// single thread that feeds the tensor pipe (tools/gpu_cluster_timers.py, gpu_mma_rate.py,
+// gpu_tma_rate.py): a tcgen05.mma costs ~48 issue cycles against 64 execution cycles at N=128,
+// every mbarrier wait ~100 more.  Hence TWO issuing warps with independent operand rings:
+//   warp 9  (leader)  Gram stream   G ring: kGStages x 24 KiB (A chunk 16 KiB + B half chunk 8 KiB)
+//   warp 10 (leader)  PV stream     V ring: kVStages x 16 KiB (64 rows of Z_J x this CTA's half slice)
+// The two streams only meet through the S buffers, the P slots and TMEM; the tensor pipe interleaves
+// them in arrival order, so no static Gram/PV schedule (and no "lag") is needed.
+// TMA issue is latency-bound per thread as well (~650 cycles per wait/expect/issue round trip):
+// two producer warps alternate over the G stages, a third feeds the V ring.
+// Only the leader issues MMAs; the peer's epilogue arrives on the leader's s_empty, the peer's warp 9
+// forwards its p_full to the leader (p_pair), and every tcgen05.commit is multicast to both CTAs.
 #include "common.cuh"
 #include "ptx.cuh"
 #include "tc_epi.cuh"
 
 namespace vg {
 
-// Pipeline shape = template parameters <STAGES, SLOTS, LAG>: STAGES x 32 KiB operand ring, SLOTS x 32 KiB
-// P tiles (STAGES + SLOTS <= 7 fits the 227 KiB of shared memory), PV(t) issued LAG periods after
-// tile t's turn.  The exchange latency (epilogue + DSMEM copy) must fit inside LAG periods.
-constexpr int kQStageBytes = 2 * kChunkBytes;
+constexpr int kGStages = 4;                        // Gram operand ring
+constexpr int kGStageBytes = kChunkBytes + kChunkBytes / 2;   // 24 KiB
+constexpr int kGProducers = 2;                     // warps 8 and 11; stage s belongs to producer s % 2
+constexpr int kVStages = 2;                        // V ring: half tiles (64 rows of Z_J)
+constexpr int kVStageBytes = kChunkBytes;          // 2 boxes of [64 x 64] bf16
+constexpr int kQSlots = 3;                         // P tiles, 32 KiB each
 constexpr int kQPBytes = 2 * kChunkBytes;
-constexpr int kQThreads = 480;                     // 8 epilogue + MMA + norms + 4 TMA producer warps + P publisher
-constexpr int kQProducers = 4;                    // warps 8, 11, 12, 13
-constexpr int kQMaxStages = 6, kQMaxSlots = 6;
+constexpr int kQThreads = 480;   // warps: 0-7 epilogue, 8/11 G producers, 9 Gram MMA (peer: P forwarder),
+                                 // 10 PV MMA, 12 V producer, 13 norms, 14 P publisher
+static_assert(kGStages % kGProducers == 0, "each G producer warp owns fixed ring stages");
 
 struct __align__(8) PairBarriers {
-  uint64_t ring_full[kQMaxStages], ring_empty[kQMaxStages];
+  uint64_t g_full[kGStages], g_empty[kGStages];
+  uint64_t v_full[kVStages], v_empty[kVStages];
   uint64_t s_full[2], s_empty[2];
   uint64_t nj_full[2];
-  uint64_t p_full[kQMaxSlots], slot_free[kQMaxSlots], p_pair[kQMaxSlots], pub_full[kQMaxSlots];
+  uint64_t p_full[kQSlots], slot_free[kQSlots], p_pair[kQSlots], pub_full[kQSlots];
   uint64_t o_full;
   uint32_t tmem_base;
   float red[8][4];
-  long long ts_issue[kQMaxStages], ts_commit[kQMaxStages];   // debug timers (p.dbg)
 };
 
-constexpr int kQSmemRing = 0;
-__host__ __device__ constexpr int q_smem_total(int stages, int slots) {
-  return stages * kQStageBytes + slots * kQPBytes + 2 * kTile * 4 + static_cast<int>(sizeof(PairBarriers));
-}
+constexpr int kQSmemG = 0;
+constexpr int kQSmemV = kQSmemG + kGStages * kGStageBytes;
+constexpr int kQSmemP = kQSmemV + kVStages * kVStageBytes;
+constexpr int kQSmemNj = kQSmemP + kQSlots * kQPBytes;
+constexpr int kQSmemBar = kQSmemNj + 2 * kTile * 4;
+constexpr int kQSmemTotal = kQSmemBar + static_cast<int>(sizeof(PairBarriers));
+static_assert(kQSmemTotal <= 232448, "shared memory budget");
+static_assert(kQSmemV % 1024 == 0 && kQSmemP % 1024 == 0, "operand tiles need 1024-byte alignment");
 
-template <bool LADDER, int STAGES, int SLOTS, int LAG>
+template <bool LADDER>
 __global__ void __launch_bounds__(kQThreads, 1)
 mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__ CUtensorMap zmap64,
                     const TcParams p) {
-  constexpr int kQStages = STAGES, kQSlots = SLOTS, kQLag = LAG;
-  constexpr int kQSmemP = kQSmemRing + kQStages * kQStageBytes;
-  constexpr int kQSmemNj = kQSmemP + kQSlots * kQPBytes;
-  constexpr int kQSmemBar = kQSmemNj + 2 * kTile * 4;
-  static_assert(q_smem_total(STAGES, SLOTS) <= 232448, "shared memory budget");
-  static_assert(STAGES % kQProducers == 0, "each producer warp owns fixed ring stages");
   extern __shared__ __align__(1024) uint8_t smem[];
   if ((smem_u32(smem) & 1023u) != 0) __trap();
   PairBarriers* bar = reinterpret_cast<PairBarriers*>(smem + kQSmemBar);
@@ -79,14 +86,17 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
   const int K = (T + CS - 1) / CS;                     // Gram tiles per CTA (the tail is padded)
   const int TT = K * CS;                               // padded tile count; tiles >= T carry P = 0
   const int slice_chunks = max(0, min(p.slice_chunks, p.kchunks - slice * p.slice_chunks));
-  const int pv_stages = slice_chunks > 0 ? 1 : 0;     // one stage per tile: this CTA's half of the slice
   const int my_chunks = slice_chunks >> 1;             // 64-feature chunks of the slice held by this CTA
+  const uint32_t pbytes = (p.dbg_flags & 1) ? 16u : static_cast<uint32_t>(kQPBytes);   // bit 0: measurement only
 
-  const uint32_t pbytes = (p.dbg_flags & 1) ? 16u : static_cast<uint32_t>(kQPBytes);
   if (threadIdx.x == 0) {
-    for (int s = 0; s < kQStages; ++s) {
-      mbar_init(&bar->ring_full[s], 1);
-      mbar_init(&bar->ring_empty[s], 1);
+    for (int s = 0; s < kGStages; ++s) {
+      mbar_init(&bar->g_full[s], 1);
+      mbar_init(&bar->g_empty[s], 1);
+    }
+    for (int s = 0; s < kVStages; ++s) {
+      mbar_init(&bar->v_full[s], 1);
+      mbar_init(&bar->v_empty[s], 1);
     }
     for (int b = 0; b < 2; ++b) {
       mbar_init(&bar->s_full[b], 1);
@@ -102,7 +112,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     mbar_init(&bar->o_full, 1);
     fence_barrier_init();
     // P tiles written by a peer land by bulk copy: the RECEIVER arms its own barrier (no remote arrive);
-    // the first kQSlots tiles here, tile t + kQSlots right after the wait for tile t (warp 9)
+    // the first kQSlots tiles here, tile t + kQSlots right after the wait for tile t (warps 9 / 10)
     for (int t = 0; t < kQSlots && t < TT; ++t)
       if (t % CS != c) mbar_arrive_expect_tx(&bar->p_full[t % kQSlots], pbytes);
   }
@@ -110,93 +120,62 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     tmem_alloc_2cta(&bar->tmem_base, 512);
     tmem_relinquish_2cta();
   }
-  if (warp == 8 && lane == 0) tma_prefetch_desc(&zmap);
+  if (warp == 8 && lane == 0) {
+    tma_prefetch_desc(&zmap);
+    tma_prefetch_desc(&zmap64);
+  }
   tc_fence_before();
   cluster_sync_all();          // peers' barriers are initialised before any remote arrive / copy
   tc_fence_after();
   const uint32_t tmem = bar->tmem_base;
   const uint32_t tmem_o = tmem + 256;
 
-  if (warp == 8 || (warp >= 11 && warp <= 13)) {
-    // ===================== TMA producers (mirror the MMA stream order exactly) =====================
-    // One thread issuing wait -> expect_tx -> 2 loads per stage sustains only ~1 stage / 800 cycles
-    // (tools/gpu_tma_rate.py: the loop is latency-bound, not L2-bound), three times slower than the MMAs
-    // drain a Gram stage.  kQProducers warps therefore walk the same stage sequence and each issues every
-    // kQProducers-th stage; within a stage the two boxes are issued by two lanes.
-    const int pj = warp == 8 ? 0 : warp - 10;            // producer index 0..kQProducers-1
+  if (warp == 8 || warp == 11) {
+    // ===================== G producers: Gram operand stages, in the Gram warp's order =====================
+    const int pj = warp == 8 ? 0 : 1;
     uint32_t s = 0, ph = 0;
-    int r = 0;                                           // stage-use counter modulo kQProducers
-    long long pw_empty = 0, rel_sum = 0;
-    int rel_n = 0, n_use = 0;
-    auto advance = [&]() {
-      ++n_use;
-      if (++r == kQProducers) r = 0;
-      if (++s == kQStages) { s = 0; ph ^= 1; }
-    };
-    auto gram_stages = [&](int k, int kc0, int kc1) {
+    for (int k = 0; k < K; ++k) {
       const int jt = min(CS * k + c, T - 1);
-      for (int kc = kc0; kc < kc1; ++kc) {
-        if (r == pj) {
-          const long long tw0 = clock64();
-          mbar_wait(&bar->ring_empty[s], ph ^ 1);
-          if (p.dbg && lane == 0) {
-            const long long now = clock64();
-            pw_empty += now - tw0;
-            if (n_use >= kQStages) { rel_sum += now - *(volatile long long*)&bar->ts_commit[s]; ++rel_n; }
-            *(volatile long long*)&bar->ts_issue[s] = now;
-          }
-          uint8_t* dst = smem + kQSmemRing + s * kQStageBytes;
+      for (int kc = 0; kc < p.kchunks; ++kc) {
+        if ((s & (kGProducers - 1)) == static_cast<uint32_t>(pj)) {
+          mbar_wait(&bar->g_empty[s], ph ^ 1);
+          uint8_t* dst = smem + kQSmemG + s * kGStageBytes;
           if (p.dbg_flags & 2) {            // measurement only: no operand loads
-            if (lane == 0 && hh == 0) mbar_arrive(&bar->ring_full[s]);
+            if (lane == 0 && hh == 0) mbar_arrive(&bar->g_full[s]);
           } else if (lane == 0) {
-            if (hh == 0) mbar_arrive_expect_tx(&bar->ring_full[s], 2 * (kChunkBytes + kChunkBytes / 2));
-            tma_load_2d_2cta(dst, &zmap, &bar->ring_full[s], kc * kChunk, ti * kTile);
+            if (hh == 0) mbar_arrive_expect_tx(&bar->g_full[s], 2 * kGStageBytes);
+            tma_load_2d_2cta(dst, &zmap, &bar->g_full[s], kc * kChunk, ti * kTile);
           } else if (lane == 1) {
-            tma_load_2d_2cta(dst + kChunkBytes, &zmap64, &bar->ring_full[s], kc * kChunk, jt * kTile + 64 * hh);
+            tma_load_2d_2cta(dst + kChunkBytes, &zmap64, &bar->g_full[s], kc * kChunk, jt * kTile + 64 * hh);
           }
           __syncwarp();
         }
-        advance();
+        if (++s == kGStages) { s = 0; ph ^= 1; }
       }
-    };
-    auto pv_stages_load = [&](int t) {
-      const int jt = min(t, T - 1);
-      for (int h = 0; h < pv_stages; ++h) {
-        if (r == pj) {
-          const long long tw0 = clock64();
-          mbar_wait(&bar->ring_empty[s], ph ^ 1);
-          if (p.dbg && lane == 0) {
-            const long long now = clock64();
-            pw_empty += now - tw0;
-            if (n_use >= kQStages) { rel_sum += now - *(volatile long long*)&bar->ts_commit[s]; ++rel_n; }
-            *(volatile long long*)&bar->ts_issue[s] = now;
-          }
-          uint8_t* dst = smem + kQSmemRing + s * kQStageBytes;
+    }
+  } else if (warp == 12) {
+    // ===================== V producer: half tiles of Z_J[:, this CTA's half of the slice] =====================
+    if (my_chunks > 0) {
+      uint32_t s = 0, ph = 0;
+      for (int t = 0; t < TT; ++t) {
+        const int jt = min(t, T - 1);
+        for (int h = 0; h < 2; ++h) {
+          mbar_wait(&bar->v_empty[s], ph ^ 1);
+          uint8_t* dst = smem + kQSmemV + s * kVStageBytes;
           if (p.dbg_flags & 4) {            // measurement only: no V loads
-            if (lane == 0 && hh == 0) mbar_arrive(&bar->ring_full[s]);
-          } else if (lane == 0 && hh == 0) mbar_arrive_expect_tx(&bar->ring_full[s], slice_chunks * kChunkBytes);
-          if (!(p.dbg_flags & 4) && lane < my_chunks)
-            tma_load_2d_2cta(dst + lane * kChunkBytes, &zmap, &bar->ring_full[s],
-                             (slice * p.slice_chunks + hh * my_chunks + lane) * kChunk, jt * kTile);
+            if (lane == 0 && hh == 0) mbar_arrive(&bar->v_full[s]);
+          } else {
+            if (lane == 0 && hh == 0) mbar_arrive_expect_tx(&bar->v_full[s], slice_chunks * (kChunkBytes / 2));
+            if (lane < my_chunks)
+              tma_load_2d_2cta(dst + lane * (kChunkBytes / 2), &zmap64, &bar->v_full[s],
+                               (slice * p.slice_chunks + hh * my_chunks + lane) * kChunk, jt * kTile + 64 * h);
+          }
           __syncwarp();
+          if (++s == kVStages) { s = 0; ph ^= 1; }
         }
-        advance();
       }
-    };
-    gram_stages(0, 0, p.kchunks);
-    for (int m = 0; m < TT + kQLag; ++m) {
-      const int kn = 1 + m / CS, q = m % CS;
-      if (kn < K) gram_stages(kn, (q * p.kchunks) / CS, ((q + 1) * p.kchunks) / CS);
-      const int tc = m - kQLag;
-      if (tc >= 0 && tc < TT) pv_stages_load(tc);
     }
-    if (p.dbg && lane == 0 && hh == 0) {
-      float* d = p.dbg + static_cast<int64_t>(blockIdx.x) * p.dbg_stride;
-      atomicAdd(&d[8], static_cast<float>(pw_empty));
-      atomicAdd(&d[9], static_cast<float>(rel_sum));
-      atomicAdd(&d[10], static_cast<float>(rel_n));
-    }
-  } else if (warp == 10) {
+  } else if (warp == 13) {
     // ===================== bulk-copy producer: scaled column norms of this CTA's tiles ============
     if (lane == 0) {
       for (int k = 0; k < K; ++k) {
@@ -214,20 +193,39 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     // pub_full[slot] counts only this CTA's own tiles (waiting on p_full would alias: it advances through
     // the peers' tiles in between, and a parity wait cannot tell phases two apart)
     uint32_t pub_mask = 0;
+    uint16_t peers = 0;                                   // the other slices of MY row tile
+    for (int d = 0; d < CS; ++d)
+      if (d != c) peers |= static_cast<uint16_t>(1u << (2 * d + hh));
+    const uint32_t smid = sm_id();
+    if (smid >= static_cast<uint32_t>(kXchgSms)) __trap();
+    uint8_t* xbase = p.xchg + static_cast<size_t>(smid) * kXchgBytesPerSm;
     for (int k = 0; k < K; ++k) {
       const int t = CS * k + c;
       const int slot = t % kQSlots;
       mbar_wait(&bar->pub_full[slot], (pub_mask >> slot) & 1);
       pub_mask ^= 1u << slot;
-      if (lane < CS && lane != c) {
-        const uint32_t peer = static_cast<uint32_t>(2 * lane + hh);
+      if (lane == 0 && peers) {
         const uint32_t src = smem_u32(smem + kQSmemP + slot * kQPBytes);
-        bulk_copy_to_peer(mapa_u32(src, peer), src, pbytes, mapa_u32(smem_u32(&bar->p_full[slot]), peer));
+        if (p.dbg_flags & 8) {
+          // DSMEM route: one bulk copy per peer (~12 B/clk per SM: 3 x 32 KiB take ~8000 cycles)
+          for (int d = 0; d < CS; ++d)
+            if (d != c) {
+              const uint32_t peer = static_cast<uint32_t>(2 * d + hh);
+              bulk_copy_to_peer(mapa_u32(src, peer), src, pbytes, mapa_u32(smem_u32(&bar->p_full[slot]), peer));
+            }
+        } else {
+          // L2 route: bulk store to this SM's scratch slot, then ONE multicast bulk load into the same slot of
+          // every peer.  The scratch slot is free for the same reason the shared-memory slot is (slot_free).
+          uint8_t* g = xbase + slot * kQPBytes;
+          bulk_store_global(g, src, pbytes);
+          bulk_commit_wait_all();
+          bulk_load_multicast(src, g, pbytes, smem_u32(&bar->p_full[slot]), peers);
+        }
       }
       __syncwarp();
     }
   } else if (warp == 9 && hh == 1) {
-    // ===================== peer CTA: forward "my P tile t is in place" to the leader's MMA warp =========
+    // ===================== peer CTA: forward "my P tile t is in place" to the leader's PV warp =========
     uint32_t pf_mask = 0;
     const uint32_t pp0 = mapa_u32(smem_u32(&bar->p_pair[0]), static_cast<uint32_t>(rank - 1));
     for (int t = 0; t < TT; ++t) {
@@ -241,36 +239,30 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
       __syncwarp();
     }
   } else if (warp == 9) {
-    // ===================== leader CTA: MMA issuer for the pair (warp-uniform; one lane issues) ==========
+    // ===================== leader CTA: Gram MMA stream (warp-uniform; one lane issues) ==========
     constexpr uint32_t idesc_gram = make_idesc_bf16(2 * kTile, kTile, 0, 0);
     constexpr uint32_t desc_hi = (1024u >> 4) | (1u << 14) | (2u << 29);
-    constexpr uint32_t lbo_v = (static_cast<uint32_t>(kChunkBytes) >> 4) << 16;
-    const uint32_t idesc_pv = make_idesc_bf16(2 * kTile, slice_chunks * kChunk, 0, 1);
-    const uint32_t ring_lo = (smem_u32(smem + kQSmemRing) & 0x3FFFFu) >> 4;
-    const uint32_t p_lo0 = (smem_u32(smem + kQSmemP) & 0x3FFFFu) >> 4;
-    uint32_t s = 0, ph = 0, pf_mask = 0;
-    long long t_pf = 0, t_ring = 0, t_se = 0, t_ring_pv = 0, lat_g = 0, lat_p = 0;
-    int lat_gn = 0, lat_pn = 0;
+    const uint32_t g_lo = (smem_u32(smem + kQSmemG) & 0x3FFFFu) >> 4;
+    uint32_t s = 0, ph = 0;
+    long long t_ring = 0, t_se = 0;
     const long long t_begin = clock64();
-    auto gram = [&](int k, int kc0, int kc1) {
+    for (int k = 0; k < K; ++k) {
       const int b = k & 1;
       const uint32_t d_tmem = tmem + b * kTile;
-      for (int kc = kc0; kc < kc1; ++kc) {
-        if (kc == 0) {
-          const long long t0 = clock64();
-          mbar_wait(&bar->s_empty[b], ((k >> 1) & 1) ^ 1);     // both CTAs' epilogues released S[b]
-          t_se += clock64() - t0;
-          tc_fence_after();
-        }
+      {
+        const long long t0 = clock64();
+        mbar_wait(&bar->s_empty[b], ((k >> 1) & 1) ^ 1);     // both CTAs' epilogues released S[b]
+        t_se += clock64() - t0;
+      }
+      tc_fence_after();
+      for (int kc = 0; kc < p.kchunks; ++kc) {
         {
           const long long t0 = clock64();
-          mbar_wait(&bar->ring_full[s], ph);
-          const long long now = clock64();
-          t_ring += now - t0;
-          if (p.dbg && now - t0 > 100) { lat_g += now - *(volatile long long*)&bar->ts_issue[s]; ++lat_gn; }
+          mbar_wait(&bar->g_full[s], ph);
+          t_ring += clock64() - t0;
         }
         tc_fence_after();
-        const uint32_t a_lo = ring_lo + s * (kQStageBytes >> 4);
+        const uint32_t a_lo = g_lo + s * (kGStageBytes >> 4);
         const uint32_t b_lo = a_lo + (kChunkBytes >> 4);
         if (elect_one()) {
 #pragma unroll
@@ -279,76 +271,77 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
             const uint64_t bdesc = (static_cast<uint64_t>(desc_hi) << 32) | (b_lo + kk * 2);
             umma_bf16_ss_2cta(d_tmem, adesc, bdesc, idesc_gram, (kc | kk) != 0);
           }
-          umma_commit_2cta_mc(&bar->ring_empty[s], pair_mask);
-          if (p.dbg) *(volatile long long*)&bar->ts_commit[s] = clock64();
+          umma_commit_2cta_mc(&bar->g_empty[s], pair_mask);
           if (kc == p.kchunks - 1) umma_commit_2cta_mc(&bar->s_full[b], pair_mask);
         }
         __syncwarp();
-        if (++s == kQStages) { s = 0; ph ^= 1; }
+        if (++s == kGStages) { s = 0; ph ^= 1; }
       }
-    };
-    auto pv = [&](int t) {
+    }
+    if (p.dbg && lane == 0) {
+      float* d = p.dbg + static_cast<int64_t>(blockIdx.x) * p.dbg_stride;
+      d[0] = static_cast<float>(clock64() - t_begin);
+      d[2] = static_cast<float>(t_ring);
+      d[3] = static_cast<float>(t_se);
+    }
+  } else if (warp == 10 && hh == 0) {
+    // ===================== leader CTA: PV MMA stream =====================
+    constexpr uint32_t desc_hi = (1024u >> 4) | (1u << 14) | (2u << 29);
+    constexpr uint32_t lbo_v = (static_cast<uint32_t>(kChunkBytes / 2) >> 4) << 16;   // next 64-feature block
+    const uint32_t idesc_pv = make_idesc_bf16(2 * kTile, slice_chunks * kChunk, 0, 1);
+    const uint32_t v_lo0 = (smem_u32(smem + kQSmemV) & 0x3FFFFu) >> 4;
+    const uint32_t p_lo0 = (smem_u32(smem + kQSmemP) & 0x3FFFFu) >> 4;
+    uint32_t s = 0, ph = 0, pf_mask = 0;
+    long long t_pf = 0, t_v = 0;
+    const long long t_begin = clock64();
+    for (int t = 0; t < TT; ++t) {
       const int slot = t % kQSlots;
       {
         const long long t0 = clock64();
         mbar_wait(&bar->p_full[slot], (pf_mask >> slot) & 1);   // my P(I0, t)
         if (lane == 0 && t + kQSlots < TT && (t + kQSlots) % CS != c)
-          mbar_arrive_expect_tx(&bar->p_full[slot], pbytes);  // arm the slot for its next (remote) tile
+          mbar_arrive_expect_tx(&bar->p_full[slot], pbytes);    // arm the slot for its next (remote) tile
         mbar_wait(&bar->p_pair[slot], (pf_mask >> slot) & 1);   // the peer's P(I1, t)
         t_pf += clock64() - t0;
       }
       pf_mask ^= 1u << slot;
       tc_fence_after();
       const uint32_t p_lo = p_lo0 + slot * (kQPBytes >> 4);
-      if (pv_stages) {
-        {
-          const long long t0 = clock64();
-          mbar_wait(&bar->ring_full[s], ph);
-          const long long now = clock64();
-          t_ring_pv += now - t0;
-          if (p.dbg && now - t0 > 100) { lat_p += now - *(volatile long long*)&bar->ts_issue[s]; ++lat_pn; }
-        }
-        tc_fence_after();
-        const uint32_t v_lo = ring_lo + s * (kQStageBytes >> 4);
-        if (elect_one()) {
-#pragma unroll
-          for (int kk = 0; kk < kTile / 16; ++kk) {
-            const uint64_t adesc = (static_cast<uint64_t>(desc_hi) << 32) |
-                                   (p_lo + (kk >> 2) * (kChunkBytes >> 4) + (kk & 3) * 2);
-            const uint64_t bdesc = (static_cast<uint64_t>(desc_hi) << 32) | (v_lo + kk * (2048 >> 4)) | lbo_v;
-            umma_bf16_ss_2cta(tmem_o, adesc, bdesc, idesc_pv, (t | kk) != 0);
+      if (my_chunks > 0) {
+        for (int h = 0; h < 2; ++h) {
+          {
+            const long long t0 = clock64();
+            mbar_wait(&bar->v_full[s], ph);
+            t_v += clock64() - t0;
           }
-          umma_commit_2cta_mc(&bar->ring_empty[s], pair_mask);
-          if (p.dbg) *(volatile long long*)&bar->ts_commit[s] = clock64();
+          tc_fence_after();
+          const uint32_t v_lo = v_lo0 + s * (kVStageBytes >> 4);
+          const uint32_t pa_lo = p_lo + h * (kChunkBytes >> 4);
+          if (elect_one()) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const uint64_t adesc = (static_cast<uint64_t>(desc_hi) << 32) | (pa_lo + j * 2);
+              const uint64_t bdesc = (static_cast<uint64_t>(desc_hi) << 32) | (v_lo + j * (2048 >> 4)) | lbo_v;
+              umma_bf16_ss_2cta(tmem_o, adesc, bdesc, idesc_pv, (t | h | j) != 0);
+            }
+            umma_commit_2cta_mc(&bar->v_empty[s], pair_mask);
+          }
+          __syncwarp();
+          if (++s == kVStages) { s = 0; ph ^= 1; }
         }
-        __syncwarp();
-        if (++s == kQStages) { s = 0; ph ^= 1; }
       }
       // both CTAs of the pair are done with slot: tell the two writers (rows I0 and I1) of tile t + kQSlots
       if (t + kQSlots < TT && elect_one())
         umma_commit_2cta_mc(&bar->slot_free[slot], static_cast<uint16_t>(3u << (2 * ((t + kQSlots) % CS))));
       __syncwarp();
-    };
-    gram(0, 0, p.kchunks);
-    for (int m = 0; m < TT + kQLag; ++m) {
-      const int kn = 1 + m / CS, q = m % CS;
-      if (kn < K) gram(kn, (q * p.kchunks) / CS, ((q + 1) * p.kchunks) / CS);
-      const int tc = m - kQLag;
-      if (tc >= 0 && tc < TT) pv(tc);
     }
     if (elect_one()) umma_commit_2cta_mc(&bar->o_full, pair_mask);
     __syncwarp();
     if (p.dbg && lane == 0) {
       float* d = p.dbg + static_cast<int64_t>(blockIdx.x) * p.dbg_stride;
-      d[0] = static_cast<float>(clock64() - t_begin);
+      d[8] = static_cast<float>(clock64() - t_begin);
       d[1] = static_cast<float>(t_pf);
-      d[2] = static_cast<float>(t_ring);
-      d[3] = static_cast<float>(t_se);
-      d[11] = static_cast<float>(t_ring_pv);
-      d[12] = static_cast<float>(lat_g);
-      d[13] = static_cast<float>(lat_gn);
-      d[14] = static_cast<float>(lat_p);
-      d[15] = static_cast<float>(lat_pn);
+      d[9] = static_cast<float>(t_v);
     }
   } else if (warp < 8) {
     // ===================== epilogue warps: this CTA's own column tiles =====================
@@ -470,17 +463,19 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
   if (warp == 11) tmem_dealloc_2cta(tmem, 512);
 }
 
-template <int STAGES, int SLOTS, int LAG>
-static int launch_pair_variant(const TcParams& p, const CUtensorMap& map, const CUtensorMap& map64, int ladder,
-                               cudaStream_t st) {
+
+int g_pair_variant = 0;   // tuning/measurement: vgan_b200_debug_variant() (bits >= 8 -> TcParams::dbg_flags)
+
+int launch_tc_pair(const TcParams& p, const CUtensorMap& map, const CUtensorMap& map64, int ladder,
+                   cudaStream_t st) {
   const int ngrad = (p.gx_end - p.gx_begin) + (p.gy_end - p.gy_begin);
-  auto kern = ladder ? mmd2_tc_pair_kernel<true, STAGES, SLOTS, LAG> : mmd2_tc_pair_kernel<false, STAGES, SLOTS, LAG>;
-  constexpr int smem = q_smem_total(STAGES, SLOTS);
-  VG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  if (ngrad <= 0) return VGAN_B200_OK;
+  auto kern = ladder ? mmd2_tc_pair_kernel<true> : mmd2_tc_pair_kernel<false>;
+  VG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kQSmemTotal));
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(static_cast<unsigned>(((ngrad + 1) / 2) * p.ngroups * 2 * p.cs));
   cfg.blockDim = dim3(kQThreads);
-  cfg.dynamicSmemBytes = smem;
+  cfg.dynamicSmemBytes = kQSmemTotal;
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -491,20 +486,6 @@ static int launch_pair_variant(const TcParams& p, const CUtensorMap& map, const 
   cfg.numAttrs = 1;
   VG_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, map, map64, p));
   return VGAN_B200_OK;
-}
-
-int g_pair_variant = 0;   // debug/tuning: vgan_b200_debug_variant()
-
-int launch_tc_pair(const TcParams& p, const CUtensorMap& map, const CUtensorMap& map64, int ladder,
-                   cudaStream_t st) {
-  const int ngrad = (p.gx_end - p.gx_begin) + (p.gy_end - p.gy_begin);
-  if (ngrad <= 0) return VGAN_B200_OK;
-  // STAGES must be a multiple of kQProducers (each producer warp owns fixed ring stages)
-  switch (g_pair_variant & 255) {
-    case 1: return launch_pair_variant<4, 3, 2>(p, map, map64, ladder, st);
-    case 2: return launch_pair_variant<4, 3, 3>(p, map, map64, ladder, st);
-    default: return launch_pair_variant<4, 3, 1>(p, map, map64, ladder, st);
-  }
 }
 
 }  // namespace vg

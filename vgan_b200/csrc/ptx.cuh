@@ -176,6 +176,30 @@ __device__ __forceinline__ void bulk_copy_to_peer(uint32_t dst_cluster_addr, uin
       ::"r"(dst_cluster_addr), "r"(src_cta_addr), "r"(bytes), "r"(cluster_bar_addr)
       : "memory");
 }
+// bulk store own shared memory -> global (bulk async-group completion)
+__device__ __forceinline__ void bulk_store_global(void* gdst, uint32_t src_cta_addr, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+               ::"l"(reinterpret_cast<uint64_t>(gdst)), "r"(src_cta_addr), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit_wait_all() {   // writes of all prior bulk stores are complete
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+  asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+// bulk load global -> the same shared-memory offset of every CTA in cta_mask; complete_tx on the mbarrier at
+// the same offset in each of them
+__device__ __forceinline__ void bulk_load_multicast(uint32_t dst_addr, const void* gsrc, uint32_t bytes,
+                                                    uint32_t bar_addr, uint16_t cta_mask) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1], %2, [%3], %4;"
+      ::"r"(dst_addr), "l"(reinterpret_cast<uint64_t>(gsrc)), "r"(bytes), "r"(bar_addr), "h"(cta_mask)
+      : "memory");
+}
+__device__ __forceinline__ uint32_t sm_id() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%smid;" : "=r"(r));
+  return r;
+}
 __device__ __forceinline__ void st_cluster_f32(uint32_t cluster_addr, float v) {
   asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(cluster_addr), "f"(v) : "memory");
 }
