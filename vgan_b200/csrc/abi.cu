@@ -1,6 +1,7 @@
 // C ABI of vgan_b200 (include/vgan_b200.h): argument checking, workspace layout, TMA
 // descriptor creation and kernel launches.  No torch types, no host synchronisation.
 #include <cstdarg>
+#include <cstdlib>
 #include <cstring>
 
 #include "common.cuh"
@@ -258,14 +259,37 @@ int vgan_b200_mmd2_fwd_bwd(void* ws, int64_t Nx, int64_t Ny, int64_t D, int64_t 
     // the S_xx-only units (no gradient GEMM, one slice) stay on the plain kernel.
     // The S_xx units run concurrently on a side stream: clusters of 4 can only occupy 132 of the
     // 148 SMs (GPC granularity), and the S_xx work (~1/9 of the total) fills the stranded ones.
-    static cudaStream_t side = nullptr;
-    static cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
-    if (p.n_xx_units > 0 && !side) {
-      VG_CUDA_CHECK(cudaStreamCreateWithFlags(&side, cudaStreamNonBlocking));
+    // Priorities: the cluster kernel runs on a high-priority internal stream, the S_xx kernel on a
+    // low-priority one, so that SMs freed by a finished cluster go to the next cluster and not to pending
+    // S_xx CTAs (which would fragment the GPC and keep the next 8-CTA cluster from launching).
+    static cudaStream_t side = nullptr, hi = nullptr;
+    static cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_join_hi = nullptr;
+    static const int xx_mode = getenv("VGAN_B200_XX_MODE") ? atoi(getenv("VGAN_B200_XX_MODE")) : 0;   // 1: serial (measurement)
+    const bool overlap = p.n_xx_units > 0 && xx_mode != 1;
+    if (overlap && !side) {
+      int lo_pri = 0, hi_pri = 0;
+      VG_CUDA_CHECK(cudaDeviceGetStreamPriorityRange(&lo_pri, &hi_pri));
+      VG_CUDA_CHECK(cudaStreamCreateWithPriority(&side, cudaStreamNonBlocking, lo_pri));
+      VG_CUDA_CHECK(cudaStreamCreateWithPriority(&hi, cudaStreamNonBlocking, hi_pri));
       VG_CUDA_CHECK(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
       VG_CUDA_CHECK(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
+      VG_CUDA_CHECK(cudaEventCreateWithFlags(&ev_join_hi, cudaEventDisableTiming));
     }
-    if (p.n_xx_units > 0) VG_CUDA_CHECK(cudaEventRecord(ev_fork, st));
+    cudaStream_t main_st = st;
+    CUtensorMap map256;
+    if (p.n_xx_units > 0)
+      if (int e = make_tmap_bf16_2d(&map256, p.zq, static_cast<uint64_t>(L.Nxp + L.Nyp), static_cast<uint64_t>(L.Dp),
+                                    256))
+        return e;
+    if (overlap) {
+      VG_CUDA_CHECK(cudaEventRecord(ev_fork, st));
+      VG_CUDA_CHECK(cudaStreamWaitEvent(hi, ev_fork, 0));
+      main_st = hi;
+      if (xx_mode == 2) {      // measurement: S_xx kernel dispatched first
+        VG_CUDA_CHECK(cudaStreamWaitEvent(side, ev_fork, 0));
+        if (int e = launch_xx(p, map, map256, ladder, side)) return e;
+      }
+    }
     // full 128/256-wide slices: CTA pairs (cta_group::2) halve the shared-memory operand traffic
     const bool pair_ok = (p.kchunks % 4 == 0 || p.kchunks % 4 == 2) && !(flags & VGAN_B200_NO_PAIR);
     if (pair_ok) {
@@ -273,19 +297,20 @@ int vgan_b200_mmd2_fwd_bwd(void* ws, int64_t Nx, int64_t Ny, int64_t D, int64_t 
       if (int e = make_tmap_bf16_2d(&map64, p.zq, static_cast<uint64_t>(L.Nxp + L.Nyp),
                                     static_cast<uint64_t>(L.Dp), 64))
         return e;
-      if (int e = launch_tc_pair(p, map, map64, ladder, st)) return e;
+      if (int e = launch_tc_pair(p, map, map64, ladder, main_st)) return e;
     } else {
-      if (int e = launch_tc_cluster(p, map, ladder, st)) return e;
+      if (int e = launch_tc_cluster(p, map, ladder, main_st)) return e;
     }
     if (p.n_xx_units == 0) return VGAN_B200_OK;
-    TcParams q = p;
-    q.gx_begin = q.gx_end = q.gy_begin = q.gy_end = 0;
-    q.pv = 0;
-    q.nslices = 1;
-    VG_CUDA_CHECK(cudaStreamWaitEvent(side, ev_fork, 0));
-    if (int e = launch_tc(q, map, ladder, side)) return e;
+    if (!overlap) return launch_xx(p, map, map256, ladder, st);
+    if (xx_mode != 2) {
+      VG_CUDA_CHECK(cudaStreamWaitEvent(side, ev_fork, 0));
+      if (int e = launch_xx(p, map, map256, ladder, side)) return e;
+    }
     VG_CUDA_CHECK(cudaEventRecord(ev_join, side));
+    VG_CUDA_CHECK(cudaEventRecord(ev_join_hi, hi));
     VG_CUDA_CHECK(cudaStreamWaitEvent(st, ev_join, 0));
+    VG_CUDA_CHECK(cudaStreamWaitEvent(st, ev_join_hi, 0));
     return VGAN_B200_OK;
   }
   return launch_tc(p, map, ladder, st);

@@ -70,6 +70,7 @@ int check_device();   // 0 when the current device is compute capability 10.x
 
 // kernels' host launchers (defined in their own .cu files)
 int launch_tc(const TcParams& p, const CUtensorMap& map, int ladder, cudaStream_t st);
+int launch_xx(const TcParams& p, const CUtensorMap& map, const CUtensorMap& map256, int ladder, cudaStream_t st);
 int launch_tc_cluster(const TcParams& p, const CUtensorMap& map, int ladder, cudaStream_t st);
 int launch_tc_pair(const TcParams& p, const CUtensorMap& map, const CUtensorMap& map64, int ladder, cudaStream_t st);
 int launch_probe(const CUtensorMap& mapA, const CUtensorMap& mapB, float* S_out, float* O_out,

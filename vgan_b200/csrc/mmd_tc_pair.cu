@@ -18,6 +18,8 @@
 // two producer warps alternate over the G stages, a third feeds the V ring.
 // Only the leader issues MMAs; the peer's epilogue arrives on the leader's s_empty, the peer's warp 9
 // forwards its p_full to the leader (p_pair), and every tcgen05.commit is multicast to both CTAs.
+#include <cstdlib>
+
 #include "common.cuh"
 #include "ptx.cuh"
 #include "tc_epi.cuh"
@@ -484,6 +486,12 @@ int launch_tc_pair(const TcParams& p, const CUtensorMap& map, const CUtensorMap&
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
+  if (getenv("VGAN_B200_VERBOSE")) {
+    int ncl = 0;
+    cudaOccupancyMaxActiveClusters(&ncl, kern, &cfg);
+    fprintf(stderr, "vgan_b200: pair kernel grid %u, cluster %u, max active clusters %d\n", cfg.gridDim.x,
+            attr[0].val.clusterDim.x, ncl);
+  }
   VG_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, map, map64, p));
   return VGAN_B200_OK;
 }
