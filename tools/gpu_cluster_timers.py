@@ -18,15 +18,12 @@ for it in range(2):
     k._freeze()
 L.vgan_b200_debug_tile_sums(None, 0)
 d = dbg[:units, :16].cpu().numpy()
-if not os.environ.get("VGAN_B200_NO_PAIR"):
-    d = d[256:]          # the S_xx side kernel writes its tile sums into the first rows of the same buffer
-    lead = d[d[:, 0] > 0]
-    R = 2 * N // 128 / 4
-    print("pair leaders, cycles per round (4 tiles):")
-    print("  Gram warp: total %.0f  wait_g_ring %.0f  wait_s_empty %.0f" % tuple(lead[:, i].mean() / R for i in (0, 2, 3)))
-    print("  PV warp:   total %.0f  wait_p %.0f  wait_v_ring %.0f" % tuple(lead[:, i].mean() / R for i in (8, 1, 9)))
-names = ["mma_total", "mma_wait_pfull", "mma_wait_ring", "mma_wait_sempty", "epi_wait_sfull", "epi_compute", "epi_wait_slot", "epi_publish"]
-tiles = 2 * N // 128
-print(f"N={N} tiles={tiles} rounds={tiles//4}; cycles per ROUND (4 tiles), mean over CTAs:")
-for i, n in enumerate(names):
-    print(f"  {n:18s} {d[:, i].mean() / (tiles / 4):10.0f}")
+d = dbg[:120, :16].cpu().numpy()      # persistent pair kernel: 15 clusters x 8 CTAs
+lead = d[0::2]
+peer = d[1::2]
+R = (N // 256) * (2 * N // 128 / 4) / 15.0     # rounds per cluster
+print(f"persistent pair kernel, cycles per round (4 tiles), {R:.0f} rounds per cluster:")
+print("  Gram warp: wait_g_ring %.0f  wait_s_empty %.0f   kernel total %.0f" % (lead[:, 0].mean() / R, lead[:, 1].mean() / R, lead[:, 12].mean() / R))
+print("  PV warp:   wait_p %.0f  wait_v_ring %.0f" % (lead[:, 10].mean() / R, lead[:, 11].mean() / R))
+print("  SM clock %.0f MHz ; tail (syncs + gradient rows) %.0f cycles per round" % (1e3 * lead[:, 12].mean() / lead[:, 13].mean(), d[:, 14].mean() / R))
+print("  epilogue:  wait_s_full %.0f  compute %.0f  wait_slot %.0f  park+sync %.0f" % tuple(d[:, i].mean() / R for i in (4, 5, 6, 7)))

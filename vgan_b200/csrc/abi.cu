@@ -297,6 +297,11 @@ int vgan_b200_mmd2_fwd_bwd(void* ws, int64_t Nx, int64_t Ny, int64_t D, int64_t 
       if (int e = make_tmap_bf16_2d(&map64, p.zq, static_cast<uint64_t>(L.Nxp + L.Nyp),
                                     static_cast<uint64_t>(L.Dp), 64))
         return e;
+      // stream-K cuts a unit between two clusters: those rows are accumulated with red.global.add
+      if (ye > row_begin)
+        VG_CUDA_CHECK(cudaMemsetAsync(dY, 0, static_cast<size_t>(ye - row_begin) * D * sizeof(float), main_st));
+      if (need_dx && xe > row_begin)
+        VG_CUDA_CHECK(cudaMemsetAsync(dX, 0, static_cast<size_t>(xe - row_begin) * D * sizeof(float), main_st));
       if (int e = launch_tc_pair(p, map, map64, ladder, main_st)) return e;
     } else {
       if (int e = launch_tc_cluster(p, map, ladder, main_st)) return e;

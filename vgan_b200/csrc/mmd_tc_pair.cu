@@ -16,6 +16,12 @@
 // them in arrival order, so no static Gram/PV schedule (and no "lag") is needed.
 // TMA issue is latency-bound per thread as well (~650 cycles per wait/expect/issue round trip):
 // two producer warps alternate over the G stages, a third feeds the V ring.
+// PERSISTENT, stream-K style: the grid is exactly the number of clusters that can be resident (15 on a
+// B200: 8-CTA clusters fit 120 of the 148 SMs); the work = (row-tile pair, slice group) units x K rounds of
+// CS column tiles is cut into equal contiguous ranges, so every cluster finishes at the same time whatever
+// the unit count (no wave quantisation, also on the small shards of a multi-GPU run), nothing is left
+// pending in the hardware queue (the S_xx kernel can then run on the 28 SMs clusters cannot use), and a
+// unit cut between two clusters accumulates its gradient rows with red.global.add (dY zeroed by the host).
 // Only the leader issues MMAs; the peer's epilogue arrives on the leader's s_empty, the peer's warp 9
 // forwards its p_full to the leader (p_pair), and every tcgen05.commit is multicast to both CTAs.
 #include <cstdlib>
@@ -33,8 +39,8 @@ constexpr int kVStages = 2;                        // V ring: half tiles (64 row
 constexpr int kVStageBytes = kChunkBytes;          // 2 boxes of [64 x 64] bf16
 constexpr int kQSlots = 3;                         // P tiles, 32 KiB each
 constexpr int kQPBytes = 2 * kChunkBytes;
-constexpr int kQThreads = 480;   // warps: 0-7 epilogue, 8/11 G producers, 9 Gram MMA (peer: P forwarder),
-                                 // 10 PV MMA, 12 V producer, 13 norms, 14 P publisher
+constexpr int kQThreads = 512;   // warps: 0-7 epilogue (192 registers), 8-15 service (64 registers): 8/11 G producers,
+                                 // 9 Gram MMA (peer: P forwarder), 10 PV MMA, 12 V producer, 13 P publisher, 14 norms
 static_assert(kGStages % kGProducers == 0, "each G producer warp owns fixed ring stages");
 
 struct __align__(8) PairBarriers {
@@ -57,6 +63,29 @@ constexpr int kQSmemTotal = kQSmemBar + static_cast<int>(sizeof(PairBarriers));
 static_assert(kQSmemTotal <= 232448, "shared memory budget");
 static_assert(kQSmemV % 1024 == 0 && kQSmemP % 1024 == 0, "operand tiles need 1024-byte alignment");
 
+#define VG_PAIR_DECODE_RANGE \
+    long long w_lo, w_hi; \
+    if (pi < n_full) { w_lo = (u_first + pi) * static_cast<long long>(K); w_hi = w_lo + K; } \
+    else if (pi == n_full && has_head) { w_lo = w_begin; w_hi = head_end; } \
+    else { w_lo = tail_begin; w_hi = w_end; } \
+    const int unit_g = static_cast<int>(w_lo / K); \
+    const int r0 = static_cast<int>(w_lo - static_cast<long long>(unit_g) * K); \
+    const int Kp = static_cast<int>(w_hi - w_lo); \
+ \
+    const bool partial = Kp < K; \
+    const int TTp = Kp * CS; \
+    const int tile0 = r0 * CS; \
+    const int grp = unit_g % p.ngroups; \
+    const int slice = grp * CS + c; \
+    int unit = 2 * (unit_g / p.ngroups) + hh; \
+    const bool dup = unit >= ngrad; \
+    if (dup) unit = ngrad - 1; \
+    const int row_is_x = unit < ngx; \
+    const int ti = row_is_x ? p.gx_begin + unit : p.tiles_x + p.gy_begin + (unit - ngx); \
+    const int slice_chunks = max(0, min(p.slice_chunks, p.kchunks - slice * p.slice_chunks)); \
+    const int my_chunks = slice_chunks >> 1; \
+    (void)0
+
 template <bool LADDER>
 __global__ void __launch_bounds__(kQThreads, 1)
 mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__ CUtensorMap zmap64,
@@ -73,22 +102,27 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
   const int c = rank >> 1;                             // pair index = slice within the group
   const int hh = rank & 1;                             // 0: leader (row tile I0), 1: peer (row tile I1)
   const int csz = 2 * CS;
-  const int grp = (blockIdx.x / csz) % p.ngroups;
-  const int slice = grp * CS + c;
-  // ---- unit decode: one cluster per PAIR of gradient row tiles
   const int ngx = p.gx_end - p.gx_begin;
   const int ngrad = ngx + (p.gy_end - p.gy_begin);
-  int unit = 2 * static_cast<int>(blockIdx.x / (csz * p.ngroups)) + hh;
-  const bool dup = unit >= ngrad;                      // odd tile count: the peer repeats I0, output dropped
-  if (dup) unit = ngrad - 1;
-  const int row_is_x = unit < ngx;
-  const int ti = row_is_x ? p.gx_begin + unit : p.tiles_x + p.gy_begin + (unit - ngx);
   const uint16_t pair_mask = static_cast<uint16_t>(3u << (2 * c));
   const int T = p.tiles_x + p.tiles_y;                 // column tiles
-  const int K = (T + CS - 1) / CS;                     // Gram tiles per CTA (the tail is padded)
-  const int TT = K * CS;                               // padded tile count; tiles >= T carry P = 0
-  const int slice_chunks = max(0, min(p.slice_chunks, p.kchunks - slice * p.slice_chunks));
-  const int my_chunks = slice_chunks >> 1;             // 64-feature chunks of the slice held by this CTA
+  const int K = (T + CS - 1) / CS;                     // rounds of CS column tiles per unit (the tail is padded)
+  // ---- stream-K partition: units x K rounds, equal contiguous ranges per cluster
+  const int n_units = ((ngrad + 1) / 2) * p.ngroups;   // (row-tile pair, slice group)
+  const long long W = static_cast<long long>(n_units) * K;
+  const int n_clusters = static_cast<int>(gridDim.x) / csz;
+  const int vc = static_cast<int>(blockIdx.x) / csz;
+  const long long w_begin = W * vc / n_clusters, w_end = W * (vc + 1) / n_clusters;
+  // Order of the ranges of this cluster: its FULL units first, every one swept from column round 0, so that all
+  // clusters walk the column operand in step (one HBM fetch per Z_J tile serves them all through L2: Z is
+  // twice the L2 at the bench shape); the cut units (head, tail) last.
+  const long long u_first = (w_begin + K - 1) / K, u_last = w_end / K;
+  const bool one_piece = u_first > u_last;              // the whole range lies inside one unit
+  const int n_full = one_piece ? 0 : static_cast<int>(u_last - u_first);
+  const long long head_end = one_piece ? w_end : u_first * K;
+  const long long tail_begin = one_piece ? w_end : u_last * K;
+  const bool has_head = head_end > w_begin;
+  const int n_parts = n_full + (has_head ? 1 : 0) + (w_end > tail_begin ? 1 : 0);
   const uint32_t pbytes = (p.dbg_flags & 1) ? 16u : static_cast<uint32_t>(kQPBytes);   // bit 0: measurement only
 
   if (threadIdx.x == 0) {
@@ -113,10 +147,6 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     }
     mbar_init(&bar->o_full, 1);
     fence_barrier_init();
-    // P tiles written by a peer land by bulk copy: the RECEIVER arms its own barrier (no remote arrive);
-    // the first kQSlots tiles here, tile t + kQSlots right after the wait for tile t (warps 9 / 10)
-    for (int t = 0; t < kQSlots && t < TT; ++t)
-      if (t % CS != c) mbar_arrive_expect_tx(&bar->p_full[t % kQSlots], pbytes);
   }
   if (warp == 11) {
     tmem_alloc_2cta(&bar->tmem_base, 512);
@@ -132,76 +162,91 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
   const uint32_t tmem = bar->tmem_base;
   const uint32_t tmem_o = tmem + 256;
 
+
+  // ---- pipeline state that persists across the work ranges of this CTA (each warp uses its role's part)
+  uint32_t rs = 0, rph = 0;            // ring stage / phase: G ring (warps 8, 11, 9), V ring (warps 12, 10)
+  uint32_t kg = 0;                     // Gram tiles of this CTA so far: S / norm buffer kg & 1, parity (kg >> 1) & 1
+  uint32_t pf_mask = 0, sf_mask = 0, pub_mask = 0;   // per-slot phase parities of p_full / slot_free / pub_full
+  uint32_t part = 0;                   // parity of o_full
+  long long tm0 = 0, tm1 = 0, tm2 = 0, tm3 = 0;      // debug timers (meaning depends on the role)
+  const long long t_begin = clock64();
+  unsigned long long gt_begin;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt_begin));
+  long long tm_tail = 0;
+  float* rsx = reinterpret_cast<float*>(smem + kQSmemP);       // [CS][128] row-sum exchange, reuses P slot 0
+
+  if (warp >= 8) {
+    // ===================== service warps (TMA, MMA issue, P exchange): few registers =====================
+    setmaxnreg_dec<64>();
+    for (int pi = 0; pi < n_parts; ++pi, ++part) {
+    VG_PAIR_DECODE_RANGE;
+    (void)partial; (void)dup; (void)row_is_x;
   if (warp == 8 || warp == 11) {
     // ===================== G producers: Gram operand stages, in the Gram warp's order =====================
-    const int pj = warp == 8 ? 0 : 1;
-    uint32_t s = 0, ph = 0;
-    for (int k = 0; k < K; ++k) {
-      const int jt = min(CS * k + c, T - 1);
+    const uint32_t pj = warp == 8 ? 0u : 1u;
+    for (int k = 0; k < Kp; ++k) {
+      const int jt = min(tile0 + CS * k + c, T - 1);
       for (int kc = 0; kc < p.kchunks; ++kc) {
-        if ((s & (kGProducers - 1)) == static_cast<uint32_t>(pj)) {
-          mbar_wait(&bar->g_empty[s], ph ^ 1);
-          uint8_t* dst = smem + kQSmemG + s * kGStageBytes;
+        if ((rs & (kGProducers - 1)) == pj) {
+          mbar_wait(&bar->g_empty[rs], rph ^ 1);
+          uint8_t* dst = smem + kQSmemG + rs * kGStageBytes;
           if (p.dbg_flags & 2) {            // measurement only: no operand loads
-            if (lane == 0 && hh == 0) mbar_arrive(&bar->g_full[s]);
+            if (lane == 0 && hh == 0) mbar_arrive(&bar->g_full[rs]);
           } else if (lane == 0) {
-            if (hh == 0) mbar_arrive_expect_tx(&bar->g_full[s], 2 * kGStageBytes);
-            tma_load_2d_2cta(dst, &zmap, &bar->g_full[s], kc * kChunk, ti * kTile);
+            if (hh == 0) mbar_arrive_expect_tx(&bar->g_full[rs], 2 * kGStageBytes);
+            tma_load_2d_2cta(dst, &zmap, &bar->g_full[rs], kc * kChunk, ti * kTile);
           } else if (lane == 1) {
-            tma_load_2d_2cta(dst + kChunkBytes, &zmap64, &bar->g_full[s], kc * kChunk, jt * kTile + 64 * hh);
+            tma_load_2d_2cta(dst + kChunkBytes, &zmap64, &bar->g_full[rs], kc * kChunk, jt * kTile + 64 * hh);
           }
           __syncwarp();
         }
-        if (++s == kGStages) { s = 0; ph ^= 1; }
+        if (++rs == kGStages) { rs = 0; rph ^= 1; }
       }
     }
   } else if (warp == 12) {
     // ===================== V producer: half tiles of Z_J[:, this CTA's half of the slice] =====================
     if (my_chunks > 0) {
-      uint32_t s = 0, ph = 0;
-      for (int t = 0; t < TT; ++t) {
-        const int jt = min(t, T - 1);
+      for (int t = 0; t < TTp; ++t) {
+        const int jt = min(tile0 + t, T - 1);
         for (int h = 0; h < 2; ++h) {
-          mbar_wait(&bar->v_empty[s], ph ^ 1);
-          uint8_t* dst = smem + kQSmemV + s * kVStageBytes;
+          mbar_wait(&bar->v_empty[rs], rph ^ 1);
+          uint8_t* dst = smem + kQSmemV + rs * kVStageBytes;
           if (p.dbg_flags & 4) {            // measurement only: no V loads
-            if (lane == 0 && hh == 0) mbar_arrive(&bar->v_full[s]);
+            if (lane == 0 && hh == 0) mbar_arrive(&bar->v_full[rs]);
           } else {
-            if (lane == 0 && hh == 0) mbar_arrive_expect_tx(&bar->v_full[s], slice_chunks * (kChunkBytes / 2));
+            if (lane == 0 && hh == 0) mbar_arrive_expect_tx(&bar->v_full[rs], slice_chunks * (kChunkBytes / 2));
             if (lane < my_chunks)
-              tma_load_2d_2cta(dst + lane * (kChunkBytes / 2), &zmap64, &bar->v_full[s],
+              tma_load_2d_2cta(dst + lane * (kChunkBytes / 2), &zmap64, &bar->v_full[rs],
                                (slice * p.slice_chunks + hh * my_chunks + lane) * kChunk, jt * kTile + 64 * h);
           }
           __syncwarp();
-          if (++s == kVStages) { s = 0; ph ^= 1; }
+          if (++rs == kVStages) { rs = 0; rph ^= 1; }
         }
       }
     }
-  } else if (warp == 13) {
+  } else if (warp == 14) {
     // ===================== bulk-copy producer: scaled column norms of this CTA's tiles ============
     if (lane == 0) {
-      for (int k = 0; k < K; ++k) {
-        const int jt = min(CS * k + c, T - 1);
-        const int b = k & 1;
-        mbar_wait(&bar->s_empty[b], ((k >> 1) & 1) ^ 1);
+      for (int k = 0; k < Kp; ++k, ++kg) {
+        const int jt = min(tile0 + CS * k + c, T - 1);
+        const uint32_t b = kg & 1;
+        mbar_wait(&bar->s_empty[b], ((kg >> 1) & 1) ^ 1);
         mbar_arrive_expect_tx(&bar->nj_full[b], kTile * 4);
         bulk_load_1d(nj_smem + b * kTile, p.nrms + static_cast<int64_t>(jt) * kTile, kTile * 4,
                      &bar->nj_full[b]);
       }
     }
-  } else if (warp == 14) {
-    // ===================== publisher: bulk-copies this CTA's P tiles to the other slices of its row tile =======
-    // (kept off the epilogue warps: the DSMEM copies of one tile take longer than the epilogue of the next)
-    // pub_full[slot] counts only this CTA's own tiles (waiting on p_full would alias: it advances through
-    // the peers' tiles in between, and a parity wait cannot tell phases two apart)
-    uint32_t pub_mask = 0;
+  } else if (warp == 13) {
+    // ===================== publisher: sends this CTA's P tiles to the other slices of its row tile =======
+    // (kept off the epilogue warps).  pub_full[slot] counts only this CTA's own tiles (waiting on p_full would
+    // alias: it advances through the peers' tiles in between, and a parity wait cannot tell phases two apart)
     uint16_t peers = 0;                                   // the other slices of MY row tile
     for (int d = 0; d < CS; ++d)
       if (d != c) peers |= static_cast<uint16_t>(1u << (2 * d + hh));
     const uint32_t smid = sm_id();
     if (smid >= static_cast<uint32_t>(kXchgSms)) __trap();
     uint8_t* xbase = p.xchg + static_cast<size_t>(smid) * kXchgBytesPerSm;
-    for (int k = 0; k < K; ++k) {
+    for (int k = 0; k < Kp; ++k) {
       const int t = CS * k + c;
       const int slot = t % kQSlots;
       mbar_wait(&bar->pub_full[slot], (pub_mask >> slot) & 1);
@@ -228,14 +273,18 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     }
   } else if (warp == 9 && hh == 1) {
     // ===================== peer CTA: forward "my P tile t is in place" to the leader's PV warp =========
-    uint32_t pf_mask = 0;
+    // P tiles written by another slice land by bulk copy: the RECEIVER arms its own barrier (no remote
+    // arrive): the first kQSlots tiles of the range here, tile t + kQSlots right after the wait for tile t
+    if (lane == 0)
+      for (int t = 0; t < kQSlots && t < TTp; ++t)
+        if (t % CS != c) mbar_arrive_expect_tx(&bar->p_full[t % kQSlots], pbytes);
     const uint32_t pp0 = mapa_u32(smem_u32(&bar->p_pair[0]), static_cast<uint32_t>(rank - 1));
-    for (int t = 0; t < TT; ++t) {
+    for (int t = 0; t < TTp; ++t) {
       const int slot = t % kQSlots;
       mbar_wait(&bar->p_full[slot], (pf_mask >> slot) & 1);
       pf_mask ^= 1u << slot;
       if (lane == 0) {
-        if (t + kQSlots < TT && (t + kQSlots) % CS != c) mbar_arrive_expect_tx(&bar->p_full[slot], pbytes);
+        if (t + kQSlots < TTp && (t + kQSlots) % CS != c) mbar_arrive_expect_tx(&bar->p_full[slot], pbytes);
         mbar_remote_arrive(pp0 + slot * 8);
       }
       __syncwarp();
@@ -245,26 +294,23 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     constexpr uint32_t idesc_gram = make_idesc_bf16(2 * kTile, kTile, 0, 0);
     constexpr uint32_t desc_hi = (1024u >> 4) | (1u << 14) | (2u << 29);
     const uint32_t g_lo = (smem_u32(smem + kQSmemG) & 0x3FFFFu) >> 4;
-    uint32_t s = 0, ph = 0;
-    long long t_ring = 0, t_se = 0;
-    const long long t_begin = clock64();
-    for (int k = 0; k < K; ++k) {
-      const int b = k & 1;
+    for (int k = 0; k < Kp; ++k, ++kg) {
+      const uint32_t b = kg & 1;
       const uint32_t d_tmem = tmem + b * kTile;
       {
         const long long t0 = clock64();
-        mbar_wait(&bar->s_empty[b], ((k >> 1) & 1) ^ 1);     // both CTAs' epilogues released S[b]
-        t_se += clock64() - t0;
+        mbar_wait(&bar->s_empty[b], ((kg >> 1) & 1) ^ 1);     // both CTAs' epilogues released S[b]
+        tm1 += clock64() - t0;
       }
       tc_fence_after();
       for (int kc = 0; kc < p.kchunks; ++kc) {
         {
           const long long t0 = clock64();
-          mbar_wait(&bar->g_full[s], ph);
-          t_ring += clock64() - t0;
+          mbar_wait(&bar->g_full[rs], rph);
+          tm0 += clock64() - t0;
         }
         tc_fence_after();
-        const uint32_t a_lo = g_lo + s * (kGStageBytes >> 4);
+        const uint32_t a_lo = g_lo + rs * (kGStageBytes >> 4);
         const uint32_t b_lo = a_lo + (kChunkBytes >> 4);
         if (elect_one()) {
 #pragma unroll
@@ -273,18 +319,12 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
             const uint64_t bdesc = (static_cast<uint64_t>(desc_hi) << 32) | (b_lo + kk * 2);
             umma_bf16_ss_2cta(d_tmem, adesc, bdesc, idesc_gram, (kc | kk) != 0);
           }
-          umma_commit_2cta_mc(&bar->g_empty[s], pair_mask);
+          umma_commit_2cta_mc(&bar->g_empty[rs], pair_mask);
           if (kc == p.kchunks - 1) umma_commit_2cta_mc(&bar->s_full[b], pair_mask);
         }
         __syncwarp();
-        if (++s == kGStages) { s = 0; ph ^= 1; }
+        if (++rs == kGStages) { rs = 0; rph ^= 1; }
       }
-    }
-    if (p.dbg && lane == 0) {
-      float* d = p.dbg + static_cast<int64_t>(blockIdx.x) * p.dbg_stride;
-      d[0] = static_cast<float>(clock64() - t_begin);
-      d[2] = static_cast<float>(t_ring);
-      d[3] = static_cast<float>(t_se);
     }
   } else if (warp == 10 && hh == 0) {
     // ===================== leader CTA: PV MMA stream =====================
@@ -293,18 +333,18 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     const uint32_t idesc_pv = make_idesc_bf16(2 * kTile, slice_chunks * kChunk, 0, 1);
     const uint32_t v_lo0 = (smem_u32(smem + kQSmemV) & 0x3FFFFu) >> 4;
     const uint32_t p_lo0 = (smem_u32(smem + kQSmemP) & 0x3FFFFu) >> 4;
-    uint32_t s = 0, ph = 0, pf_mask = 0;
-    long long t_pf = 0, t_v = 0;
-    const long long t_begin = clock64();
-    for (int t = 0; t < TT; ++t) {
+    if (lane == 0)                                       // arm the first remote tiles of the range (see warp 9, peer)
+      for (int t = 0; t < kQSlots && t < TTp; ++t)
+        if (t % CS != c) mbar_arrive_expect_tx(&bar->p_full[t % kQSlots], pbytes);
+    for (int t = 0; t < TTp; ++t) {
       const int slot = t % kQSlots;
       {
         const long long t0 = clock64();
         mbar_wait(&bar->p_full[slot], (pf_mask >> slot) & 1);   // my P(I0, t)
-        if (lane == 0 && t + kQSlots < TT && (t + kQSlots) % CS != c)
+        if (lane == 0 && t + kQSlots < TTp && (t + kQSlots) % CS != c)
           mbar_arrive_expect_tx(&bar->p_full[slot], pbytes);    // arm the slot for its next (remote) tile
         mbar_wait(&bar->p_pair[slot], (pf_mask >> slot) & 1);   // the peer's P(I1, t)
-        t_pf += clock64() - t0;
+        tm2 += clock64() - t0;
       }
       pf_mask ^= 1u << slot;
       tc_fence_after();
@@ -313,11 +353,11 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
         for (int h = 0; h < 2; ++h) {
           {
             const long long t0 = clock64();
-            mbar_wait(&bar->v_full[s], ph);
-            t_v += clock64() - t0;
+            mbar_wait(&bar->v_full[rs], rph);
+            tm3 += clock64() - t0;
           }
           tc_fence_after();
-          const uint32_t v_lo = v_lo0 + s * (kVStageBytes >> 4);
+          const uint32_t v_lo = v_lo0 + rs * (kVStageBytes >> 4);
           const uint32_t pa_lo = p_lo + h * (kChunkBytes >> 4);
           if (elect_one()) {
 #pragma unroll
@@ -326,26 +366,31 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
               const uint64_t bdesc = (static_cast<uint64_t>(desc_hi) << 32) | (v_lo + j * (2048 >> 4)) | lbo_v;
               umma_bf16_ss_2cta(tmem_o, adesc, bdesc, idesc_pv, (t | h | j) != 0);
             }
-            umma_commit_2cta_mc(&bar->v_empty[s], pair_mask);
+            umma_commit_2cta_mc(&bar->v_empty[rs], pair_mask);
           }
           __syncwarp();
-          if (++s == kVStages) { s = 0; ph ^= 1; }
+          if (++rs == kVStages) { rs = 0; rph ^= 1; }
         }
       }
       // both CTAs of the pair are done with slot: tell the two writers (rows I0 and I1) of tile t + kQSlots
-      if (t + kQSlots < TT && elect_one())
+      if (t + kQSlots < TTp && elect_one())
         umma_commit_2cta_mc(&bar->slot_free[slot], static_cast<uint16_t>(3u << (2 * ((t + kQSlots) % CS))));
       __syncwarp();
     }
     if (elect_one()) umma_commit_2cta_mc(&bar->o_full, pair_mask);
     __syncwarp();
-    if (p.dbg && lane == 0) {
-      float* d = p.dbg + static_cast<int64_t>(blockIdx.x) * p.dbg_stride;
-      d[8] = static_cast<float>(clock64() - t_begin);
-      d[1] = static_cast<float>(t_pf);
-      d[9] = static_cast<float>(t_v);
+  }
+    tc_fence_before();
+    cluster_sync_all();      // #1, #2, #3 of the epilogue warps below
+    cluster_sync_all();
+    cluster_sync_all();
     }
-  } else if (warp < 8) {
+  } else {
+    // ===================== epilogue warps: this CTA's own column tiles (register-hungry) =====================
+    setmaxnreg_inc<192>();
+    for (int pi = 0; pi < n_parts; ++pi, ++part) {
+    VG_PAIR_DECODE_RANGE;
+    {
     // ===================== epilogue warps: this CTA's own column tiles =====================
     const int q = warp & 3, g = warp >> 2;
     const int row = q * 32 + lane;
@@ -360,21 +405,20 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
       coef_y[m] = p.par[18 + m];
     }
     float acc_x = 0.f, acc_y = 0.f, rsum = 0.f;
-    uint32_t sf_mask = 0;
-    long long e_sfull = 0, e_comp = 0, e_slot = 0, e_pub = 0;
-    for (int k = 0; k < K; ++k) {
-      const int t = CS * k + c;
-      const bool valid = t < T;
-      const int jt = min(t, T - 1);
-      const int b = k & 1;
+    for (int k = 0; k < Kp; ++k, ++kg) {
+      const int t = CS * k + c;                          // tile index within the range (slot protocol)
+      const int tg = tile0 + t;                          // column tile
+      const bool valid = tg < T;
+      const int jt = min(tg, T - 1);
+      const uint32_t b = kg & 1;
       const bool col_is_x = jt < p.tiles_x;
       float cf[VGAN_B200_MAX_SCALES];
 #pragma unroll
       for (int m = 0; m < VGAN_B200_MAX_SCALES; ++m) cf[m] = valid ? (col_is_x ? coef_x[m] : coef_y[m]) : 0.f;
       long long tq = clock64();
-      mbar_wait(&bar->nj_full[b], (k >> 1) & 1);
-      mbar_wait(&bar->s_full[b], (k >> 1) & 1);
-      e_sfull += clock64() - tq; tq = clock64();
+      mbar_wait(&bar->nj_full[b], (kg >> 1) & 1);
+      mbar_wait(&bar->s_full[b], (kg >> 1) & 1);
+      tm0 += clock64() - tq; tq = clock64();
       tc_fence_after();
       const float* njp = nj_smem + b * kTile + g * 64;
       float ksum = 0.f;
@@ -392,14 +436,14 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
       mbar_arrive(&bar->s_empty[b]);          // S and the norms are free; P is parked in registers
       if (hh == 1) mbar_remote_arrive(mapa_u32(smem_u32(&bar->s_empty[b]), static_cast<uint32_t>(rank - 1)));
       if (valid) { if (col_is_x) acc_x += ksum; else acc_y += ksum; }
-      // ---- publish the P tile: own slot first, then a bulk copy into the same slot of every peer
+      // ---- park the P tile in its slot; the publisher warp sends it to the other slices of this row tile
       const int slot = t % kQSlots;
-      e_comp += clock64() - tq; tq = clock64();
+      tm1 += clock64() - tq; tq = clock64();
       if (t >= kQSlots) {
         mbar_wait(&bar->slot_free[slot], (sf_mask >> slot) & 1);   // every CTA finished PV(t - kQSlots)
         sf_mask ^= 1u << slot;
       }
-      e_slot += clock64() - tq; tq = clock64();
+      tm2 += clock64() - tq; tq = clock64();
       uint8_t* p_slot = smem + kQSmemP + slot * kQPBytes;
       uint8_t* p_row = p_slot + g * kChunkBytes + row * 128;
 #pragma unroll
@@ -408,17 +452,10 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
       fence_proxy_async_smem();
       asm volatile("bar.sync 1, 256;" ::: "memory");
       if (threadIdx.x == 0) {
-        mbar_arrive(&bar->p_full[slot]);     // own MMA warp
+        mbar_arrive(&bar->p_full[slot]);     // own PV warp / forwarder
         mbar_arrive(&bar->pub_full[slot]);   // publisher warp
       }
-      e_pub += clock64() - tq;
-    }
-    if (p.dbg && threadIdx.x == 0) {
-      float* d = p.dbg + static_cast<int64_t>(blockIdx.x) * p.dbg_stride;
-      d[4] = static_cast<float>(e_sfull);
-      d[5] = static_cast<float>(e_comp);
-      d[6] = static_cast<float>(e_slot);
-      d[7] = static_cast<float>(e_pub);
+      tm3 += clock64() - tq;
     }
     // ---- partial sums of this CTA's tiles
     acc_x = warp_sum(acc_x);
@@ -436,35 +473,54 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
         atomicAdd(&p.sums[2], sy);
       }
     }
-    mbar_wait(&bar->o_full, 0);      // every PV of this CTA has completed: its P slots are dead
+    mbar_wait(&bar->o_full, part & 1);   // every PV of this range has completed: its P slots are dead
     tc_fence_after();
+    }
+
+    // ===================== cluster-wide row sums of P, then the gradient rows of this range =====================
+    const long long tq_tail = clock64();
+    tc_fence_before();
+    cluster_sync_all();      // #1: no CTA of the cluster reads a P slot any more
+    if (warp < 4) {
+      const int row = warp * 32 + lane;
+      const float tot = nj_smem[row] + nj_smem[kTile + row];     // both column halves of this CTA's tiles
+      const uint32_t a = smem_u32(rsx + c * kTile + row);
+      for (int d = 0; d < CS; ++d) st_cluster_f32(mapa_u32(a, static_cast<uint32_t>(2 * d + hh)), tot);
+    }
+    cluster_sync_all();      // #2: all partial row sums have arrived
+    if (warp < 8) {
+      const int q = warp & 3, g = warp >> 2;
+      const int row = q * 32 + lane;
+      float rtot = 0.f;
+      for (int d = 0; d < CS; ++d) rtot += rsx[d * kTile + row];
+      tc_fence_after();
+      if (!dup)
+        write_grad_rows(p, tmem_o, static_cast<uint32_t>(q * 32) << 16, g, row, ti, row_is_x, slice, slice_chunks,
+                        rtot, partial);
+    }
+    tc_fence_before();
+    cluster_sync_all();      // #3: O, the norm buffers and P slot 0 may be reused by the next range
+    tm_tail += clock64() - tq_tail;
+    }
   }
 
-  // ===================== cluster-wide row sums of P, then the gradient rows =====================
-  float* rsx = reinterpret_cast<float*>(smem + kQSmemP);       // [CS][128], reuses P slot 0
-  tc_fence_before();
-  cluster_sync_all();      // #1: no CTA of the cluster reads a P slot any more
-  if (warp < 4) {
-    const int row = warp * 32 + lane;
-    const float tot = nj_smem[row] + nj_smem[kTile + row];     // both column halves of this CTA's tiles
-    const uint32_t a = smem_u32(rsx + c * kTile + row);
-    for (int d = 0; d < CS; ++d) st_cluster_f32(mapa_u32(a, static_cast<uint32_t>(2 * d + hh)), tot);
+  if (p.dbg && lane == 0 && (warp == 0 || ((warp == 9 || warp == 10) && hh == 0))) {
+    float* d = p.dbg + static_cast<int64_t>(blockIdx.x) * p.dbg_stride;
+    const int o = warp == 0 ? 4 : (warp == 9 ? 0 : 8);
+    d[o + 0] = static_cast<float>(tm0);
+    d[o + 1] = static_cast<float>(tm1);
+    d[o + 2] = static_cast<float>(tm2);
+    d[o + 3] = static_cast<float>(tm3);
+    if (warp == 9) {
+      d[12] = static_cast<float>(clock64() - t_begin);
+      unsigned long long gt_end;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt_end));
+      d[13] = static_cast<float>(gt_end - gt_begin);
+    }
+    if (warp == 0) d[14] = static_cast<float>(tm_tail);
   }
-  cluster_sync_all();      // #2: all partial row sums have arrived
-  if (warp < 8) {
-    const int q = warp & 3, g = warp >> 2;
-    const int row = q * 32 + lane;
-    float rtot = 0.f;
-    for (int d = 0; d < CS; ++d) rtot += rsx[d * kTile + row];
-    tc_fence_after();
-    if (!dup)
-      write_grad_rows(p, tmem_o, static_cast<uint32_t>(q * 32) << 16, g, row, ti, row_is_x, slice, slice_chunks, rtot);
-  }
-  tc_fence_before();
-  cluster_sync_all();      // both CTAs of every pair are done with tensor memory
   if (warp == 11) tmem_dealloc_2cta(tmem, 512);
 }
-
 
 int g_pair_variant = 0;   // tuning/measurement: vgan_b200_debug_variant() (bits >= 8 -> TcParams::dbg_flags)
 
@@ -474,8 +530,8 @@ int launch_tc_pair(const TcParams& p, const CUtensorMap& map, const CUtensorMap&
   if (ngrad <= 0) return VGAN_B200_OK;
   auto kern = ladder ? mmd2_tc_pair_kernel<true> : mmd2_tc_pair_kernel<false>;
   VG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kQSmemTotal));
+  const int n_units = ((ngrad + 1) / 2) * p.ngroups;
   cudaLaunchConfig_t cfg{};
-  cfg.gridDim = dim3(static_cast<unsigned>(((ngrad + 1) / 2) * p.ngroups * 2 * p.cs));
   cfg.blockDim = dim3(kQThreads);
   cfg.dynamicSmemBytes = kQSmemTotal;
   cfg.stream = st;
@@ -486,12 +542,19 @@ int launch_tc_pair(const TcParams& p, const CUtensorMap& map, const CUtensorMap&
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  if (getenv("VGAN_B200_VERBOSE")) {
-    int ncl = 0;
-    cudaOccupancyMaxActiveClusters(&ncl, kern, &cfg);
-    fprintf(stderr, "vgan_b200: pair kernel grid %u, cluster %u, max active clusters %d\n", cfg.gridDim.x,
-            attr[0].val.clusterDim.x, ncl);
+  // persistent grid: as many clusters as can be resident at once (cached per cluster size)
+  static int max_clusters[9] = {0};
+  int& ncl = max_clusters[2 * p.cs];
+  if (ncl == 0) {
+    cfg.gridDim = dim3(static_cast<unsigned>(2 * p.cs * 64));
+    VG_CUDA_CHECK(cudaOccupancyMaxActiveClusters(&ncl, kern, &cfg));
+    if (ncl < 1) ncl = 1;
+    if (getenv("VGAN_B200_VERBOSE"))
+      fprintf(stderr, "vgan_b200: pair kernel, cluster %d: %d resident clusters\n", 2 * p.cs, ncl);
   }
+  static const int persist = getenv("VGAN_B200_PERSIST") ? atoi(getenv("VGAN_B200_PERSIST")) : 1;   // 0: one cluster per unit (measurement)
+  const int n_clusters = (persist && ncl < n_units) ? ncl : n_units;
+  cfg.gridDim = dim3(static_cast<unsigned>(n_clusters * 2 * p.cs));
   VG_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, map, map64, p));
   return VGAN_B200_OK;
 }

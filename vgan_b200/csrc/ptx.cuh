@@ -255,6 +255,14 @@ __device__ __forceinline__ void mbar_remote_arrive(uint32_t cluster_bar_addr) {
   asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar_addr) : "memory");
 }
 
+// register reallocation between warpgroups (4 consecutive warps must all execute it)
+template <int N> __device__ __forceinline__ void setmaxnreg_inc() {
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N));
+}
+template <int N> __device__ __forceinline__ void setmaxnreg_dec() {
+  asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N));
+}
+
 // ------------------------------------------------------------------ descriptors
 // Shared-memory matrix descriptor, 128-byte swizzle (sm_100 "version 1").
 //   bits [0,14)  start address >> 4        bits [16,30) leading byte offset >> 4

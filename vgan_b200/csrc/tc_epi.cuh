@@ -53,10 +53,11 @@ __device__ __forceinline__ void epi_half_tile(uint32_t taddr, const float* __res
 }
 
 // dZ rows of one unit: out[row, f] = 4 c_i (O[row, f] - rtot z[row, f]) (x mul), f in the slice.
+// The expression is linear in (O, rtot): a unit cut into column ranges adds the ranges' results (accumulate).
 // Thread = (row, column half g); O columns of the slice live at tmem_o.
 __device__ __forceinline__ void write_grad_rows(const TcParams& p, uint32_t tmem_o, uint32_t lane_addr, int g,
                                                 int row, int ti, int row_is_x, int slice, int slice_chunks,
-                                                float rtot) {
+                                                float rtot, bool accumulate = false) {
   const int slice_w = slice_chunks * kChunk;
   const int64_t region_row = static_cast<int64_t>(row_is_x ? ti : ti - p.tiles_x) * kTile + row;
   const int64_t n_region = row_is_x ? p.Nx : p.Ny;
@@ -84,7 +85,8 @@ __device__ __forceinline__ void write_grad_rows(const TcParams& p, uint32_t tmem
           if (f < p.D) {
             float gval = ci4 * (__uint_as_float(v[c * 8 + e]) - rtot * z);
             if (mul) gval *= mul[f];
-            out[f] = gval;
+            if (accumulate) atomicAdd(out + f, gval);   // unit shared between clusters (stream-K cut)
+            else out[f] = gval;
           }
         }
       }
