@@ -28,7 +28,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 N_DEFAULT, D_DEFAULT, WEIGHT = 65536, 1024, 10.0
-KERNELS_PER_STEP = 9   # colstats, mean, pack, scales, setup, K1, colmax, penalty, finalize
+KERNELS_PER_STEP = 10  # colstats, mean, pack, scales, setup, K1 (pair kernel), K1s (S_xx sums), colmax, penalty, finalize
 
 
 def make_inputs(N, D, seed=0):
@@ -217,8 +217,11 @@ def main():
                            "parallelism": f"row-tile shards x{world}", "loss": loss_val},
                 "gpu_launches": KERNELS_PER_STEP * args.steps,
                 "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                             "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                             "kernel": "mmd2_tc_kernel", "kernel_ms": k1_ms,
+                             "frac": achieved / peak,
+                             # DRAM read+write bytes of one pair-kernel launch, ncu --set full (profiles/r1b_pair_k1_summary.txt)
+                             "traffic": (10.68e9 / world) if (N, D) == (N_DEFAULT, D_DEFAULT) else None, "peak_source": peak_src,
+                             "kernel": "mmd2_tc_pair_kernel (gradient units) with mmd2_xx_kernel (S_xx sums) overlapped",
+                             "kernel_ms": k1_ms,
                              "algorithmic": "8*N^2*D flops per evaluation (SURVEY.md 8(d))"},
                 "clocks": sampler.result()}
         if e2e:
