@@ -128,8 +128,9 @@ int vgan_b200_mmd2_matrix(const float* Z, int64_t n, int64_t D, const float* inv
  * (work unit, column tile) to buf[unit * stride + tile] (device floats).  NULL switches it off. */
 int vgan_b200_debug_tile_sums(float* buf, int stride);
 
-/* Tuning aid: selects the pipeline shape (operand-ring stages, P slots, PV lag) of the CTA-pair kernel;
- * 0 = default.  Results do not depend on it. */
+/* Test / measurement aid for the CTA-pair kernel: bits 0-7 = cap on the number of persistent clusters (0 = as many
+ * as fit; a small cap forces the stream-K partition to cut units between clusters on small problems); bits 8+ =
+ * measurement switches that break results (see TcParams::dbg_flags).  0 = default. */
 int vgan_b200_debug_variant(int v);
 
 /* Debug aid: cta_group::2 Gram + gradient tile on one CTA pair. A0,A1,B bf16 [128,128], V bf16 [128,256];

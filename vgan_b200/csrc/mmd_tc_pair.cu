@@ -390,6 +390,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     setmaxnreg_inc<192>();
     for (int pi = 0; pi < n_parts; ++pi, ++part) {
     VG_PAIR_DECODE_RANGE;
+    (void)TTp; (void)my_chunks;
     {
     // ===================== epilogue warps: this CTA's own column tiles =====================
     const int q = warp & 3, g = warp >> 2;
@@ -553,7 +554,9 @@ int launch_tc_pair(const TcParams& p, const CUtensorMap& map, const CUtensorMap&
       fprintf(stderr, "vgan_b200: pair kernel, cluster %d: %d resident clusters\n", 2 * p.cs, ncl);
   }
   static const int persist = getenv("VGAN_B200_PERSIST") ? atoi(getenv("VGAN_B200_PERSIST")) : 1;   // 0: one cluster per unit (measurement)
-  const int n_clusters = (persist && ncl < n_units) ? ncl : n_units;
+  int cap = ncl;
+  if ((g_pair_variant & 255) > 0 && (g_pair_variant & 255) < cap) cap = g_pair_variant & 255;   // tests: force stream-K cuts
+  const int n_clusters = (persist && cap < n_units) ? cap : n_units;
   cfg.gridDim = dim3(static_cast<unsigned>(n_clusters * 2 * p.cs));
   VG_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, map, map64, p));
   return VGAN_B200_OK;

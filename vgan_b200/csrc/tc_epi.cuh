@@ -67,6 +67,8 @@ __device__ __forceinline__ void write_grad_rows(const TcParams& p, uint32_t tmem
   const float* mul = (!row_is_x && p.dY_mul) ? p.dY_mul + (region_row - p.row_begin) * p.D : nullptr;
   const __nv_bfloat16* zrow = p.zq + (static_cast<int64_t>(ti) * kTile + row) * p.Dp;
   const int f_slice = slice * p.slice_chunks * kChunk;
+  const bool vec_ok = !accumulate && (p.D & 3) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0 &&
+                      (!mul || (reinterpret_cast<uintptr_t>(mul) & 15) == 0);
   for (int cc = 0; cc < slice_chunks; ++cc) {
     const int col = g * (slice_w / 2) + cc * 32;
     uint32_t v[32];
@@ -78,15 +80,32 @@ __device__ __forceinline__ void write_grad_rows(const TcParams& p, uint32_t tmem
       for (int c = 0; c < 4; ++c) {
         const uint4 zz = z4[c];
         const uint32_t zw[4] = {zz.x, zz.y, zz.z, zz.w};
+        float gv[8];
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
           const float z = __uint_as_float((e & 1) ? (zw[e >> 1] & 0xffff0000u) : (zw[e >> 1] << 16));
-          const int f = f_slice + col + c * 8 + e;
-          if (f < p.D) {
-            float gval = ci4 * (__uint_as_float(v[c * 8 + e]) - rtot * z);
-            if (mul) gval *= mul[f];
-            if (accumulate) atomicAdd(out + f, gval);   // unit shared between clusters (stream-K cut)
-            else out[f] = gval;
+          gv[e] = ci4 * (__uint_as_float(v[c * 8 + e]) - rtot * z);
+        }
+        const int f0 = f_slice + col + c * 8;
+        if (vec_ok && f0 + 8 <= p.D) {
+          // 16-byte accesses (rows are 16-byte aligned when D % 4 == 0)
+          if (mul) {
+            const float4 m0 = *reinterpret_cast<const float4*>(mul + f0), m1 = *reinterpret_cast<const float4*>(mul + f0 + 4);
+            gv[0] *= m0.x; gv[1] *= m0.y; gv[2] *= m0.z; gv[3] *= m0.w;
+            gv[4] *= m1.x; gv[5] *= m1.y; gv[6] *= m1.z; gv[7] *= m1.w;
+          }
+          *reinterpret_cast<float4*>(out + f0) = make_float4(gv[0], gv[1], gv[2], gv[3]);
+          *reinterpret_cast<float4*>(out + f0 + 4) = make_float4(gv[4], gv[5], gv[6], gv[7]);
+        } else {
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            const int f = f0 + e;
+            if (f < p.D) {
+              float gval = gv[e];
+              if (mul) gval *= mul[f];
+              if (accumulate) atomicAdd(out + f, gval);   // unit shared between clusters (stream-K cut)
+              else out[f] = gval;
+            }
           }
         }
       }
