@@ -38,26 +38,43 @@ __device__ __forceinline__ float epi_ksum_32(uint32_t taddr, const float* __rest
   uint32_t v[32];
   tmem_ld_32x32(taddr, v);
   tmem_ld_wait();
-  float ks0 = 0.f, ks1 = 0.f;
+  if constexpr (LADDER) {
+    const uint64_t m2 = f2_pack(m2c0, m2c0), ni2 = f2_pack(ni, ni);
+    uint64_t ks2 = f2_pack(0.f, 0.f);
 #pragma unroll
-  for (int c = 0; c < 8; ++c) {
-    const float4 nj4 = *reinterpret_cast<const float4*>(njp + c * 4);
-    const float njv[4] = {nj4.x, nj4.y, nj4.z, nj4.w};
+    for (int c = 0; c < 8; ++c) {
+      const float4 nj4 = *reinterpret_cast<const float4*>(njp + c * 4);
+      const uint64_t nj2[2] = {f2_pack(nj4.x, nj4.y), f2_pack(nj4.z, nj4.w)};
 #pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      float uarg = fmaf(__uint_as_float(v[c * 4 + e]), m2c0, ni + njv[e]);
-      uarg = fmaxf(uarg, 0.f);
-      if (LADDER) {
-        const float t1 = ex2_approx(-uarg);
-        const float t2 = t1 * t1, t4 = t2 * t2, t8 = t4 * t4, t16 = t8 * t8;
-        ks0 += (t1 + t2) + t16;
-        ks1 += t4 + t8;
-      } else {
-        for (int m = 0; m < n_scales; ++m) ks0 += ex2_approx(-uarg * ratio[m]);
+      for (int q = 0; q < 2; ++q) {
+        const uint64_t s2 = f2_pack(__uint_as_float(v[c * 4 + 2 * q]), __uint_as_float(v[c * 4 + 2 * q + 1]));
+        float u0, u1;
+        f2_unpack(f2_fma(s2, m2, f2_add(ni2, nj2[q])), u0, u1);
+        u0 = fmaxf(u0, 0.f);
+        u1 = fmaxf(u1, 0.f);
+        const uint64_t t1 = f2_pack(ex2_approx(-u0), ex2_approx(-u1));
+        const uint64_t t2 = f2_mul(t1, t1), t4 = f2_mul(t2, t2), t8 = f2_mul(t4, t4), t16 = f2_mul(t8, t8);
+        ks2 = f2_add(ks2, f2_add(f2_add(t1, t2), f2_add(f2_add(t4, t8), t16)));
       }
     }
+    float a, b;
+    f2_unpack(ks2, a, b);
+    return a + b;
+  } else {
+    float ks = 0.f;
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+      const float4 nj4 = *reinterpret_cast<const float4*>(njp + c * 4);
+      const float njv[4] = {nj4.x, nj4.y, nj4.z, nj4.w};
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        float uarg = fmaf(__uint_as_float(v[c * 4 + e]), m2c0, ni + njv[e]);
+        uarg = fmaxf(uarg, 0.f);
+        for (int m = 0; m < n_scales; ++m) ks += ex2_approx(-uarg * ratio[m]);
+      }
+    }
+    return ks;
   }
-  return ks0 + ks1;
 }
 
 template <bool LADDER>

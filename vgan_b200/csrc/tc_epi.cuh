@@ -17,6 +17,43 @@ __device__ __forceinline__ void epi_half_tile(uint32_t taddr, const float* __res
   uint32_t v[32];
   tmem_ld_32x32(taddr, v);
   tmem_ld_wait();
+  if constexpr (LADDER) {
+    // two columns per issue slot (packed f32x2): ~11.5 instead of ~19.5 instructions per pair
+    const uint64_t m2 = f2_pack(m2c0, m2c0), ni2 = f2_pack(ni, ni);
+    const uint64_t c0 = f2_pack(cf[0], cf[0]), c1 = f2_pack(cf[1], cf[1]), c2 = f2_pack(cf[2], cf[2]),
+                   c3 = f2_pack(cf[3], cf[3]), c4 = f2_pack(cf[4], cf[4]);
+    uint64_t ks2 = f2_pack(0.f, 0.f), rs2 = f2_pack(0.f, 0.f);
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      const float4 nja = *reinterpret_cast<const float4*>(njp + c * 8);
+      const float4 njb = *reinterpret_cast<const float4*>(njp + c * 8 + 4);
+      const uint64_t nj2[4] = {f2_pack(nja.x, nja.y), f2_pack(nja.z, nja.w), f2_pack(njb.x, njb.y), f2_pack(njb.z, njb.w)};
+      uint32_t pw[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const uint64_t s2 = f2_pack(__uint_as_float(v[c * 8 + 2 * q]), __uint_as_float(v[c * 8 + 2 * q + 1]));
+        float u0, u1;
+        f2_unpack(f2_fma(s2, m2, f2_add(ni2, nj2[q])), u0, u1);
+        u0 = fmaxf(u0, 0.f);
+        u1 = fmaxf(u1, 0.f);
+        const uint64_t t1 = f2_pack(ex2_approx(-u0), ex2_approx(-u1));
+        const uint64_t t2 = f2_mul(t1, t1), t4 = f2_mul(t2, t2), t8 = f2_mul(t4, t4), t16 = f2_mul(t8, t8);
+        ks2 = f2_add(ks2, f2_add(f2_add(t1, t2), f2_add(f2_add(t4, t8), t16)));
+        // scale index 4 is the widest kernel (t1), index 0 the narrowest (t16)
+        const uint64_t w2 = f2_fma(t16, c0, f2_fma(t8, c1, f2_fma(t4, c2, f2_fma(t2, c3, f2_mul(t1, c4)))));
+        rs2 = f2_add(rs2, w2);
+        float w0, w1;
+        f2_unpack(w2, w0, w1);
+        pw[q] = pack_bf16x2(w0, w1);
+      }
+      pk[c].x = pw[0]; pk[c].y = pw[1]; pk[c].z = pw[2]; pk[c].w = pw[3];
+    }
+    float a, b;
+    f2_unpack(ks2, a, b);
+    ksum += a + b;
+    f2_unpack(rs2, a, b);
+    rsum += a + b;
+  } else {
 #pragma unroll
   for (int c = 0; c < 4; ++c) {
     const float4 nja = *reinterpret_cast<const float4*>(njp + c * 8);
@@ -27,28 +64,21 @@ __device__ __forceinline__ void epi_half_tile(uint32_t taddr, const float* __res
     for (int e = 0; e < 8; ++e) {
       float uarg = fmaf(__uint_as_float(v[c * 8 + e]), m2c0, ni + njv[e]);
       uarg = fmaxf(uarg, 0.f);
-      if (LADDER) {
-        const float t1 = ex2_approx(-uarg);
-        const float t2 = t1 * t1, t4 = t2 * t2, t8 = t4 * t4, t16 = t8 * t8;
-        ksum += (t1 + t2) + (t4 + t8) + t16;
-        // scale index 4 is the widest kernel (t1), index 0 the narrowest (t16)
-        w[e] = fmaf(t16, cf[0], fmaf(t8, cf[1], fmaf(t4, cf[2], fmaf(t2, cf[3], t1 * cf[4]))));
-      } else {
-        float kk = 0.f, ww = 0.f;
-        for (int m = 0; m < n_scales; ++m) {
-          const float em = ex2_approx(-uarg * ratio[m]);
-          kk += em;
-          ww = fmaf(em, cf[m], ww);
-        }
-        ksum += kk;
-        w[e] = ww;
+      float kk = 0.f, ww = 0.f;
+      for (int m = 0; m < n_scales; ++m) {
+        const float em = ex2_approx(-uarg * ratio[m]);
+        kk += em;
+        ww = fmaf(em, cf[m], ww);
       }
+      ksum += kk;
+      w[e] = ww;
       rsum += w[e];
     }
     pk[c].x = pack_bf16x2(w[0], w[1]);
     pk[c].y = pack_bf16x2(w[2], w[3]);
     pk[c].z = pack_bf16x2(w[4], w[5]);
     pk[c].w = pack_bf16x2(w[6], w[7]);
+  }
   }
 }
 
