@@ -17,6 +17,7 @@
 // warp 10 = TMA producer for V slices + column norms, warp 11 = TMEM allocator.
 #include "common.cuh"
 #include "ptx.cuh"
+#include "tc_epi.cuh"
 
 namespace vg {
 
@@ -267,54 +268,16 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const TcParams p) {
       mbar_wait(&bar->nj_full[b], (n >> 1) & 1);
       mbar_wait(&bar->s_full[b], (n >> 1) & 1);
       tc_fence_after();
-      if (u.pv) mbar_wait(&bar->p_empty[b], ((n >> 1) & 1) ^ 1);   // PV(n-2) done with P[b]
       uint8_t* p_row = smem + kSmemP + b * kPBytes + g * kChunkBytes + row * 128;
       const float* njp = nj_smem + b * kTile + g * 64;
       float ksum = 0.f;
+      uint4 pk[8];
+      epi_tile_64<LADDER>(tmem + lane_addr + b * kTile + g * 64, njp, ni, m2c0, cf, ratio, p.n_scales, ksum, rsum, pk);
+      if (u.pv) {
+        mbar_wait(&bar->p_empty[b], ((n >> 1) & 1) ^ 1);   // PV(n-2) done with P[b]
 #pragma unroll
-      for (int half = 0; half < 2; ++half) {
-        uint32_t v[32];
-        tmem_ld_32x32(tmem + lane_addr + b * kTile + g * 64 + half * 32, v);
-        tmem_ld_wait();
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {   // 8 columns -> one 16-byte chunk of 8 bf16
-          const float4 nja = *reinterpret_cast<const float4*>(njp + half * 32 + c * 8);
-          const float4 njb = *reinterpret_cast<const float4*>(njp + half * 32 + c * 8 + 4);
-          const float njv[8] = {nja.x, nja.y, nja.z, nja.w, njb.x, njb.y, njb.z, njb.w};
-          float w[8];
-#pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            float uarg = fmaf(__uint_as_float(v[c * 8 + e]), m2c0, ni + njv[e]);
-            uarg = fmaxf(uarg, 0.f);
-            if (LADDER) {
-              const float t1 = ex2_approx(-uarg);
-              const float t2 = t1 * t1, t4 = t2 * t2, t8 = t4 * t4, t16 = t8 * t8;
-              ksum += (t1 + t2) + (t4 + t8) + t16;
-              // scale index 4 is the widest kernel (t1), index 0 the narrowest (t16)
-              w[e] = fmaf(t16, cf[0],
-                          fmaf(t8, cf[1], fmaf(t4, cf[2], fmaf(t2, cf[3], t1 * cf[4]))));
-            } else {
-              float kk = 0.f, ww = 0.f;
-              for (int m = 0; m < p.n_scales; ++m) {
-                const float em = ex2_approx(-uarg * ratio[m]);
-                kk += em;
-                ww = fmaf(em, cf[m], ww);
-              }
-              ksum += kk;
-              w[e] = ww;
-            }
-            rsum += w[e];
-          }
-          if (u.pv) {
-            uint4 pk;
-            pk.x = pack_bf16x2(w[0], w[1]);
-            pk.y = pack_bf16x2(w[2], w[3]);
-            pk.z = pack_bf16x2(w[4], w[5]);
-            pk.w = pack_bf16x2(w[6], w[7]);
-            const int chunk16 = half * 4 + c;   // 128B-swizzled K-major A operand
-            *reinterpret_cast<uint4*>(p_row + ((chunk16 ^ (row & 7)) << 4)) = pk;
-          }
-        }
+        for (int i = 0; i < 8; ++i)                          // 128B-swizzled K-major A operand
+          *reinterpret_cast<uint4*>(p_row + ((i ^ (row & 7)) << 4)) = pk[i];
       }
       tc_fence_before();
       mbar_arrive(&bar->s_empty[b]);

@@ -276,15 +276,7 @@ mmd2_tc_cluster_kernel(const __grid_constant__ CUtensorMap zmap, const TcParams 
       const float* njp = nj_smem + b * kTile + g * 64;
       float ksum = 0.f;
       uint4 pk[8];
-      {
-        uint4 h0[4], h1[4];
-        epi_half_tile<LADDER>(tmem + lane_addr + b * kTile + g * 64, njp, ni, m2c0, cf, ratio, p.n_scales,
-                              ksum, rsum, h0);
-        epi_half_tile<LADDER>(tmem + lane_addr + b * kTile + g * 64 + 32, njp + 32, ni, m2c0, cf, ratio,
-                              p.n_scales, ksum, rsum, h1);
-#pragma unroll
-        for (int i = 0; i < 4; ++i) { pk[i] = h0[i]; pk[4 + i] = h1[i]; }
-      }
+      epi_tile_64<LADDER>(tmem + lane_addr + b * kTile + g * 64, njp, ni, m2c0, cf, ratio, p.n_scales, ksum, rsum, pk);
       tc_fence_before();
       mbar_arrive(&bar->s_empty[b]);          // S and the norms are free; P is parked in registers
       if (valid) { if (col_is_x) acc_x += ksum; else acc_y += ksum; }

@@ -5,18 +5,12 @@
 
 namespace vg {
 
-// One thread = one row of the tile.  Reads S[row, col0 .. col0+31] from TMEM, forms
-//   u = c0*d2 = fma(S, -2c0, ni + nj),  t = 2^-u,  k = sum_m t^(2^q),  w = sum_m coef_m t^(2^q)
-// (ladder) or the general n_scales form, adds k to ksum and w to rsum, and returns the 32 values of
-// P = w as bf16 packed into 4 x uint4 (8 columns each, ascending).
+// Kernel values of 32 columns already in registers (see epi_half_tile for the math).
 template <bool LADDER>
-__device__ __forceinline__ void epi_half_tile(uint32_t taddr, const float* __restrict__ njp, float ni,
-                                              float m2c0, const float (&cf)[VGAN_B200_MAX_SCALES],
-                                              const float (&ratio)[VGAN_B200_MAX_SCALES], int n_scales,
-                                              float& ksum, float& rsum, uint4 (&pk)[4]) {
-  uint32_t v[32];
-  tmem_ld_32x32(taddr, v);
-  tmem_ld_wait();
+__device__ __forceinline__ void epi_compute_32(const uint32_t (&v)[32], const float* __restrict__ njp, float ni,
+                                                    float m2c0, const float (&cf)[VGAN_B200_MAX_SCALES],
+                                                    const float (&ratio)[VGAN_B200_MAX_SCALES], int n_scales,
+                                                    float& ksum, float& rsum, uint4 (&pk)[4]) {
   if constexpr (LADDER) {
     // two columns per issue slot (packed f32x2): ~11.5 instead of ~19.5 instructions per pair
     const uint64_t m2 = f2_pack(m2c0, m2c0), ni2 = f2_pack(ni, ni);
@@ -80,6 +74,38 @@ __device__ __forceinline__ void epi_half_tile(uint32_t taddr, const float* __res
     pk[c].w = pack_bf16x2(w[6], w[7]);
   }
   }
+}
+
+// One thread = one row of the tile.  Reads S[row, col0 .. col0+31] from TMEM, forms
+//   u = c0*d2 = fma(S, -2c0, ni + nj),  t = 2^-u,  k = sum_m t^(2^q),  w = sum_m coef_m t^(2^q)
+// (ladder) or the general n_scales form, adds k to ksum and w to rsum, and returns the 32 values of
+// P = w as bf16 packed into 4 x uint4 (8 columns each, ascending).
+template <bool LADDER>
+__device__ __forceinline__ void epi_half_tile(uint32_t taddr, const float* __restrict__ njp, float ni,
+                                              float m2c0, const float (&cf)[VGAN_B200_MAX_SCALES],
+                                              const float (&ratio)[VGAN_B200_MAX_SCALES], int n_scales,
+                                              float& ksum, float& rsum, uint4 (&pk)[4]) {
+  uint32_t v[32];
+  tmem_ld_32x32(taddr, v);
+  tmem_ld_wait();
+  epi_compute_32<LADDER>(v, njp, ni, m2c0, cf, ratio, n_scales, ksum, rsum, pk);
+}
+
+// 64 columns: both TMEM loads are issued before the single wait, so their latencies overlap
+template <bool LADDER>
+__device__ __forceinline__ void epi_tile_64(uint32_t taddr, const float* __restrict__ njp, float ni, float m2c0,
+                                            const float (&cf)[VGAN_B200_MAX_SCALES],
+                                            const float (&ratio)[VGAN_B200_MAX_SCALES], int n_scales,
+                                            float& ksum, float& rsum, uint4 (&pk)[8]) {
+  uint32_t va[32], vb[32];
+  tmem_ld_32x32(taddr, va);
+  tmem_ld_32x32(taddr + 32, vb);
+  tmem_ld_wait();
+  uint4 h0[4], h1[4];
+  epi_compute_32<LADDER>(va, njp, ni, m2c0, cf, ratio, n_scales, ksum, rsum, h0);
+  epi_compute_32<LADDER>(vb, njp + 32, ni, m2c0, cf, ratio, n_scales, ksum, rsum, h1);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { pk[i] = h0[i]; pk[4 + i] = h1[i]; }
 }
 
 // dZ rows of one unit: out[row, f] = 4 c_i (O[row, f] - rtot z[row, f]) (x mul), f in the slice.
