@@ -121,6 +121,15 @@ int vgan_b200_finalize_loss(const double* sums, int64_t Nx, int64_t Ny, const fl
 int vgan_b200_mmd2_matrix(const float* Z, int64_t n, int64_t D, const float* inv_scales,
                           int n_scales, float eps, float* K_out, void* stream);
 
+/* Subspace distribution (vgan.py:372-382 / 649-659): unique rows of the boolean mask matrix
+ * (U[i,d] >= threshold for float U, U[i,d] != 0 when in_is_bool) in np.unique(axis=0) order, and how often each
+ * occurs.  unique_out uint8 [n, D] (the first *n_unique rows are written), counts_out int64 [n], n_unique device
+ * int; scratch >= vgan_b200_subspace_scratch_bytes(n, D).  Replaces generate_subspaces' threshold
+ * (vgan.py:369 / 646) + np.unique on the host. */
+int vgan_b200_subspace_scratch_bytes(int64_t n, int64_t D, size_t* out);
+int vgan_b200_subspace_dist(const void* U, int in_is_bool, int64_t n, int64_t D, float threshold, void* scratch,
+                            uint8_t* unique_out, long long* counts_out, int* n_unique, void* stream);
+
 /* Debug aid: one Gram tile and one gradient tile through the tcgen05 pipeline with raw
  * outputs, used by tests to localise descriptor/layout errors. A,B bf16 [128,128] row-major;
  * S_out float [128,128] = A B^T;  O_out float [128,128] = bf16(S) B. */

@@ -5,6 +5,7 @@ Public surface mirrors the reference (/root/reference/src): ``RBF``, ``MMDLossCo
 ``VGAN`` / ``VGAN_no_kl`` (vgan.py)."""
 from .loss import RBF, MMDLossConstrained, mmd2_eval  # noqa: F401
 from .statistic import MMDStatistic  # noqa: F401
+from .subspace import unique_subspaces  # noqa: F401
 from .vgan import VGAN, VGAN_no_kl  # noqa: F401
 
-__all__ = ["RBF", "MMDLossConstrained", "MMDStatistic", "VGAN", "VGAN_no_kl", "mmd2_eval"]
+__all__ = ["RBF", "MMDLossConstrained", "MMDStatistic", "VGAN", "VGAN_no_kl", "mmd2_eval", "unique_subspaces"]

@@ -78,6 +78,7 @@ int run_penalty(const float*, int64_t, int64_t, float, unsigned long long*, floa
                 cudaStream_t);
 int run_finalize(const double*, int64_t, int64_t, const float*, float*, cudaStream_t);
 int launch_matrix(const float*, int64_t, int64_t, const float*, int, float, float*, cudaStream_t);
+int run_subspace_dist(const void*, int, int64_t, int64_t, float, void*, uint8_t*, long long*, int*, cudaStream_t);
 struct SimtParams;
 int launch_rate_probe(const CUtensorMap& zmap, int n, int iters, int b_mn, int tma_warps, int tma_tiles, int grid,
                       long long* out, cudaStream_t st);
@@ -350,6 +351,26 @@ int vgan_b200_mmd2_matrix(const float* Z, int64_t n, int64_t D, const float* inv
     return VGAN_B200_ERR_ARG;
   }
   return launch_matrix(Z, n, D, inv_scales, n_scales, eps, K_out, static_cast<cudaStream_t>(stream));
+}
+
+int vgan_b200_subspace_scratch_bytes(int64_t n, int64_t D, size_t* out) {
+  if (!out || n < 1 || D < 1) {
+    set_error("subspace_scratch_bytes: bad arguments");
+    return VGAN_B200_ERR_ARG;
+  }
+  *out = static_cast<size_t>(n) * ((D + 63) / 64) * 8 + static_cast<size_t>(n) * 8;
+  return VGAN_B200_OK;
+}
+
+int vgan_b200_subspace_dist(const void* U, int in_is_bool, int64_t n, int64_t D, float threshold, void* scratch,
+                            uint8_t* unique_out, long long* counts_out, int* n_unique, void* stream) {
+  if (int e = check_device()) return e;
+  if (!U || !scratch || !unique_out || !counts_out || !n_unique || n < 1 || D < 1 || n > (1 << 20)) {
+    set_error("subspace_dist: null pointer or bad size (1 <= n <= 2^20)");
+    return VGAN_B200_ERR_ARG;
+  }
+  return run_subspace_dist(U, in_is_bool, n, D, threshold, scratch, unique_out, counts_out, n_unique,
+                           static_cast<cudaStream_t>(stream));
 }
 
 int vgan_b200_debug_tile_sums(float* buf, int stride) {

@@ -29,6 +29,7 @@ import torch
 from .loss import MMDLossConstrained
 from .models import Decoder, Detector, Encoder, Generator_big
 from .statistic import MMDStatistic
+from .subspace import unique_subspaces as unique_subspaces_device
 
 
 def _device():
@@ -112,7 +113,9 @@ class _SubspaceGAN:
 
     def approx_subspace_dist(self, subspace_count=500, add_leftover_features=False):
         u = self.generate_subspaces(subspace_count)
-        unique_subspaces, proba = np.unique(np.array(u.to('cpu')), axis=0, return_counts=True)
+        # unique rows + multiplicities on the device, in np.unique(axis=0) order (subspace.py)
+        uniq_d, counts_d = unique_subspaces_device(u)
+        unique_subspaces, proba = uniq_d.cpu().numpy(), counts_d.cpu().numpy()
         unused = unique_subspaces.sum(axis=0) < 1
         if unused.sum() != 0 and add_leftover_features:
             unique_subspaces = np.append(unique_subspaces, [unused], axis=0)
