@@ -56,10 +56,15 @@ class ClockSampler(threading.Thread):
         self.max_mhz = None
 
     def run(self):
+        while not self.stop_flag:
+            self._once()
+            time.sleep(0.2)
+
+    def _once(self):
         q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        while not self.stop_flag:
+        if True:
             try:
                 out = subprocess.run(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits",
                                       "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
@@ -71,9 +76,11 @@ class ClockSampler(threading.Thread):
                         self.reasons.add(nm)
             except Exception:
                 pass
-            time.sleep(0.2)
 
     def result(self):
+        if not self.samples:
+            self.stop_flag = False
+            self._once()                       # timed region shorter than one sampling period: sample right after it
         if not self.samples:
             return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
         return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz,

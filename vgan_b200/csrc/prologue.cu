@@ -88,6 +88,82 @@ __global__ void __launch_bounds__(256) pack_kernel(PackArgs a) {
   if (lane == 0) a.nrm[r] = valid ? nrm : kPadNorm;
 }
 
+// ---- masked fast path (Y = U*X, Nx == Ny, D % 4 == 0, 16-byte aligned inputs): X and U are read ONCE per pass
+// for both halves of the stack (the generic kernels read X twice), with 16-byte loads.
+__global__ void __launch_bounds__(256) colstats_masked_kernel(PackArgs a, int rows_per_block) {
+  const int64_t r0 = static_cast<int64_t>(blockIdx.x) * rows_per_block;
+  const int64_t r1 = min(r0 + rows_per_block, a.Nx);
+  const int64_t D4 = a.D >> 2;
+  float sq = 0.f;
+  for (int64_t f4 = threadIdx.x; f4 < D4; f4 += blockDim.x) {
+    float4 cs = make_float4(0.f, 0.f, 0.f, 0.f);
+    const float4* xp = reinterpret_cast<const float4*>(a.X) + r0 * D4 + f4;
+    const float4* up = reinterpret_cast<const float4*>(a.U) + r0 * D4 + f4;
+#pragma unroll 4
+    for (int64_t r = r0; r < r1; ++r, xp += D4, up += D4) {
+      const float4 x = __ldg(xp), u = __ldg(up);
+      const float4 y = make_float4(u.x * x.x, u.y * x.y, u.z * x.z, u.w * x.w);
+      cs.x += x.x + y.x; cs.y += x.y + y.y; cs.z += x.z + y.z; cs.w += x.w + y.w;
+      sq = fmaf(x.x, x.x, fmaf(x.y, x.y, fmaf(x.z, x.z, fmaf(x.w, x.w, sq))));
+      sq = fmaf(y.x, y.x, fmaf(y.y, y.y, fmaf(y.z, y.z, fmaf(y.w, y.w, sq))));
+    }
+    atomicAdd(&a.stats[2 + 4 * f4 + 0], static_cast<double>(cs.x));
+    atomicAdd(&a.stats[2 + 4 * f4 + 1], static_cast<double>(cs.y));
+    atomicAdd(&a.stats[2 + 4 * f4 + 2], static_cast<double>(cs.z));
+    atomicAdd(&a.stats[2 + 4 * f4 + 3], static_cast<double>(cs.w));
+  }
+  sq = warp_sum(sq);
+  __shared__ float red[8];
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = sq;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+    for (int w = 0; w < 8; ++w) t += red[w];
+    atomicAdd(&a.stats[0], t);
+  }
+}
+
+__device__ __forceinline__ uint2 pack4_bf16(float a, float b, float c, float d, float& nrm) {
+  const __nv_bfloat16 q0 = __float2bfloat16_rn(a), q1 = __float2bfloat16_rn(b), q2 = __float2bfloat16_rn(c),
+                      q3 = __float2bfloat16_rn(d);
+  const float r0 = __bfloat162float(q0), r1 = __bfloat162float(q1), r2 = __bfloat162float(q2), r3 = __bfloat162float(q3);
+  nrm = fmaf(r0, r0, fmaf(r1, r1, fmaf(r2, r2, fmaf(r3, r3, nrm))));   // norm of the values the tensor core will see
+  uint2 o;
+  o.x = static_cast<uint32_t>(__bfloat16_as_ushort(q0)) | (static_cast<uint32_t>(__bfloat16_as_ushort(q1)) << 16);
+  o.y = static_cast<uint32_t>(__bfloat16_as_ushort(q2)) | (static_cast<uint32_t>(__bfloat16_as_ushort(q3)) << 16);
+  return o;
+}
+
+// one warp per sample row r: writes stored rows r (X half) and Nxp + r (Y half), bf16 path
+__global__ void __launch_bounds__(256) pack_masked_kernel(PackArgs a) {
+  const int lane = threadIdx.x & 31;
+  const int64_t r = static_cast<int64_t>(blockIdx.x) * 8 + (threadIdx.x >> 5);
+  if (r >= a.Nxp) return;
+  const bool valid = r < a.Nx;
+  const int64_t D4 = a.D >> 2, Dp4 = a.Dp >> 2;
+  float nx = 0.f, ny = 0.f;
+  uint2* zx = reinterpret_cast<uint2*>(a.zq + r * a.Dp);
+  uint2* zy = reinterpret_cast<uint2*>(a.zq + (a.Nxp + r) * a.Dp);
+  for (int64_t f4 = lane; f4 < Dp4; f4 += 32) {
+    uint2 ox = make_uint2(0u, 0u), oy = make_uint2(0u, 0u);
+    if (valid && f4 < D4) {
+      const float4 x = __ldg(reinterpret_cast<const float4*>(a.X) + r * D4 + f4);
+      const float4 u = __ldg(reinterpret_cast<const float4*>(a.U) + r * D4 + f4);
+      const float4 m = *reinterpret_cast<const float4*>(a.mean + 4 * f4);
+      ox = pack4_bf16(x.x - m.x, x.y - m.y, x.z - m.z, x.w - m.w, nx);
+      oy = pack4_bf16(u.x * x.x - m.x, u.y * x.y - m.y, u.z * x.z - m.z, u.w * x.w - m.w, ny);
+    }
+    zx[f4] = ox;
+    zy[f4] = oy;
+  }
+  nx = warp_sum(nx);
+  ny = warp_sum(ny);
+  if (lane == 0) {
+    a.nrm[r] = valid ? nx : kPadNorm;
+    a.nrm[a.Nxp + r] = valid ? ny : kPadNorm;
+  }
+}
+
 struct ScaleArgs {
   float mults[VGAN_B200_MAX_SCALES];
   int n_scales, frozen;
@@ -168,9 +244,18 @@ int run_prologue(const float* X, const float* U, const float* Y, const vgan_b200
   VG_CUDA_CHECK(cudaMemsetAsync(a.stats, 0, sizeof(double) * (2 + L.Dp), st));
   const int64_t n = L.Nx + L.Ny;
   const int rpb = 64;
-  colstats_kernel<<<static_cast<unsigned>((n + rpb - 1) / rpb), 256, 0, st>>>(a, rpb);
-  mean_kernel<<<static_cast<unsigned>((L.Dp + 255) / 256), 256, 0, st>>>(a);
-  pack_kernel<<<static_cast<unsigned>((L.Nxp + L.Nyp + 7) / 8), 256, 0, st>>>(a);
+  const bool masked_fast = !Y && U && !a.fp32 && L.Nx == L.Ny && (L.D & 3) == 0 &&
+                           ((reinterpret_cast<uintptr_t>(X) | reinterpret_cast<uintptr_t>(U)) & 15) == 0;
+  if (masked_fast) {
+    const int rpb2 = 32;
+    colstats_masked_kernel<<<static_cast<unsigned>((L.Nx + rpb2 - 1) / rpb2), 256, 0, st>>>(a, rpb2);
+    mean_kernel<<<static_cast<unsigned>((L.Dp + 255) / 256), 256, 0, st>>>(a);
+    pack_masked_kernel<<<static_cast<unsigned>((L.Nxp + 7) / 8), 256, 0, st>>>(a);
+  } else {
+    colstats_kernel<<<static_cast<unsigned>((n + rpb - 1) / rpb), 256, 0, st>>>(a, rpb);
+    mean_kernel<<<static_cast<unsigned>((L.Dp + 255) / 256), 256, 0, st>>>(a);
+    pack_kernel<<<static_cast<unsigned>((L.Nxp + L.Nyp + 7) / 8), 256, 0, st>>>(a);
+  }
   VG_CUDA_CHECK(cudaGetLastError());
   return VGAN_B200_OK;
 }
