@@ -137,6 +137,10 @@ int vgan_b200_subspace_dist(const void* U, int in_is_bool, int64_t n, int64_t D,
  * (work unit, column tile) to buf[unit * stride + tile] (device floats).  NULL switches it off. */
 int vgan_b200_debug_tile_sums(float* buf, int stride);
 
+/* Measurement aid: when buf != NULL (4 device uint64, caller presets {~0, 0, ~0, 0}) the D > 256 kernels record the
+ * %globaltimer (ns) of their first CTA start / last CTA end: [0,1] gradient kernel, [2,3] S_xx kernel. */
+int vgan_b200_debug_timeline(unsigned long long* buf);
+
 /* Test / measurement aid for the CTA-pair kernel: bits 0-7 = cap on the number of persistent clusters (0 = as many
  * as fit; a small cap forces the stream-K partition to cut units between clusters on small problems); bits 8+ =
  * measurement switches that break results (see TcParams::dbg_flags).  0 = default. */

@@ -23,7 +23,7 @@ EXPORTS = [
     "vgan_b200_colmax_penalty", "vgan_b200_finalize_loss", "vgan_b200_mmd2_matrix",
     "vgan_b200_umma_probe", "vgan_b200_debug_tile_sums", "vgan_b200_umma_rate_probe", "vgan_b200_pair_probe",
     "vgan_b200_debug_variant", "vgan_b200_tma_rate_probe",
-    "vgan_b200_subspace_scratch_bytes", "vgan_b200_subspace_dist",
+    "vgan_b200_subspace_scratch_bytes", "vgan_b200_subspace_dist", "vgan_b200_debug_timeline",
 ]
 
 
@@ -76,6 +76,7 @@ def lib() -> C.CDLL:
             L.vgan_b200_umma_rate_probe.argtypes = [i, i, i, p, i64, i, i, p, p]
             L.vgan_b200_pair_probe.argtypes = [p, p, p, p, p, p, p]
             L.vgan_b200_debug_variant.argtypes = [i]
+            L.vgan_b200_debug_timeline.argtypes = [p]
             L.vgan_b200_subspace_scratch_bytes.argtypes = [i64, i64, C.POINTER(C.c_size_t)]
             L.vgan_b200_subspace_dist.argtypes = [p, i, i64, i64, f, p, p, p, p, p]
             L.vgan_b200_tma_rate_probe.argtypes = [p, i64, i64, i, i, i, i, i, i, i, p, p]

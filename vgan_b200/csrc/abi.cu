@@ -91,6 +91,7 @@ int launch_simt_from_abi(const vgan_b200_layout_t& L, void* ws, int64_t row_begi
                          float* dY, const float* dY_mul, float* dX, cudaStream_t st);
 
 extern int g_pair_variant;
+static unsigned long long* g_timeline = nullptr;
 static float* g_dbg = nullptr;
 static int g_dbg_stride = 0;
 
@@ -248,6 +249,7 @@ int vgan_b200_mmd2_fwd_bwd(void* ws, int64_t Nx, int64_t Ny, int64_t D, int64_t 
   p.sums = sums; p.dY = dY; p.dY_mul = dY_mul; p.dX = dX;
   p.xchg = L.Dp > kSliceMax ? base + L.off_xchg : nullptr;
   p.dbg = g_dbg; p.dbg_stride = g_dbg_stride;
+  p.timeline = g_timeline;
   p.dbg_flags = g_pair_variant >> 8;
   CUtensorMap map;
   if (int e = make_tmap_bf16_2d(&map, p.zq, static_cast<uint64_t>(L.Nxp + L.Nyp), static_cast<uint64_t>(L.Dp)))
@@ -282,6 +284,16 @@ int vgan_b200_mmd2_fwd_bwd(void* ws, int64_t Nx, int64_t Ny, int64_t D, int64_t 
       if (int e = make_tmap_bf16_2d(&map256, p.zq, static_cast<uint64_t>(L.Nxp + L.Nyp), static_cast<uint64_t>(L.Dp),
                                     256))
         return e;
+    const bool pair_ok = (p.kchunks % 4 == 0 || p.kchunks % 4 == 2) && !(flags & VGAN_B200_NO_PAIR);
+    if (pair_ok) {
+      // stream-K cuts a unit between two clusters: those rows are accumulated with red.global.add.  Zeroed BEFORE
+      // the fork: a memset in front of the gradient kernel on its own stream lets the S_xx kernel start first and
+      // occupy SMs the persistent clusters need (measured: the clusters then start up to 9 ms late).
+      if (ye > row_begin)
+        VG_CUDA_CHECK(cudaMemsetAsync(dY, 0, static_cast<size_t>(ye - row_begin) * D * sizeof(float), st));
+      if (need_dx && xe > row_begin)
+        VG_CUDA_CHECK(cudaMemsetAsync(dX, 0, static_cast<size_t>(xe - row_begin) * D * sizeof(float), st));
+    }
     if (overlap) {
       VG_CUDA_CHECK(cudaEventRecord(ev_fork, st));
       VG_CUDA_CHECK(cudaStreamWaitEvent(hi, ev_fork, 0));
@@ -292,17 +304,11 @@ int vgan_b200_mmd2_fwd_bwd(void* ws, int64_t Nx, int64_t Ny, int64_t D, int64_t 
       }
     }
     // full 128/256-wide slices: CTA pairs (cta_group::2) halve the shared-memory operand traffic
-    const bool pair_ok = (p.kchunks % 4 == 0 || p.kchunks % 4 == 2) && !(flags & VGAN_B200_NO_PAIR);
     if (pair_ok) {
       CUtensorMap map64;
       if (int e = make_tmap_bf16_2d(&map64, p.zq, static_cast<uint64_t>(L.Nxp + L.Nyp),
                                     static_cast<uint64_t>(L.Dp), 64))
         return e;
-      // stream-K cuts a unit between two clusters: those rows are accumulated with red.global.add
-      if (ye > row_begin)
-        VG_CUDA_CHECK(cudaMemsetAsync(dY, 0, static_cast<size_t>(ye - row_begin) * D * sizeof(float), main_st));
-      if (need_dx && xe > row_begin)
-        VG_CUDA_CHECK(cudaMemsetAsync(dX, 0, static_cast<size_t>(xe - row_begin) * D * sizeof(float), main_st));
       if (int e = launch_tc_pair(p, map, map64, ladder, main_st)) return e;
     } else {
       if (int e = launch_tc_cluster(p, map, ladder, main_st)) return e;
@@ -376,6 +382,11 @@ int vgan_b200_subspace_dist(const void* U, int in_is_bool, int64_t n, int64_t D,
 int vgan_b200_debug_tile_sums(float* buf, int stride) {
   g_dbg = buf;
   g_dbg_stride = stride;
+  return VGAN_B200_OK;
+}
+
+int vgan_b200_debug_timeline(unsigned long long* buf) {
+  g_timeline = buf;
   return VGAN_B200_OK;
 }
 

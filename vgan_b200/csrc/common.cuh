@@ -52,6 +52,7 @@ struct TcParams {
   uint8_t* xchg;              // P-tile exchange scratch, kXchgSms x kXchgBytesPerSm (cluster kernels), L2 resident
   float* dbg;                 // debug: per-(unit, tile) kernel sums, or nullptr
   int dbg_stride;
+  unsigned long long* timeline;   // debug: [0,1] = first start / last end (globaltimer ns) of the pair kernel, [2,3] = S_xx kernel
   int dbg_flags;              // measurement only: bit 0 = exchange 16 bytes per P tile instead of 32 KiB (wrong results)
 };
 

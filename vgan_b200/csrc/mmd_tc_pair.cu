@@ -512,6 +512,10 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     }
     if (warp == 0) d[14] = static_cast<float>(tm_tail);
   }
+  if (p.timeline && threadIdx.x == 0) {
+    atomicMin(&p.timeline[0], gt_begin);
+    atomicMax(&p.timeline[1], global_timer_ns());
+  }
   if (warp == 11) tmem_dealloc_2cta(tmem, 512);
 }
 

@@ -91,6 +91,7 @@ mmd2_xx_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__
   const int q_begin = ti >> 1;                         // column-tile PAIRS [q_begin, q_end) cover tiles ti .. tiles_x-1
   const int q_end = (p.tiles_x + 1) >> 1;
   const int nq = q_end - q_begin;
+  const unsigned long long gt_begin = global_timer_ns();
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kXStages; ++s) {
@@ -218,6 +219,10 @@ mmd2_xx_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__
   }
   tc_fence_before();
   __syncthreads();
+  if (p.timeline && threadIdx.x == 0) {
+    atomicMin(&p.timeline[2], gt_begin);
+    atomicMax(&p.timeline[3], global_timer_ns());
+  }
   if (warp == 11) tmem_dealloc(tmem, 512);
 }
 

@@ -195,6 +195,11 @@ __device__ __forceinline__ void bulk_load_multicast(uint32_t dst_addr, const voi
       ::"r"(dst_addr), "l"(reinterpret_cast<uint64_t>(gsrc)), "r"(bytes), "r"(bar_addr), "h"(cta_mask)
       : "memory");
 }
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
 __device__ __forceinline__ uint32_t sm_id() {
   uint32_t r;
   asm volatile("mov.u32 %0, %%smid;" : "=r"(r));
