@@ -49,6 +49,20 @@ static EncodeTiledFn get_encode() {
   return fn;
 }
 
+typedef CUresult (*StreamWaitValueFn)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
+
+static StreamWaitValueFn get_stream_wait() {
+  static StreamWaitValueFn fn = nullptr;
+  if (!fn) {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuStreamWaitValue32", &ptr, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<StreamWaitValueFn>(ptr);
+  }
+  return fn;
+}
+
 // bf16 [rows, cols] row-major, box = 64 columns x 128 rows, 128-byte swizzle
 int make_tmap_bf16_2d(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint32_t box_rows) {
   EncodeTiledFn enc = get_encode();
@@ -250,6 +264,7 @@ int vgan_b200_mmd2_fwd_bwd(void* ws, int64_t Nx, int64_t Ny, int64_t D, int64_t 
   p.xchg = L.Dp > kSliceMax ? base + L.off_xchg : nullptr;
   p.dbg = g_dbg; p.dbg_stride = g_dbg_stride;
   p.timeline = g_timeline;
+  p.started = nullptr;
   p.dbg_flags = g_pair_variant >> 8;
   CUtensorMap map;
   if (int e = make_tmap_bf16_2d(&map, p.zq, static_cast<uint64_t>(L.Nxp + L.Nyp), static_cast<uint64_t>(L.Dp)))
@@ -265,6 +280,9 @@ int vgan_b200_mmd2_fwd_bwd(void* ws, int64_t Nx, int64_t Ny, int64_t D, int64_t 
     // Priorities: the cluster kernel runs on a high-priority internal stream, the S_xx kernel on a
     // low-priority one, so that SMs freed by a finished cluster go to the next cluster and not to pending
     // S_xx CTAs (which would fragment the GPC and keep the next 8-CTA cluster from launching).
+    // With the persistent pair kernel the order is enforced instead: its CTAs count themselves in at their first
+    // instruction, the side stream holds the S_xx launch (cuStreamWaitValue32, no SM occupied) until all of them
+    // are resident, and the S_xx grid is sized to the SMs they leave free.
     static cudaStream_t side = nullptr, hi = nullptr;
     static cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_join_hi = nullptr;
     static const int xx_mode = getenv("VGAN_B200_XX_MODE") ? atoi(getenv("VGAN_B200_XX_MODE")) : 0;   // 1: serial (measurement)
@@ -294,6 +312,12 @@ int vgan_b200_mmd2_fwd_bwd(void* ws, int64_t Nx, int64_t Ny, int64_t D, int64_t 
       if (need_dx && xe > row_begin)
         VG_CUDA_CHECK(cudaMemsetAsync(dX, 0, static_cast<size_t>(xe - row_begin) * D * sizeof(float), st));
     }
+    StreamWaitValueFn stream_wait = (overlap && pair_ok && xx_mode == 0) ? get_stream_wait() : nullptr;
+    if (stream_wait) {
+      p.started = reinterpret_cast<unsigned*>(base + L.off_par + kParStartedOffset);
+      VG_CUDA_CHECK(cudaMemsetAsync(p.started, 0, sizeof(unsigned), st));
+    }
+    int resident_ctas = 0;
     if (overlap) {
       VG_CUDA_CHECK(cudaEventRecord(ev_fork, st));
       VG_CUDA_CHECK(cudaStreamWaitEvent(hi, ev_fork, 0));
@@ -309,7 +333,7 @@ int vgan_b200_mmd2_fwd_bwd(void* ws, int64_t Nx, int64_t Ny, int64_t D, int64_t 
       if (int e = make_tmap_bf16_2d(&map64, p.zq, static_cast<uint64_t>(L.Nxp + L.Nyp),
                                     static_cast<uint64_t>(L.Dp), 64))
         return e;
-      if (int e = launch_tc_pair(p, map, map64, ladder, main_st)) return e;
+      if (int e = launch_tc_pair(p, map, map64, ladder, main_st, &resident_ctas)) return e;
     } else {
       if (int e = launch_tc_cluster(p, map, ladder, main_st)) return e;
     }
@@ -317,7 +341,24 @@ int vgan_b200_mmd2_fwd_bwd(void* ws, int64_t Nx, int64_t Ny, int64_t D, int64_t 
     if (!overlap) return launch_xx(p, map, map256, ladder, st);
     if (xx_mode != 2) {
       VG_CUDA_CHECK(cudaStreamWaitEvent(side, ev_fork, 0));
-      if (int e = launch_xx(p, map, map256, ladder, side)) return e;
+      int free_sms = 0;
+      if (stream_wait && resident_ctas > 0) {
+        int dev = 0, n_sms = 0;
+        VG_CUDA_CHECK(cudaGetDevice(&dev));
+        VG_CUDA_CHECK(cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev));
+        free_sms = n_sms - resident_ctas;
+      }
+      if (free_sms >= kXxMinFreeSms) {
+        CUresult r = stream_wait(reinterpret_cast<CUstream>(side), reinterpret_cast<CUdeviceptr>(p.started),
+                                 static_cast<cuuint32_t>(resident_ctas), CU_STREAM_WAIT_VALUE_GEQ);
+        if (r != CUDA_SUCCESS) {
+          set_error("cuStreamWaitValue32 failed with CUresult %d", static_cast<int>(r));
+          return VGAN_B200_ERR_CUDA;
+        }
+      } else {
+        free_sms = 0;       // no room beside the clusters: plain low-priority launch over all SMs
+      }
+      if (int e = launch_xx(p, map, map256, ladder, side, free_sms)) return e;
     }
     VG_CUDA_CHECK(cudaEventRecord(ev_join, side));
     VG_CUDA_CHECK(cudaEventRecord(ev_join_hi, hi));

@@ -24,6 +24,8 @@ constexpr float kLog2e = 1.4426950408889634f;
 // par[10 + m] = cx * inv_s[m]              (P coefficients for X columns, cx = +1/Nx)
 // par[18 + m] = cy * inv_s[m]              (P coefficients for Y columns, cy = -1/Ny)
 constexpr int kParFloats = 32;
+constexpr int kParStartedOffset = 512;   // byte offset in the (1 KiB) parameter block of the pair kernel's "CTAs started" counter
+constexpr int kXxMinFreeSms = 8;         // fewer SMs left free by the gradient clusters: S_xx runs over all SMs at low priority instead
 // P-tile exchange scratch (pair kernel): 3 slots of one bf16 [128,128] tile per SM, indexed by %smid so that a
 // region is only ever rewritten by the CTA resident on that SM (stays in L2, never streams to HBM)
 constexpr int kXchgSms = 256;
@@ -49,6 +51,7 @@ struct TcParams {
   float* dY;
   const float* dY_mul;
   float* dX;
+  unsigned* started;          // pair kernel: CTAs that have begun executing (the S_xx launch waits on it), or nullptr
   uint8_t* xchg;              // P-tile exchange scratch, kXchgSms x kXchgBytesPerSm (cluster kernels), L2 resident
   float* dbg;                 // debug: per-(unit, tile) kernel sums, or nullptr
   int dbg_stride;
@@ -71,9 +74,11 @@ int check_device();   // 0 when the current device is compute capability 10.x
 
 // kernels' host launchers (defined in their own .cu files)
 int launch_tc(const TcParams& p, const CUtensorMap& map, int ladder, cudaStream_t st);
-int launch_xx(const TcParams& p, const CUtensorMap& map, const CUtensorMap& map256, int ladder, cudaStream_t st);
+int launch_xx(const TcParams& p, const CUtensorMap& map, const CUtensorMap& map256, int ladder, cudaStream_t st,
+              int max_ctas = 0);
 int launch_tc_cluster(const TcParams& p, const CUtensorMap& map, int ladder, cudaStream_t st);
-int launch_tc_pair(const TcParams& p, const CUtensorMap& map, const CUtensorMap& map64, int ladder, cudaStream_t st);
+int launch_tc_pair(const TcParams& p, const CUtensorMap& map, const CUtensorMap& map64, int ladder, cudaStream_t st,
+                   int* resident_ctas = nullptr);
 int launch_probe(const CUtensorMap& mapA, const CUtensorMap& mapB, float* S_out, float* O_out,
                  cudaStream_t st);
 int make_tmap_bf16_2d(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint32_t box_rows = 128);

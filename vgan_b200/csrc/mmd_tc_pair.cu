@@ -172,6 +172,8 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
   const long long t_begin = clock64();
   unsigned long long gt_begin;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt_begin));
+  // resident now: the host makes the S_xx launch wait until every persistent CTA has counted itself in
+  if (p.started && threadIdx.x == 0) atomicAdd(p.started, 1u);
   long long tm_tail = 0;
   float* rsx = reinterpret_cast<float*>(smem + kQSmemP);       // [CS][128] row-sum exchange, reuses P slot 0
 
@@ -522,7 +524,8 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
 int g_pair_variant = 0;   // tuning/measurement: vgan_b200_debug_variant() (bits >= 8 -> TcParams::dbg_flags)
 
 int launch_tc_pair(const TcParams& p, const CUtensorMap& map, const CUtensorMap& map64, int ladder,
-                   cudaStream_t st) {
+                   cudaStream_t st, int* resident_ctas) {
+  if (resident_ctas) *resident_ctas = 0;
   const int ngrad = (p.gx_end - p.gx_begin) + (p.gy_end - p.gy_begin);
   if (ngrad <= 0) return VGAN_B200_OK;
   auto kern = ladder ? mmd2_tc_pair_kernel<true> : mmd2_tc_pair_kernel<false>;
@@ -554,6 +557,7 @@ int launch_tc_pair(const TcParams& p, const CUtensorMap& map, const CUtensorMap&
   if ((g_pair_variant & 255) > 0 && (g_pair_variant & 255) < cap) cap = g_pair_variant & 255;   // tests: force stream-K cuts
   const int n_clusters = (persist && cap < n_units) ? cap : n_units;
   cfg.gridDim = dim3(static_cast<unsigned>(n_clusters * 2 * p.cs));
+  if (resident_ctas) *resident_ctas = (n_clusters < ncl ? n_clusters : ncl) * 2 * p.cs;
   VG_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, map, map64, p));
   return VGAN_B200_OK;
 }

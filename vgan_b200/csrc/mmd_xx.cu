@@ -1,6 +1,6 @@
 // K1s — kernel sums only (no gradient GEMM) on tcgen05, N = 256: the S_xx block of the no-KL path
 // (Mmd_loss_constrained.py:46, needed for the loss value only) walks the upper triangle of X x X.
-// One CTA = one row tile I; per step TWO column tiles (2q, 2q+1) share every Z_I chunk:
+// One step = one row tile I against TWO column tiles (2q, 2q+1) that share every Z_I chunk:
 //   S[128 x 256] = Z_I Z_{J,J+1}^T   4 x tcgen05.mma M=128 N=256 K=16 per 48 KiB stage (A 16 + B 32 KiB)
 // An N=128 Gram stream is bound by the ISSUE rate of its one thread (~48 cycles per MMA + ~160 per
 // stage against 256 execution cycles); at N=256 the same issue cost buys 512 execution cycles and the
@@ -9,6 +9,10 @@
 // 0 (below the diagonal / outside X), 1 (diagonal tile), 2 (above).
 // Warps: 0-7 epilogue (warp%4 = lane quadrant, warp/4 = which of the two column tiles),
 // 8 and 10 TMA producers (alternate stages), 9 MMA issuer, 11 TMEM allocator + column norms.
+// Work partition: the (row tile, column pair) steps of this shard's row tiles form one flat sequence
+// that the grid's CTAs cut into equal contiguous ranges (a range may span several row tiles), so the
+// grid can be any size — all SMs when the kernel runs alone, the SMs the persistent gradient clusters
+// leave free when it runs beside them.
 #include "common.cuh"
 #include "ptx.cuh"
 
@@ -30,6 +34,24 @@ constexpr int kXSmemNj = kXStages * kXStageBytes;
 constexpr int kXSmemBar = kXSmemNj + 2 * 2 * kTile * 4;
 constexpr int kXSmemTotal = kXSmemBar + static_cast<int>(sizeof(XxBarriers));
 static_assert(kXSmemTotal <= 232448, "shared memory budget");
+
+// walks the flat step sequence: unit u = row tile xx_part + u * xx_nparts, column pairs [ti / 2, q_end)
+struct XxIter {
+  int ti, q, q_end, nparts;
+  __device__ __forceinline__ void advance() {
+    if (++q == q_end) {
+      ti += nparts;
+      q = ti >> 1;
+    }
+  }
+};
+
+__host__ __device__ inline long long xx_total_steps(int xx_part, int xx_nparts, int n_units, int tiles_x) {
+  const int q_end = (tiles_x + 1) >> 1;
+  long long t = 0;
+  for (int u = 0; u < n_units; ++u) t += q_end - ((xx_part + u * xx_nparts) >> 1);
+  return t;
+}
 
 // sum over 32 TMEM columns of k = sum_m exp(-d2 / s_m) for one row
 template <bool LADDER>
@@ -87,10 +109,20 @@ mmd2_xx_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__
   float* nj_smem = reinterpret_cast<float*>(smem + kXSmemNj);
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int ti = p.xx_part + static_cast<int>(blockIdx.x) * p.xx_nparts;   // X row tile (long units first)
-  const int q_begin = ti >> 1;                         // column-tile PAIRS [q_begin, q_end) cover tiles ti .. tiles_x-1
-  const int q_end = (p.tiles_x + 1) >> 1;
-  const int nq = q_end - q_begin;
+  // this CTA's range of the flat step sequence, and the (row tile, column pair) it starts at
+  const int q_end = (p.tiles_x + 1) >> 1;              // column-tile PAIRS [ti / 2, q_end) cover tiles ti .. tiles_x-1
+  const long long total = xx_total_steps(p.xx_part, p.xx_nparts, p.n_xx_units, p.tiles_x);
+  const long long s_begin = total * blockIdx.x / gridDim.x, s_end = total * (blockIdx.x + 1) / gridDim.x;
+  const int nq = static_cast<int>(s_end - s_begin);
+  XxIter it0{p.xx_part, p.xx_part >> 1, q_end, p.xx_nparts};
+  {
+    long long skip = s_begin;
+    while (skip >= q_end - (it0.ti >> 1)) {
+      skip -= q_end - (it0.ti >> 1);
+      it0.ti += p.xx_nparts;
+    }
+    it0.q = (it0.ti >> 1) + static_cast<int>(skip);
+  }
   const unsigned long long gt_begin = global_timer_ns();
 
   if (threadIdx.x == 0) {
@@ -122,8 +154,10 @@ mmd2_xx_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__
     // ===================== TMA producers =====================
     const uint32_t pj = warp == 8 ? 0u : 1u;
     uint32_t s = 0, ph = 0;
-    for (int it = 0; it < nq; ++it) {
-      const int jrow = (q_begin + it) * 2 * kTile;
+    XxIter w = it0;
+    for (int it = 0; it < nq; ++it, w.advance()) {
+      const int jrow = w.q * 2 * kTile;
+      const int ti = w.ti;
       for (int kc = 0; kc < p.kchunks; ++kc) {
         if ((s & 1u) == pj) {
           mbar_wait(&bar->ring_empty[s], ph ^ 1);
@@ -142,11 +176,12 @@ mmd2_xx_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__
   } else if (warp == 11) {
     // ===================== scaled column norms of the tile pair =====================
     if (lane == 0) {
-      for (int it = 0; it < nq; ++it) {
+      XxIter w = it0;
+      for (int it = 0; it < nq; ++it, w.advance()) {
         const int b = it & 1;
         mbar_wait(&bar->s_empty[b], ((it >> 1) & 1) ^ 1);
         mbar_arrive_expect_tx(&bar->nj_full[b], 2 * kTile * 4);
-        bulk_load_1d(nj_smem + b * 2 * kTile, p.nrms + static_cast<int64_t>(q_begin + it) * 2 * kTile, 2 * kTile * 4,
+        bulk_load_1d(nj_smem + b * 2 * kTile, p.nrms + static_cast<int64_t>(w.q) * 2 * kTile, 2 * kTile * 4,
                      &bar->nj_full[b]);
       }
     }
@@ -186,14 +221,19 @@ mmd2_xx_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__
     const int row = q * 32 + lane;
     const uint32_t lane_addr = static_cast<uint32_t>(q * 32) << 16;
     const float m2c0 = p.par[1];
-    const float ni = p.nrms[static_cast<int64_t>(ti) * kTile + row];
     float ratio[VGAN_B200_MAX_SCALES];
 #pragma unroll
     for (int m = 0; m < VGAN_B200_MAX_SCALES; ++m) ratio[m] = p.par[2 + m];
-    float acc = 0.f;
-    for (int it = 0; it < nq; ++it) {
+    float acc = 0.f, ni = 0.f;
+    XxIter w = it0;
+    int ti = -1;
+    for (int it = 0; it < nq; ++it, w.advance()) {
       const int b = it & 1;
-      const int jt = (q_begin + it) * 2 + g;           // this warp's column tile
+      if (w.ti != ti) {
+        ti = w.ti;
+        ni = p.nrms[static_cast<int64_t>(ti) * kTile + row];
+      }
+      const int jt = w.q * 2 + g;                      // this warp's column tile
       const float wgt = (jt < ti || jt >= p.tiles_x) ? 0.f : (jt == ti ? 1.f : 2.f);
       mbar_wait(&bar->nj_full[b], (it >> 1) & 1);
       mbar_wait(&bar->s_full[b], (it >> 1) & 1);
@@ -226,11 +266,23 @@ mmd2_xx_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__
   if (warp == 11) tmem_dealloc(tmem, 512);
 }
 
-int launch_xx(const TcParams& p, const CUtensorMap& map, const CUtensorMap& map256, int ladder, cudaStream_t st) {
+// max_ctas > 0 bounds the grid (the SMs a concurrently running kernel leaves free); 0 = one CTA per SM
+int launch_xx(const TcParams& p, const CUtensorMap& map, const CUtensorMap& map256, int ladder, cudaStream_t st,
+              int max_ctas) {
   if (p.n_xx_units <= 0) return VGAN_B200_OK;
   auto kern = ladder ? mmd2_xx_kernel<true> : mmd2_xx_kernel<false>;
   VG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kXSmemTotal));
-  kern<<<p.n_xx_units, kXThreads, kXSmemTotal, st>>>(map, map256, p);
+  static int n_sms = 0;
+  if (n_sms == 0) {
+    int dev = 0;
+    VG_CUDA_CHECK(cudaGetDevice(&dev));
+    VG_CUDA_CHECK(cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev));
+  }
+  const long long total = xx_total_steps(p.xx_part, p.xx_nparts, p.n_xx_units, p.tiles_x);
+  long long grid = max_ctas > 0 ? max_ctas : n_sms;
+  if (grid > total) grid = total;
+  if (grid < 1) return VGAN_B200_OK;
+  kern<<<static_cast<unsigned>(grid), kXThreads, kXSmemTotal, st>>>(map, map256, p);
   VG_CUDA_CHECK(cudaGetLastError());
   return VGAN_B200_OK;
 }
