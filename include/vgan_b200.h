@@ -121,6 +121,16 @@ int vgan_b200_finalize_loss(const double* sums, int64_t Nx, int64_t Ny, const fl
 int vgan_b200_mmd2_matrix(const float* Z, int64_t n, int64_t D, const float* inv_scales,
                           int n_scales, float eps, float* K_out, void* stream);
 
+/* Permutation test of the unbiased MMD^2 statistic (torch_two_sample MMDStatistic.pval ->
+ * permutation_test.pyx::permutation_test_mat, reached from vgan.py:425-428 / 702-705).  K float [n,n] kernel
+ * matrix (vgan_b200_mmd2_matrix), member uint8 [n_perm, n]: row p marks with 1 the n_1 points that relabeling p
+ * assigns to sample 1 (row with the first n_1 ones = the observed labels).  stats double [n_perm] receives
+ * a00 (sum K11 - tr K11) + a11 (sum K22 - tr K22) + 2 a01 sum K12 of every relabeling; the p-value is the fraction
+ * of rows whose statistic is >= the observed one.  scratch >= vgan_b200_permutation_scratch_bytes(n). */
+int vgan_b200_permutation_scratch_bytes(int64_t n, size_t* out);
+int vgan_b200_permutation_stats(const float* K, int64_t n, int64_t n_1, const uint8_t* member, int64_t n_perm,
+                                void* scratch, double* stats, void* stream);
+
 /* Subspace distribution (vgan.py:372-382 / 649-659): unique rows of the boolean mask matrix
  * (U[i,d] >= threshold for float U, U[i,d] != 0 when in_is_bool) in np.unique(axis=0) order, and how often each
  * occurs.  unique_out uint8 [n, D] (the first *n_unique rows are written), counts_out int64 [n], n_unique device

@@ -106,3 +106,21 @@ def test_check_if_myopic_runs(monkeypatch, capsys):
     df = m.check_if_myopic(X, bandwidth=0.01, count=300)
     assert list(df.columns) == [0.01, "recommended bandwidth"]
     assert ((df.values >= 0) & (df.values <= 1)).all()
+
+
+def test_graph_replay_matches_eager_steps(monkeypatch, capsys):
+    """The CUDA-graph replayed step (after 3 eager steps) and the all-eager loop train identically: same seeds, same
+    RNG consumption, same kernels — only fp32 atomics order may differ."""
+    from vgan_b200 import VGAN_no_kl
+    X = _data()
+    kw = dict(batch_size=250, epochs=6, lr=0.01, seed=777)
+    graphed = _fit(VGAN_no_kl, None, X, monkeypatch, **kw)
+    assert graphed.used_cuda_graph
+    monkeypatch.setattr(VGAN_no_kl, "cuda_graph", False)
+    eager = _fit(VGAN_no_kl, None, X, monkeypatch, **kw)
+    assert not eager.used_cuda_graph
+    a, b = np.array(graphed.train_history["generator_loss"]), np.array(eager.train_history["generator_loss"])
+    np.testing.assert_allclose(a, b, rtol=1e-4, atol=1e-6)
+    fa = graphed.generate_subspaces(500).float().mean(0).cpu().numpy()
+    fb = eager.generate_subspaces(500).float().mean(0).cpu().numpy()
+    assert np.abs(fa - fb).max() <= 0.01

@@ -23,7 +23,8 @@ EXPORTS = [
     "vgan_b200_colmax_penalty", "vgan_b200_finalize_loss", "vgan_b200_mmd2_matrix",
     "vgan_b200_umma_probe", "vgan_b200_debug_tile_sums", "vgan_b200_umma_rate_probe", "vgan_b200_pair_probe",
     "vgan_b200_debug_variant", "vgan_b200_tma_rate_probe",
-    "vgan_b200_subspace_scratch_bytes", "vgan_b200_subspace_dist", "vgan_b200_debug_timeline",
+    "vgan_b200_subspace_scratch_bytes", "vgan_b200_subspace_dist",
+    "vgan_b200_permutation_scratch_bytes", "vgan_b200_permutation_stats", "vgan_b200_debug_timeline",
 ]
 
 
@@ -78,6 +79,8 @@ def lib() -> C.CDLL:
             L.vgan_b200_debug_variant.argtypes = [i]
             L.vgan_b200_debug_timeline.argtypes = [p]
             L.vgan_b200_subspace_scratch_bytes.argtypes = [i64, i64, C.POINTER(C.c_size_t)]
+            L.vgan_b200_permutation_scratch_bytes.argtypes = [i64, C.POINTER(C.c_size_t)]
+            L.vgan_b200_permutation_stats.argtypes = [p, i64, i64, p, i64, p, p, p]
             L.vgan_b200_subspace_dist.argtypes = [p, i, i64, i64, f, p, p, p, p, p]
             L.vgan_b200_tma_rate_probe.argtypes = [p, i64, i64, i, i, i, i, i, i, i, p, p]
             for name in EXPORTS:

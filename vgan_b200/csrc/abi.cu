@@ -93,6 +93,8 @@ int run_penalty(const float*, int64_t, int64_t, float, unsigned long long*, floa
 int run_finalize(const double*, int64_t, int64_t, const float*, float*, cudaStream_t);
 int launch_matrix(const float*, int64_t, int64_t, const float*, int, float, float*, cudaStream_t);
 int run_subspace_dist(const void*, int, int64_t, int64_t, float, void*, uint8_t*, long long*, int*, cudaStream_t);
+size_t perm_scratch_bytes(int64_t n);
+int run_permutation_stats(const float*, int64_t, int64_t, const uint8_t*, int64_t, void*, double*, cudaStream_t);
 struct SimtParams;
 int launch_rate_probe(const CUtensorMap& zmap, int n, int iters, int b_mn, int tma_warps, int tma_tiles, int grid,
                       long long* out, cudaStream_t st);
@@ -312,7 +314,11 @@ int vgan_b200_mmd2_fwd_bwd(void* ws, int64_t Nx, int64_t Ny, int64_t D, int64_t 
       if (need_dx && xe > row_begin)
         VG_CUDA_CHECK(cudaMemsetAsync(dX, 0, static_cast<size_t>(xe - row_begin) * D * sizeof(float), st));
     }
-    StreamWaitValueFn stream_wait = (overlap && pair_ok && xx_mode == 0) ? get_stream_wait() : nullptr;
+    // (not while the caller captures a CUDA graph: the plain low-priority launch is used there)
+    cudaStreamCaptureStatus capturing = cudaStreamCaptureStatusNone;
+    VG_CUDA_CHECK(cudaStreamIsCapturing(st, &capturing));
+    StreamWaitValueFn stream_wait =
+        (overlap && pair_ok && xx_mode == 0 && capturing == cudaStreamCaptureStatusNone) ? get_stream_wait() : nullptr;
     if (stream_wait) {
       p.started = reinterpret_cast<unsigned*>(base + L.off_par + kParStartedOffset);
       VG_CUDA_CHECK(cudaMemsetAsync(p.started, 0, sizeof(unsigned), st));
@@ -398,6 +404,25 @@ int vgan_b200_mmd2_matrix(const float* Z, int64_t n, int64_t D, const float* inv
     return VGAN_B200_ERR_ARG;
   }
   return launch_matrix(Z, n, D, inv_scales, n_scales, eps, K_out, static_cast<cudaStream_t>(stream));
+}
+
+int vgan_b200_permutation_scratch_bytes(int64_t n, size_t* out) {
+  if (!out || n < 1) {
+    set_error("permutation_scratch_bytes: bad arguments");
+    return VGAN_B200_ERR_ARG;
+  }
+  *out = perm_scratch_bytes(n);
+  return VGAN_B200_OK;
+}
+
+int vgan_b200_permutation_stats(const float* K, int64_t n, int64_t n_1, const uint8_t* member, int64_t n_perm,
+                                void* scratch, double* stats, void* stream) {
+  if (int e = check_device()) return e;
+  if (!K || !member || !scratch || !stats || n_1 < 2 || n - n_1 < 2 || n > 200000 || n_perm < 1) {
+    set_error("permutation_stats: null pointer or bad size (n_1 >= 2, n - n_1 >= 2, n <= 200000, n_perm >= 1)");
+    return VGAN_B200_ERR_ARG;
+  }
+  return run_permutation_stats(K, n, n_1, member, n_perm, scratch, stats, static_cast<cudaStream_t>(stream));
 }
 
 int vgan_b200_subspace_scratch_bytes(int64_t n, int64_t D, size_t* out) {

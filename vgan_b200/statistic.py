@@ -7,8 +7,9 @@ unpinned and absent in the reference environment) as V-GAN uses it in ``check_if
     p = mmd.pval(K, n_permutations=1000)
 
 Unbiased (diagonal-removed) MMD^2 with k = sum_a exp(-a (d2 + 1e-5)).  The kernel matrix comes
-from the CUDA ``mmd2_matrix`` kernel; the permutation test evaluates all relabelings as one
-batched quadratic form on the device instead of the upstream Cython O(n_perm n^2) loop.
+from the CUDA ``mmd2_matrix`` kernel; the permutation test evaluates all relabelings on the device
+(``vgan_b200_permutation_stats``, csrc/permtest.cu: 8 relabelings per CTA share every K_ij read) instead of
+the upstream Cython O(n_perm n^2) host loop.
 Parity for this class is UNPINNED (no upstream source or vectors available): it is checked
 against the restatement in oracle/mmd_oracle.py only."""
 from __future__ import annotations
@@ -28,17 +29,20 @@ class MMDStatistic:
         self.a01 = - 1. / (n_1 * n_2)
 
     def _statistic(self, K, member_1):
-        """member_1: [P, n] {0,1} float rows marking sample 1; returns [P] statistics."""
-        KA = member_1 @ K
-        aKa = (KA * member_1).sum(1)
-        aK1 = KA.sum(1)
-        total = K.sum()
-        diag = torch.diagonal(K)
-        d1 = member_1 @ diag
-        d2 = diag.sum() - d1
-        aKb = aK1 - aKa
-        bKb = total - 2.0 * aK1 + aKa
-        return self.a00 * (aKa - d1) + self.a11 * (bKb - d2) + 2.0 * self.a01 * aKb
+        """member_1: uint8 [P, n] rows marking sample 1 with ones; returns the [P] statistics (fp64) from the
+        device permutation kernel (csrc/permtest.cu) — no torch matmul on this path."""
+        import ctypes as C
+        K = K.contiguous()
+        member_1 = member_1.contiguous()
+        n = K.shape[0]
+        L = _lib.lib()
+        nbytes = C.c_size_t()
+        _lib.check(L.vgan_b200_permutation_scratch_bytes(n, C.byref(nbytes)), "permutation_scratch_bytes")
+        scratch = torch.empty(nbytes.value, dtype=torch.uint8, device=K.device)
+        stats = torch.empty(member_1.shape[0], dtype=torch.float64, device=K.device)
+        _lib.check(L.vgan_b200_permutation_stats(_ptr(K), n, self.n_1, _ptr(member_1), member_1.shape[0],
+                                                 _ptr(scratch), _ptr(stats), _stream()), "permutation_stats")
+        return stats
 
     def __call__(self, sample_1, sample_2, alphas, ret_matrix=False):
         if sample_1.device.type != "cuda":
@@ -54,21 +58,23 @@ class MMDStatistic:
         K = torch.empty((n, n), dtype=torch.float32, device=dev)
         _lib.check(_lib.lib().vgan_b200_mmd2_matrix(_ptr(Z), n, D, _ptr(inv), inv.numel(), 1e-5, _ptr(K),
                                                     _stream()), "mmd2_matrix")
-        member = torch.zeros(1, n, dtype=torch.float64, device=dev)
+        member = torch.zeros(1, n, dtype=torch.uint8, device=dev)
         member[0, :self.n_1] = 1
-        mmd = self._statistic(K.double(), member)[0].float()
+        mmd = self._statistic(K, member)[0].float()
         if ret_matrix:
             return mmd, K
         return mmd
 
     def pval(self, distances, n_permutations=1000):
         """Fraction of random relabelings whose statistic is >= the observed one."""
-        K = distances.double()
+        if distances.device.type != "cuda":
+            raise RuntimeError("vgan_b200.MMDStatistic needs CUDA tensors on an sm_100 device")
+        K = distances.float()
         n = K.shape[0]
         dev = K.device
-        member = torch.zeros(n_permutations + 1, n, dtype=torch.float64, device=dev)
+        member = torch.zeros(n_permutations + 1, n, dtype=torch.uint8, device=dev)
         member[0, :self.n_1] = 1
-        order = torch.rand(n_permutations, n, device=dev).argsort(1)
-        member[1:].scatter_(1, order[:, :self.n_1], 1.0)
+        order = torch.rand(n_permutations, n, device=dev).argsort(1)       # the relabelings (RNG stays in torch)
+        member[1:].scatter_(1, order[:, :self.n_1], 1)
         st = self._statistic(K, member)
         return float((st[1:] >= st[0]).double().mean().item())

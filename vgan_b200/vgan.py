@@ -55,6 +55,18 @@ class _SubspaceGAN:
         for b in range(n // self.batch_size):
             yield Xd[perm[b * self.batch_size:(b + 1) * self.batch_size]]
 
+    cuda_graph = True            # replay the training step as a CUDA graph (VGAN_B200_NO_GRAPH=1 or False: eager)
+    _graph_warmup_steps = 3
+
+    @staticmethod
+    def _capture_step(step, static_batch):
+        """Capture one training step on ``static_batch`` (nothing executes during capture)."""
+        graph = torch.cuda.CUDAGraph()
+        torch.cuda.synchronize()
+        with torch.cuda.graph(graph):
+            step(static_batch)
+        return graph
+
     def _save_run(self, generator, also_detector_slot: bool):
         if self.path_to_directory is None:
             return
@@ -294,26 +306,47 @@ class VGAN_no_kl(_SubspaceGAN):
         ndims = X.shape[1]
         self.batch_size = min(self.batch_size, X.shape[0])
         generator = self.get_the_networks(ndims, latent_size, device=self.device)
-        optimizer = torch.optim.Adadelta(generator.parameters(), lr=self.lr, weight_decay=self.weight_decay)
+        use_graph = (self.cuda_graph and self.device.type == 'cuda'
+                     and not os.environ.get('VGAN_B200_NO_GRAPH'))
+        optimizer = torch.optim.Adadelta(generator.parameters(), lr=self.lr, weight_decay=self.weight_decay,
+                                         capturable=use_graph)
         self.generator_optimizer = optimizer.__class__.__name__
         loss_function = MMDLossConstrained(weight=10)
         Xd = self._to_device(X)
         batch_number = Xd.shape[0] // self.batch_size
         noise = torch.empty(self.batch_size, latent_size, device=self.device)
+        acc = torch.zeros((), device=self.device)
+
+        def step(batch):
+            noise.normal_()
+            optimizer.zero_grad(set_to_none=True)
+            fake_subspaces = generator(noise)
+            batch_loss = loss_function.forward_masked(batch, fake_subspaces)   # loss(x, u*x, u)
+            batch_loss.backward()
+            optimizer.step()
+            acc.add_(batch_loss.detach() / batch_number)
+
+        # The step (noise -> generator -> prologue -> fused MMD kernel -> backward -> Adadelta) is launch-bound at the
+        # reference's batch sizes (N = 500): after a few eager steps (bandwidth frozen, optimizer state and
+        # workspaces allocated) it is captured once into a CUDA graph and replayed per batch.
+        graph, static_batch, eager_steps = None, None, 0
         for epoch in range(self.epochs):
             print(f'\rEpoch {epoch} of {self.epochs}')
-            acc = torch.zeros((), device=self.device)
+            acc.zero_()
             for batch in self._batches(Xd):
-                noise.normal_()
-                optimizer.zero_grad()
-                fake_subspaces = generator(noise)
-                batch_loss = loss_function.forward_masked(batch, fake_subspaces)   # loss(x, u*x, u)
-                self.bandwidth = loss_function.bandwidth
-                batch_loss.backward()
-                optimizer.step()
-                acc += batch_loss.detach() / batch_number
+                if graph is not None:
+                    static_batch.copy_(batch)
+                    graph.replay()
+                    continue
+                step(batch)
+                eager_steps += 1
+                if use_graph and eager_steps == self._graph_warmup_steps:
+                    static_batch = torch.empty_like(batch)
+                    graph = self._capture_step(step, static_batch)
+            self.bandwidth = loss_function.bandwidth
             generator_loss = float(acc)                 # one host sync per epoch
             print(f"Average loss in the epoch: {generator_loss}")
             self.train_history["generator_loss"].append(generator_loss)
+        self.used_cuda_graph = graph is not None
         self._save_run(generator, also_detector_slot=False)
         self.generator = generator
