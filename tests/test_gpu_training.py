@@ -124,3 +124,17 @@ def test_graph_replay_matches_eager_steps(monkeypatch, capsys):
     fa = graphed.generate_subspaces(500).float().mean(0).cpu().numpy()
     fb = eager.generate_subspaces(500).float().mean(0).cpu().numpy()
     assert np.abs(fa - fb).max() <= 0.01
+
+
+def test_kl_graph_replay_matches_eager_steps(monkeypatch, capsys):
+    from vgan_b200 import VGAN
+    X = _data(1000, 32, seed=1)
+    kw = dict(batch_size=250, epochs=8)
+    graphed = _fit(VGAN, None, X, monkeypatch, **kw)
+    assert graphed.used_cuda_graph
+    monkeypatch.setattr(VGAN, "cuda_graph", False)
+    eager = _fit(VGAN, None, X, monkeypatch, **kw)
+    assert not eager.used_cuda_graph
+    for key in ("detector_loss", "generator_loss"):
+        a, b = np.array(graphed.train_history[key]), np.array(eager.train_history[key])
+        np.testing.assert_allclose(a, b, rtol=2e-4, atol=1e-6, equal_nan=True)

@@ -36,6 +36,31 @@ def _device():
     return torch.device('cuda:0' if torch.cuda.is_available() else 'cpu')
 
 
+class _GraphedStep:
+    """Runs ``fn(batch)`` eagerly for ``warmup`` calls, then captures it once into a CUDA graph on a static batch
+    buffer (nothing executes during capture) and replays it for every later batch.  The steps are launch-bound at
+    the reference's batch sizes (N = 500); a replay costs one launch."""
+
+    def __init__(self, fn, enabled: bool, warmup: int = 3):
+        self.fn, self.enabled, self.warmup = fn, enabled, warmup
+        self.graph, self.static, self.calls = None, None, 0
+
+    def __call__(self, batch):
+        if self.graph is not None:
+            self.static.copy_(batch)
+            self.graph.replay()
+            return
+        self.fn(batch)
+        self.calls += 1
+        if self.enabled and self.calls == self.warmup:
+            self.static = torch.empty_like(batch)
+            graph = torch.cuda.CUDAGraph()
+            torch.cuda.synchronize()
+            with torch.cuda.graph(graph):
+                self.fn(self.static)
+            self.graph = graph
+
+
 class _SubspaceGAN:
     """Everything the two reference classes share."""
 
@@ -58,14 +83,8 @@ class _SubspaceGAN:
     cuda_graph = True            # replay the training step as a CUDA graph (VGAN_B200_NO_GRAPH=1 or False: eager)
     _graph_warmup_steps = 3
 
-    @staticmethod
-    def _capture_step(step, static_batch):
-        """Capture one training step on ``static_batch`` (nothing executes during capture)."""
-        graph = torch.cuda.CUDAGraph()
-        torch.cuda.synchronize()
-        with torch.cuda.graph(graph):
-            step(static_batch)
-        return graph
+    def _use_graph(self) -> bool:
+        return bool(self.cuda_graph and self.device.type == 'cuda' and not os.environ.get('VGAN_B200_NO_GRAPH'))
 
     def _save_run(self, generator, also_detector_slot: bool):
         if self.path_to_directory is None:
@@ -209,8 +228,11 @@ class VGAN(_SubspaceGAN):
         generator, detector = self.get_the_networks(ndims, latent_size, device=self.device)
         generator.apply(self._weights_init)
         detector.apply(self._weights_init)
-        gen_optimizer = torch.optim.Adadelta(generator.parameters(), lr=self.lr_G, weight_decay=self.weight_decay)
-        det_optimizer = torch.optim.Adadelta(detector.parameters(), lr=self.lr_D, weight_decay=self.weight_decay)
+        use_graph = self._use_graph()
+        gen_optimizer = torch.optim.Adadelta(generator.parameters(), lr=self.lr_G, weight_decay=self.weight_decay,
+                                             capturable=use_graph)
+        det_optimizer = torch.optim.Adadelta(detector.parameters(), lr=self.lr_D, weight_decay=self.weight_decay,
+                                             capturable=use_graph)
         self.generator_optimizer = gen_optimizer.__class__.__name__
         self.detector_optimizer = det_optimizer.__class__.__name__
         loss_function = MMDLossConstrained(weight=self.temperature)
@@ -218,45 +240,58 @@ class VGAN(_SubspaceGAN):
         batch_number = Xd.shape[0] // self.batch_size
         noise = torch.empty(self.batch_size, latent_size, device=self.device)
         l2 = lambda a, b: (a - b).pow(2).mean()     # noqa: E731
+        acc = torch.zeros((), device=self.device)
+
+        def detector_step(batch):
+            # maximise MMD(enc, penc) - 0.1 (reconstruction terms)  (:251-291)
+            for p in detector.parameters():
+                p.requires_grad = True
+            enc, dec = detector(batch)
+            with torch.no_grad():
+                U = generator(noise.normal_()).clone().detach()
+            masked = U * batch
+            penc, pdec = detector(masked)
+            det_optimizer.zero_grad()
+            loss_D = -(loss_function(enc, penc, U) - .1 * l2(batch, dec) - .1 * l2(masked, pdec))
+            loss_D.backward()
+            det_optimizer.step()
+            acc.add_(loss_D.detach() / batch_number)
+
+        def generator_step(batch):
+            # (:293-332)  `Variable(generator(noise))` in the reference is a detached leaf: the MMD gradient stops
+            # at U and the generator gets none.  Kept.
+            # The detector's (unused) gradients of this phase are dropped first so that a captured step allocates
+            # and frees them inside its own graph instead of accumulating into another graph's buffers.
+            det_optimizer.zero_grad()
+            enc, _ = detector(batch)
+            U = generator(noise.normal_()).detach().requires_grad_(True)
+            penc, _ = detector(U * batch)
+            for p in detector.parameters():
+                p.requires_grad = False
+            gen_optimizer.zero_grad()
+            loss_G = loss_function(enc, penc, U)
+            loss_G.backward()
+            gen_optimizer.step()
+            acc.add_(loss_G.detach() / batch_number)
+
+        run_detector = _GraphedStep(detector_step, use_graph, self._graph_warmup_steps)
+        run_generator = _GraphedStep(generator_step, use_graph, self._graph_warmup_steps)
         iternum_d = iternum_g = 1
         detector_loss = generator_loss = np.nan
         for epoch in range(self.epochs):
             print(f'\rEpoch {epoch} of {self.epochs}')
-            acc = torch.zeros((), device=self.device)
+            acc.zero_()
             if iternum_d <= self.iternum_d:
-                # ---- detector epoch: maximise MMD(enc, penc) - 0.1 (reconstruction terms)  (:251-291)
                 for batch in self._batches(Xd):
-                    for p in detector.parameters():
-                        p.requires_grad = True
-                    enc, dec = detector(batch)
-                    with torch.no_grad():
-                        U = generator(noise.normal_()).clone().detach()
-                    masked = U * batch
-                    penc, pdec = detector(masked)
-                    det_optimizer.zero_grad()
-                    loss_D = -(loss_function(enc, penc, U) - .1 * l2(batch, dec) - .1 * l2(masked, pdec))
-                    self.bandwidth = loss_function.bandwidth
-                    loss_D.backward()
-                    det_optimizer.step()
-                    acc += loss_D.detach() / batch_number
+                    run_detector(batch)
+                self.bandwidth = loss_function.bandwidth
                 detector_loss = float(acc)
                 iternum_d += 1
                 iternum_g = 1
             elif iternum_g <= self.iternum_g:
-                # ---- generator epoch (:293-332).  `Variable(generator(noise))` in the reference is a
-                # detached leaf: the MMD gradient stops at U and the generator gets none.  Kept.
                 for batch in self._batches(Xd):
-                    enc, _ = detector(batch)
-                    U = generator(noise.normal_()).detach().requires_grad_(True)
-                    penc, _ = detector(U * batch)
-                    for p in detector.parameters():
-                        p.requires_grad = False
-                    gen_optimizer.zero_grad()
-                    loss_G = loss_function(enc, penc, U)
-                    self.bandwidth = loss_function.bandwidth
-                    loss_G.backward()
-                    gen_optimizer.step()
-                    acc += loss_G.detach() / batch_number
+                    run_generator(batch)
+                self.bandwidth = loss_function.bandwidth
                 generator_loss = float(acc)
                 iternum_g += 1
                 if iternum_g > self.iternum_g:
@@ -265,6 +300,7 @@ class VGAN(_SubspaceGAN):
             print(f"Average loss in the epoch Detector: {detector_loss}")
             self.train_history["generator_loss"].append(generator_loss)
             self.train_history["detector_loss"].append(detector_loss)
+        self.used_cuda_graph = run_detector.graph is not None or run_generator.graph is not None
         self._save_run(generator, also_detector_slot=True)
         self.generator = generator
         self.detector = detector
@@ -306,8 +342,7 @@ class VGAN_no_kl(_SubspaceGAN):
         ndims = X.shape[1]
         self.batch_size = min(self.batch_size, X.shape[0])
         generator = self.get_the_networks(ndims, latent_size, device=self.device)
-        use_graph = (self.cuda_graph and self.device.type == 'cuda'
-                     and not os.environ.get('VGAN_B200_NO_GRAPH'))
+        use_graph = self._use_graph()
         optimizer = torch.optim.Adadelta(generator.parameters(), lr=self.lr, weight_decay=self.weight_decay,
                                          capturable=use_graph)
         self.generator_optimizer = optimizer.__class__.__name__
@@ -326,27 +361,18 @@ class VGAN_no_kl(_SubspaceGAN):
             optimizer.step()
             acc.add_(batch_loss.detach() / batch_number)
 
-        # The step (noise -> generator -> prologue -> fused MMD kernel -> backward -> Adadelta) is launch-bound at the
-        # reference's batch sizes (N = 500): after a few eager steps (bandwidth frozen, optimizer state and
-        # workspaces allocated) it is captured once into a CUDA graph and replayed per batch.
-        graph, static_batch, eager_steps = None, None, 0
+        # noise -> generator -> prologue -> fused MMD kernel -> backward -> Adadelta: captured into a CUDA graph after
+        # a few eager steps (bandwidth frozen, optimizer state and workspaces allocated), then replayed per batch
+        run_step = _GraphedStep(step, use_graph, self._graph_warmup_steps)
         for epoch in range(self.epochs):
             print(f'\rEpoch {epoch} of {self.epochs}')
             acc.zero_()
             for batch in self._batches(Xd):
-                if graph is not None:
-                    static_batch.copy_(batch)
-                    graph.replay()
-                    continue
-                step(batch)
-                eager_steps += 1
-                if use_graph and eager_steps == self._graph_warmup_steps:
-                    static_batch = torch.empty_like(batch)
-                    graph = self._capture_step(step, static_batch)
+                run_step(batch)
             self.bandwidth = loss_function.bandwidth
             generator_loss = float(acc)                 # one host sync per epoch
             print(f"Average loss in the epoch: {generator_loss}")
             self.train_history["generator_loss"].append(generator_loss)
-        self.used_cuda_graph = graph is not None
+        self.used_cuda_graph = run_step.graph is not None
         self._save_run(generator, also_detector_slot=False)
         self.generator = generator
