@@ -51,7 +51,7 @@ enum {
 /* Layout of the caller-provided workspace (all offsets in bytes from `ws`).
  * Z is the stacked sample [X ; Y] (Mmd_loss_constrained.py:43): X rows at [0,Nx),
  * zero rows up to Nxp (multiple of 128), Y rows at [Nxp, Nxp+Ny), zero rows up to
- * Nxp+Nyp; Dp = D rounded up to 64 with zero columns. */
+ * Nxp+Nyp; Dp = D rounded up to 64 with zero columns (to 128 on the bf16 path when D > 256). */
 typedef struct {
   int64_t Nx, Ny, D;
   int64_t Dp, Nxp, Nyp;

@@ -126,6 +126,10 @@ static int fill_layout(int64_t Nx, int64_t Ny, int64_t D, int64_t D_u, int flags
   memset(L, 0, sizeof(*L));
   L->Nx = Nx; L->Ny = Ny; L->D = D;
   L->Dp = (D + kChunk - 1) / kChunk * kChunk;
+  // bf16, more than one feature slice: an even chunk count, so that every slice is 2 or 4 chunks wide and the
+  // CTA-pair kernel (each CTA of a pair holds half a slice) serves every width; at most one extra zero chunk
+  if ((flags & VGAN_B200_PREC_MASK) != VGAN_B200_PREC_FP32 && L->Dp > kSliceMax)
+    L->Dp = (D + 2 * kChunk - 1) / (2 * kChunk) * (2 * kChunk);
   L->Nxp = (Nx + kTile - 1) / kTile * kTile;
   L->Nyp = (Ny + kTile - 1) / kTile * kTile;
   const size_t rows = static_cast<size_t>(L->Nxp + L->Nyp);
