@@ -44,6 +44,9 @@ enum {
   VGAN_B200_CENTER    = 2,      /* subtract the stacked column mean (distance invariant) */
   VGAN_B200_NEED_DX   = 4,      /* also produce dL/dX (VGAN.fit, vgan.py:283)           */
   VGAN_B200_LADDER    = 8,      /* scales are s, s/2, s/4, s/8, s/16: 1 ex2 + 4 squarings */
+  VGAN_B200_BF16X3    = 64,     /* with PREC_BF16: fp32-class results on the tensor cores.  Every operand value is split
+                                   z = hi + lo (two bf16), the Gram is hi.hi + hi.lo + lo.hi in ONE K = 3 D GEMM, the
+                                   gradient GEMM runs three passes (P_hi V_hi, P_hi V_lo, P_lo V_hi): ~6x the bf16 cost */
   VGAN_B200_NO_PAIR   = 32,     /* D > 256: 1-CTA cluster kernel instead of the cta_group::2 pair kernel */
   VGAN_B200_NO_CLUSTER = 16     /* D > 256: independent slice CTAs (Gram recomputed) instead of the cluster kernel */
 };
@@ -55,7 +58,8 @@ enum {
 typedef struct {
   int64_t Nx, Ny, D;
   int64_t Dp, Nxp, Nyp;
-  size_t off_zq;      /* bf16  [Nxp+Nyp, Dp]  (PREC_BF16)                                   */
+  size_t off_zq;      /* bf16  [Nxp+Nyp, Dp]  (PREC_BF16); with BF16X3 two arrays [Nxp+Nyp, 3 Dp] back to back:
+                         row operand [hi | hi | lo], then column operand [hi | lo | hi]                 */
   size_t off_zf;      /* float [Nxp+Nyp, Dp]  (PREC_FP32; same offset, one of the two exists) */
   size_t off_nrm;     /* float [Nxp+Nyp]  |z_i|^2 of the stored (rounded) rows; 1e30 on pads */
   size_t off_nrms;    /* float [Nxp+Nyp]  the same, scaled for the exp2 argument             */

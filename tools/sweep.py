@@ -1,4 +1,5 @@
-"""Config 2/3/5 sweep on one B200: fused fwd+bwd evaluations/s of vgan_b200 (bf16 and fp32 paths)
+"""Config 2/3/5 sweep on one B200: fused fwd+bwd evaluations/s of vgan_b200 (bf16, and the two fp32-class paths:
+bf16x3 = split operands on the tensor cores, simt = CUDA cores)
 next to torch-eager running the reference formula on the same GPU (where its [5,2N,2N] tensor
 fits).  Prints one JSON line per (N, D)."""
 import json, os, sys, time
@@ -25,8 +26,8 @@ def main():
         p = torch.softmax(torch.randn(N, D, device="cuda", generator=g), 1)
         U0 = torch.where(p < 1.0 / D, p, torch.ones_like(p))
         row = {"N": N, "D": D}
-        for prec in ("bf16", "fp32"):
-            if prec == "fp32" and N * N * D > 16384 * 16384 * 512: continue
+        for prec in ("bf16", "bf16x3", "simt"):
+            if prec == "simt" and N * N * D > 16384 * 16384 * 512: continue
             loss_fn = MMDLossConstrained(10.0, kernel=RBF(), precision=prec)
             U = U0.clone().requires_grad_()
             def step():

@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libvgan_b200.so")
 CSRC = os.path.join(HERE, "csrc")
 
-PREC_BF16, PREC_FP32, CENTER, NEED_DX, LADDER, NO_CLUSTER, NO_PAIR = 0, 1, 2, 4, 8, 16, 32
+PREC_BF16, PREC_FP32, CENTER, NEED_DX, LADDER, NO_CLUSTER, NO_PAIR, BF16X3 = 0, 1, 2, 4, 8, 16, 32, 64
 MAX_SCALES = 8
 
 EXPORTS = [

@@ -145,7 +145,8 @@ static int fill_layout(int64_t Nx, int64_t Ny, int64_t D, int64_t D_u, int flags
   L->off_xchg = off;  // before the operand: must not depend on D_u (callers pass D_u = 0 to recompute offsets)
   if (!fp32 && L->Dp > kSliceMax) off = align_up(off + static_cast<size_t>(kXchgSms) * kXchgBytesPerSm, 1024);
   L->off_zq = off;
-  L->off_zf = off;    off = align_up(off + rows * L->Dp * (fp32 ? 4 : 2), 1024);
+  const bool split = !fp32 && (flags & VGAN_B200_BF16X3);
+  L->off_zf = off;    off = align_up(off + rows * L->Dp * (fp32 ? 4 : (split ? 12 : 2)), 1024);
   L->off_cmax = off;  off = align_up(off + static_cast<size_t>(D_u > 0 ? D_u : 1) * 8, 1024);
 
   L->total = off;
@@ -272,12 +273,37 @@ int vgan_b200_mmd2_fwd_bwd(void* ws, int64_t Nx, int64_t Ny, int64_t D, int64_t 
   p.timeline = g_timeline;
   p.started = nullptr;
   p.dbg_flags = g_pair_variant >> 8;
-  CUtensorMap map;
-  if (int e = make_tmap_bf16_2d(&map, p.zq, static_cast<uint64_t>(L.Nxp + L.Nyp), static_cast<uint64_t>(L.Dp)))
-    return e;
+  // ---- operand arrays and their tensor maps.  Plain bf16: one array [rows, Dp] serves as row operand, column operand
+  // and V.  BF16X3: row operand [hi | hi | lo] and column operand [hi | lo | hi], both [rows, 3 Dp]; V = the hi or lo
+  // block of the row-operand array.
+  const bool split = (flags & VGAN_B200_BF16X3) != 0;
+  const uint64_t rows = static_cast<uint64_t>(L.Nxp + L.Nyp);
+  const uint64_t width = static_cast<uint64_t>(split ? 3 * L.Dp : L.Dp);
+  const __nv_bfloat16* zb = split ? p.zq + rows * width : p.zq;
+  p.gchunks = split ? 3 * p.kchunks : p.kchunks;
+  p.zq_stride = static_cast<int64_t>(width);
+  p.zq_lo = split ? p.zq + 2 * L.Dp : nullptr;
   const int ladder = (flags & VGAN_B200_LADDER) ? 1 : 0;
   p.cs = p.nslices < 4 ? p.nslices : 4;
   p.ngroups = (p.nslices + p.cs - 1) / p.cs;
+  const bool multi_slice = p.pv && p.nslices >= 2 && !(flags & VGAN_B200_NO_CLUSTER);
+  if (split && multi_slice && (flags & VGAN_B200_NO_PAIR)) {
+    set_error("mmd2_fwd_bwd: BF16X3 is not available on the NO_PAIR fallback kernel");
+    return VGAN_B200_ERR_UNSUPPORTED;
+  }
+  CUtensorMap map, mapB, mapV, mapB64, mapV64, mapB256;
+  if (int e = make_tmap_bf16_2d(&map, p.zq, rows, width)) return e;
+  if (int e = make_tmap_bf16_2d(&mapB, zb, rows, width)) return e;
+  mapV = map;
+  if (multi_slice) {
+    if (int e = make_tmap_bf16_2d(&mapB64, zb, rows, width, 64)) return e;
+    if (int e = make_tmap_bf16_2d(&mapV64, p.zq, rows, width, 64)) return e;
+    if (p.n_xx_units > 0)
+      if (int e = make_tmap_bf16_2d(&mapB256, zb, rows, width, 256)) return e;
+  }
+
+  // one pass of the tcgen05 kernels over this shard (BF16X3 runs three: see below)
+  auto run_pass = [&](TcParams& p, bool zero_outputs) -> int {
   if (p.pv && p.nslices >= 2 && !(flags & VGAN_B200_NO_CLUSTER)) {
     // D_p > 256: the slice CTAs of a row tile run as one thread-block cluster sharing P over DSMEM;
     // the S_xx-only units (no gradient GEMM, one slice) stay on the plain kernel.
@@ -303,13 +329,8 @@ int vgan_b200_mmd2_fwd_bwd(void* ws, int64_t Nx, int64_t Ny, int64_t D, int64_t 
       VG_CUDA_CHECK(cudaEventCreateWithFlags(&ev_join_hi, cudaEventDisableTiming));
     }
     cudaStream_t main_st = st;
-    CUtensorMap map256;
-    if (p.n_xx_units > 0)
-      if (int e = make_tmap_bf16_2d(&map256, p.zq, static_cast<uint64_t>(L.Nxp + L.Nyp), static_cast<uint64_t>(L.Dp),
-                                    256))
-        return e;
     const bool pair_ok = (p.kchunks % 4 == 0 || p.kchunks % 4 == 2) && !(flags & VGAN_B200_NO_PAIR);
-    if (pair_ok) {
+    if (pair_ok && zero_outputs) {
       // stream-K cuts a unit between two clusters: those rows are accumulated with red.global.add.  Zeroed BEFORE
       // the fork: a memset in front of the gradient kernel on its own stream lets the S_xx kernel start first and
       // occupy SMs the persistent clusters need (measured: the clusters then start up to 9 ms late).
@@ -334,21 +355,17 @@ int vgan_b200_mmd2_fwd_bwd(void* ws, int64_t Nx, int64_t Ny, int64_t D, int64_t 
       main_st = hi;
       if (xx_mode == 2) {      // measurement: S_xx kernel dispatched first
         VG_CUDA_CHECK(cudaStreamWaitEvent(side, ev_fork, 0));
-        if (int e = launch_xx(p, map, map256, ladder, side)) return e;
+        if (int e = launch_xx(p, map, mapB256, ladder, side)) return e;
       }
     }
     // full 128/256-wide slices: CTA pairs (cta_group::2) halve the shared-memory operand traffic
     if (pair_ok) {
-      CUtensorMap map64;
-      if (int e = make_tmap_bf16_2d(&map64, p.zq, static_cast<uint64_t>(L.Nxp + L.Nyp),
-                                    static_cast<uint64_t>(L.Dp), 64))
-        return e;
-      if (int e = launch_tc_pair(p, map, map64, ladder, main_st, &resident_ctas)) return e;
+      if (int e = launch_tc_pair(p, map, mapB64, mapV64, ladder, main_st, &resident_ctas)) return e;
     } else {
       if (int e = launch_tc_cluster(p, map, ladder, main_st)) return e;
     }
     if (p.n_xx_units == 0) return VGAN_B200_OK;
-    if (!overlap) return launch_xx(p, map, map256, ladder, st);
+    if (!overlap) return launch_xx(p, map, mapB256, ladder, st);
     if (xx_mode != 2) {
       VG_CUDA_CHECK(cudaStreamWaitEvent(side, ev_fork, 0));
       int free_sms = 0;
@@ -368,7 +385,7 @@ int vgan_b200_mmd2_fwd_bwd(void* ws, int64_t Nx, int64_t Ny, int64_t D, int64_t 
       } else {
         free_sms = 0;       // no room beside the clusters: plain low-priority launch over all SMs
       }
-      if (int e = launch_xx(p, map, map256, ladder, side, free_sms)) return e;
+      if (int e = launch_xx(p, map, mapB256, ladder, side, free_sms)) return e;
     }
     VG_CUDA_CHECK(cudaEventRecord(ev_join, side));
     VG_CUDA_CHECK(cudaEventRecord(ev_join_hi, hi));
@@ -376,7 +393,27 @@ int vgan_b200_mmd2_fwd_bwd(void* ws, int64_t Nx, int64_t Ny, int64_t D, int64_t 
     VG_CUDA_CHECK(cudaStreamWaitEvent(st, ev_join_hi, 0));
     return VGAN_B200_OK;
   }
-  return launch_tc(p, map, ladder, st);
+  return launch_tc(p, map, mapB, mapV, ladder, st);
+  };
+  if (!split) return run_pass(p, true);
+  // BF16X3: O = P_hi V_hi + P_hi V_lo + P_lo V_hi, one pass each into zeroed outputs; pass 1 also produces the kernel
+  // sums and the rowsum(P) z_i term, the S_xx units run once beside it
+  if (p.pv) {
+    if (ye > row_begin)
+      VG_CUDA_CHECK(cudaMemsetAsync(dY, 0, static_cast<size_t>(ye - row_begin) * D * sizeof(float), st));
+    if (need_dx && xe > row_begin)
+      VG_CUDA_CHECK(cudaMemsetAsync(dX, 0, static_cast<size_t>(xe - row_begin) * D * sizeof(float), st));
+  }
+  p.pass_flags = kPassAccumulate;
+  p.v_chunk0 = 0; p.p_lo = 0;
+  if (int e = run_pass(p, false)) return e;
+  if (!p.pv) return VGAN_B200_OK;
+  p.n_xx_units = 0;
+  p.pass_flags = kPassAccumulate | kPassNoSums | kPassNoRowsum;
+  p.v_chunk0 = 2 * p.kchunks; p.p_lo = 0;
+  if (int e = run_pass(p, false)) return e;
+  p.v_chunk0 = 0; p.p_lo = 1;
+  return run_pass(p, false);
 }
 
 int vgan_b200_colmax_penalty(const float* U, int64_t N, int64_t D_u, float weight, void* scratch,

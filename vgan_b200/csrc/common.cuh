@@ -23,6 +23,7 @@ constexpr float kLog2e = 1.4426950408889634f;
 // par[2 + m]  = inv_s[m] / inv_s[ref]      (general path exponent ratios)
 // par[10 + m] = cx * inv_s[m]              (P coefficients for X columns, cx = +1/Nx)
 // par[18 + m] = cy * inv_s[m]              (P coefficients for Y columns, cy = -1/Ny)
+constexpr int kPassNoSums = 1, kPassNoRowsum = 2, kPassAccumulate = 4;
 constexpr int kParFloats = 32;
 constexpr int kParStartedOffset = 512;   // byte offset in the (1 KiB) parameter block of the pair kernel's "CTAs started" counter
 constexpr int kXxMinFreeSms = 8;         // fewer SMs left free by the gradient clusters: S_xx runs over all SMs at low priority instead
@@ -33,7 +34,11 @@ constexpr int kXchgBytesPerSm = 3 * 2 * kChunkBytes;
 
 struct TcParams {
   int tiles_x, tiles_y;       // 128-row tiles in the X / Y regions of the stacked operand
-  int kchunks;                // Dp / 64
+  int kchunks;                // Dp / 64 (feature chunks: slices, O columns, V operand)
+  int gchunks;                // K chunks of the Gram GEMM: kchunks, or 3 * kchunks with split operands (BF16X3)
+  int v_chunk0;               // chunk offset of the V operand inside its array (split: hi block 0, lo block 2 * kchunks)
+  int p_lo;                   // 1: the P operand is the bf16 remainder P - bf16(P) (third pass of BF16X3)
+  int pass_flags;             // kPassNoSums | kPassNoRowsum | kPassAccumulate (passes 2, 3 of BF16X3)
   int nslices, slice_chunks;  // output feature slices per row tile, chunks per (full) slice
   int cs, ngroups;            // cluster kernel: CTAs per cluster, slice groups (clusters) per row tile
   int gx_begin, gx_end;       // X row tiles that need a gradient (NEED_DX), else empty
@@ -44,7 +49,9 @@ struct TcParams {
   int n_scales;
   int64_t Nx, Ny, D, Dp;
   int64_t row_begin, row_end; // gradient row range (rows of Y, and of X with NEED_DX)
-  const __nv_bfloat16* zq;    // stacked operand (for the final z_i read)
+  const __nv_bfloat16* zq;    // stacked operand (for the final z_i read), row stride zq_stride
+  const __nv_bfloat16* zq_lo; // split operands: the low halves (z_i = hi + lo), same stride; else nullptr
+  int64_t zq_stride;
   const float* nrms;          // scaled norms
   const float* par;           // parameter block
   double* sums;
@@ -73,12 +80,15 @@ void set_error(const char* fmt, ...);
 int check_device();   // 0 when the current device is compute capability 10.x
 
 // kernels' host launchers (defined in their own .cu files)
-int launch_tc(const TcParams& p, const CUtensorMap& map, int ladder, cudaStream_t st);
+// map = row operand (A), mapB = column operand of the Gram, mapV = value operand of the gradient GEMM; the three are
+// the same array on the plain bf16 path and differ with split operands (BF16X3, see prologue.cu)
+int launch_tc(const TcParams& p, const CUtensorMap& map, const CUtensorMap& mapB, const CUtensorMap& mapV, int ladder,
+              cudaStream_t st);
 int launch_xx(const TcParams& p, const CUtensorMap& map, const CUtensorMap& map256, int ladder, cudaStream_t st,
               int max_ctas = 0);
 int launch_tc_cluster(const TcParams& p, const CUtensorMap& map, int ladder, cudaStream_t st);
-int launch_tc_pair(const TcParams& p, const CUtensorMap& map, const CUtensorMap& map64, int ladder, cudaStream_t st,
-                   int* resident_ctas = nullptr);
+int launch_tc_pair(const TcParams& p, const CUtensorMap& map, const CUtensorMap& mapB64, const CUtensorMap& mapV64,
+                   int ladder, cudaStream_t st, int* resident_ctas = nullptr);
 int launch_probe(const CUtensorMap& mapA, const CUtensorMap& mapB, float* S_out, float* O_out,
                  cudaStream_t st);
 int make_tmap_bf16_2d(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint32_t box_rows = 128);

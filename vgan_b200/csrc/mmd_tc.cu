@@ -83,7 +83,8 @@ __device__ __forceinline__ Unit decode_unit(const TcParams& p) {
 
 template <bool LADDER>
 __global__ void __launch_bounds__(kThreads, 1)
-mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const TcParams p) {
+mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__ CUtensorMap zmapB,
+               const __grid_constant__ CUtensorMap zmapV, const TcParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];   // SWIZZLE_128B tiles need 1024-byte alignment
   if ((smem_u32(smem) & 1023u) != 0) __trap();
   TcBarriers* bar = reinterpret_cast<TcBarriers*>(smem + kSmemBar);
@@ -95,7 +96,6 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const TcParams p) {
   const int n_tiles = u.j_end - u.j_begin;
   const int slice_chunks =
       min(p.slice_chunks, p.kchunks - u.slice * p.slice_chunks);  // chunks in this slice
-  const int slice_w = slice_chunks * kChunk;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kStages; ++s) {
@@ -116,7 +116,11 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const TcParams p) {
     tmem_alloc(&bar->tmem_base, 512);
     tmem_relinquish();
   }
-  if (warp == 8 && lane == 0) tma_prefetch_desc(&zmap);
+  if (warp == 8 && lane == 0) {
+    tma_prefetch_desc(&zmap);
+    tma_prefetch_desc(&zmapB);
+    tma_prefetch_desc(&zmapV);
+  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -133,12 +137,12 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const TcParams p) {
       for (int n = 0; n <= n_tiles; ++n) {
         if (n < n_tiles) {
           const int jt = u.j_begin + n;
-          for (int kc = 0; kc < p.kchunks; ++kc) {
+          for (int kc = 0; kc < p.gchunks; ++kc) {
             mbar_wait(&bar->ring_empty[s], ph ^ 1);
             uint8_t* dst = smem + kSmemRing + s * kStageBytes;
             mbar_arrive_expect_tx(&bar->ring_full[s], kStageBytes);
             tma_load_2d(dst, &zmap, &bar->ring_full[s], kc * kChunk, u.ti * kTile);
-            tma_load_2d(dst + kChunkBytes, &zmap, &bar->ring_full[s], kc * kChunk, jt * kTile);
+            tma_load_2d(dst + kChunkBytes, &zmapB, &bar->ring_full[s], kc * kChunk, jt * kTile);
             if (++s == kStages) { s = 0; ph ^= 1; }
           }
         }
@@ -150,8 +154,8 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const TcParams p) {
             uint8_t* dst = smem + kSmemRing + s * kStageBytes;
             mbar_arrive_expect_tx(&bar->ring_full[s], nch * kChunkBytes);
             for (int c = 0; c < nch; ++c)
-              tma_load_2d(dst + c * kChunkBytes, &zmap, &bar->ring_full[s],
-                          (u.slice * p.slice_chunks + 2 * h + c) * kChunk, jt * kTile);
+              tma_load_2d(dst + c * kChunkBytes, &zmapV, &bar->ring_full[s],
+                          (p.v_chunk0 + u.slice * p.slice_chunks + 2 * h + c) * kChunk, jt * kTile);
             if (++s == kStages) { s = 0; ph ^= 1; }
           }
         }
@@ -188,7 +192,7 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const TcParams p) {
         mbar_wait(&bar->s_empty[b], ((n >> 1) & 1) ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem + b * kTile;
-        for (int kc = 0; kc < p.kchunks; ++kc) {
+        for (int kc = 0; kc < p.gchunks; ++kc) {
           mbar_wait(&bar->ring_full[s], ph);
           tc_fence_after();
           const uint32_t a_lo = ring_lo + s * (kStageBytes >> 4);
@@ -272,7 +276,8 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const TcParams p) {
       const float* njp = nj_smem + b * kTile + g * 64;
       float ksum = 0.f;
       uint4 pk[8];
-      epi_tile_64<LADDER>(tmem + lane_addr + b * kTile + g * 64, njp, ni, m2c0, cf, ratio, p.n_scales, ksum, rsum, pk);
+      epi_tile_64<LADDER>(tmem + lane_addr + b * kTile + g * 64, njp, ni, m2c0, cf, ratio, p.n_scales, ksum, rsum, pk,
+                          p.p_lo != 0);
       if (u.pv) {
         mbar_wait(&bar->p_empty[b], ((n >> 1) & 1) ^ 1);   // PV(n-2) done with P[b]
 #pragma unroll
@@ -299,7 +304,7 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const TcParams p) {
     asm volatile("bar.sync 1, 256;" ::: "memory");   // every epilogue warp is done reading the norms
     nj_smem[g * kTile + row] = rsum;                  // ... so their buffer can carry the row-sum exchange
     asm volatile("bar.sync 1, 256;" ::: "memory");
-    if (threadIdx.x == 0 && u.slice == 0) {
+    if (threadIdx.x == 0 && u.slice == 0 && !(p.pass_flags & kPassNoSums)) {
       double sx = 0.0, sy = 0.0;
       for (int wv = 0; wv < 8; ++wv) {
         sx += bar->red[wv][0];
@@ -316,40 +321,9 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const TcParams p) {
     // ---- gradient rows: dZ_i[slice] = 4 c_i (O_i - rowsum(P)_i z_i)  (x dY_mul)
     if (u.pv) {
       const float rtot = nj_smem[row] + nj_smem[kTile + row];
-      const int64_t region_row = static_cast<int64_t>(u.row_is_x ? u.ti : u.ti - p.tiles_x) * kTile + row;
-      const int64_t n_region = u.row_is_x ? p.Nx : p.Ny;
-      const bool row_ok = region_row < n_region && region_row >= p.row_begin && region_row < p.row_end;
-      const float ci4 = 4.f * (u.row_is_x ? 1.f / static_cast<float>(p.Nx) : -1.f / static_cast<float>(p.Ny));
-      float* out = (u.row_is_x ? p.dX : p.dY) + (region_row - p.row_begin) * p.D;
-      const float* mul = (!u.row_is_x && p.dY_mul) ? p.dY_mul + (region_row - p.row_begin) * p.D : nullptr;
-      const __nv_bfloat16* zrow = p.zq + (static_cast<int64_t>(u.ti) * kTile + row) * p.Dp;
-      const int f_slice = u.slice * p.slice_chunks * kChunk;
       mbar_wait(&bar->o_full, 0);
       tc_fence_after();
-      for (int cc = 0; cc < slice_chunks; ++cc) {
-        const int col = g * (slice_w / 2) + cc * 32;
-        uint32_t v[32];
-        tmem_ld_32x32(tmem_o + lane_addr + col, v);
-        tmem_ld_wait();
-        if (row_ok) {
-          const uint4* z4 = reinterpret_cast<const uint4*>(zrow + f_slice + col);
-#pragma unroll
-          for (int c = 0; c < 4; ++c) {
-            const uint4 zz = z4[c];
-            const uint32_t zw[4] = {zz.x, zz.y, zz.z, zz.w};
-#pragma unroll
-            for (int e = 0; e < 8; ++e) {
-              const float z = __uint_as_float((e & 1) ? (zw[e >> 1] & 0xffff0000u) : (zw[e >> 1] << 16));
-              const int f = f_slice + col + c * 8 + e;
-              if (f < p.D) {
-                float gval = ci4 * (__uint_as_float(v[c * 8 + e]) - rtot * z);
-                if (mul) gval *= mul[f];
-                out[f] = gval;
-              }
-            }
-          }
-        }
-      }
+      write_grad_rows(p, tmem_o, lane_addr, g, row, u.ti, u.row_is_x, u.slice, slice_chunks, rtot);
     }
   }
 
@@ -358,13 +332,14 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const TcParams p) {
   if (warp == 11) tmem_dealloc(tmem, 512);
 }
 
-int launch_tc(const TcParams& p, const CUtensorMap& map, int ladder, cudaStream_t st) {
+int launch_tc(const TcParams& p, const CUtensorMap& map, const CUtensorMap& mapB, const CUtensorMap& mapV, int ladder,
+              cudaStream_t st) {
   const int ngrad = (p.gx_end - p.gx_begin) + (p.gy_end - p.gy_begin);
   const int grid = ngrad * p.nslices + p.n_xx_units;
   if (grid <= 0) return VGAN_B200_OK;
   auto kern = ladder ? mmd2_tc_kernel<true> : mmd2_tc_kernel<false>;
   VG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
-  kern<<<grid, kThreads, kSmemTotal, st>>>(map, p);
+  kern<<<grid, kThreads, kSmemTotal, st>>>(map, mapB, mapV, p);
   VG_CUDA_CHECK(cudaGetLastError());
   return VGAN_B200_OK;
 }

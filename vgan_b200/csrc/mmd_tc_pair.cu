@@ -89,7 +89,9 @@ static_assert(kQSmemV % 1024 == 0 && kQSmemP % 1024 == 0, "operand tiles need 10
 template <bool LADDER>
 __global__ void __launch_bounds__(kQThreads, 1)
 mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__ CUtensorMap zmap64,
-                    const TcParams p) {
+                    const __grid_constant__ CUtensorMap vmap64, const TcParams p) {
+  // zmap: row operand (128-row boxes), zmap64: Gram column operand (64-row boxes), vmap64: V operand of the gradient
+  // GEMM (64-row boxes); one array on the plain bf16 path, the split arrays of prologue.cu with BF16X3
   extern __shared__ __align__(1024) uint8_t smem[];
   if ((smem_u32(smem) & 1023u) != 0) __trap();
   PairBarriers* bar = reinterpret_cast<PairBarriers*>(smem + kQSmemBar);
@@ -155,6 +157,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
   if (warp == 8 && lane == 0) {
     tma_prefetch_desc(&zmap);
     tma_prefetch_desc(&zmap64);
+    tma_prefetch_desc(&vmap64);
   }
   tc_fence_before();
   cluster_sync_all();          // peers' barriers are initialised before any remote arrive / copy
@@ -188,7 +191,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     const uint32_t pj = warp == 8 ? 0u : 1u;
     for (int k = 0; k < Kp; ++k) {
       const int jt = min(tile0 + CS * k + c, T - 1);
-      for (int kc = 0; kc < p.kchunks; ++kc) {
+      for (int kc = 0; kc < p.gchunks; ++kc) {
         if ((rs & (kGProducers - 1)) == pj) {
           mbar_wait(&bar->g_empty[rs], rph ^ 1);
           uint8_t* dst = smem + kQSmemG + rs * kGStageBytes;
@@ -218,8 +221,9 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
           } else {
             if (lane == 0 && hh == 0) mbar_arrive_expect_tx(&bar->v_full[rs], slice_chunks * (kChunkBytes / 2));
             if (lane < my_chunks)
-              tma_load_2d_2cta(dst + lane * (kChunkBytes / 2), &zmap64, &bar->v_full[rs],
-                               (slice * p.slice_chunks + hh * my_chunks + lane) * kChunk, jt * kTile + 64 * h);
+              tma_load_2d_2cta(dst + lane * (kChunkBytes / 2), &vmap64, &bar->v_full[rs],
+                               (p.v_chunk0 + slice * p.slice_chunks + hh * my_chunks + lane) * kChunk,
+                               jt * kTile + 64 * h);
           }
           __syncwarp();
           if (++rs == kVStages) { rs = 0; rph ^= 1; }
@@ -305,7 +309,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
         tm1 += clock64() - t0;
       }
       tc_fence_after();
-      for (int kc = 0; kc < p.kchunks; ++kc) {
+      for (int kc = 0; kc < p.gchunks; ++kc) {
         {
           const long long t0 = clock64();
           mbar_wait(&bar->g_full[rs], rph);
@@ -322,7 +326,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
             umma_bf16_ss_2cta(d_tmem, adesc, bdesc, idesc_gram, (kc | kk) != 0);
           }
           umma_commit_2cta_mc(&bar->g_empty[rs], pair_mask);
-          if (kc == p.kchunks - 1) umma_commit_2cta_mc(&bar->s_full[b], pair_mask);
+          if (kc == p.gchunks - 1) umma_commit_2cta_mc(&bar->s_full[b], pair_mask);
         }
         __syncwarp();
         if (++rs == kGStages) { rs = 0; rph ^= 1; }
@@ -426,7 +430,8 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
       const float* njp = nj_smem + b * kTile + g * 64;
       float ksum = 0.f;
       uint4 pk[8];
-      epi_tile_64<LADDER>(tmem + lane_addr + b * kTile + g * 64, njp, ni, m2c0, cf, ratio, p.n_scales, ksum, rsum, pk);
+      epi_tile_64<LADDER>(tmem + lane_addr + b * kTile + g * 64, njp, ni, m2c0, cf, ratio, p.n_scales, ksum, rsum, pk,
+                          p.p_lo != 0);
       tc_fence_before();
       mbar_arrive(&bar->s_empty[b]);          // S and the norms are free; P is parked in registers
       if (hh == 1) mbar_remote_arrive(mapa_u32(smem_u32(&bar->s_empty[b]), static_cast<uint32_t>(rank - 1)));
@@ -458,7 +463,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     if (lane == 0) { bar->red[warp][0] = acc_x; bar->red[warp][1] = acc_y; }
     asm volatile("bar.sync 1, 256;" ::: "memory");   // all epilogue warps are done with the norms
     nj_smem[g * kTile + row] = rsum;
-    if (threadIdx.x == 0 && grp == 0 && !dup) {
+    if (threadIdx.x == 0 && grp == 0 && !dup && !(p.pass_flags & kPassNoSums)) {
       double sx = 0.0, sy = 0.0;
       for (int wv = 0; wv < 8; ++wv) { sx += bar->red[wv][0]; sy += bar->red[wv][1]; }
       if (row_is_x) {
@@ -523,8 +528,8 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
 
 int g_pair_variant = 0;   // tuning/measurement: vgan_b200_debug_variant() (bits >= 8 -> TcParams::dbg_flags)
 
-int launch_tc_pair(const TcParams& p, const CUtensorMap& map, const CUtensorMap& map64, int ladder,
-                   cudaStream_t st, int* resident_ctas) {
+int launch_tc_pair(const TcParams& p, const CUtensorMap& map, const CUtensorMap& map64, const CUtensorMap& mapV64,
+                   int ladder, cudaStream_t st, int* resident_ctas) {
   if (resident_ctas) *resident_ctas = 0;
   const int ngrad = (p.gx_end - p.gx_begin) + (p.gy_end - p.gy_begin);
   if (ngrad <= 0) return VGAN_B200_OK;
@@ -558,7 +563,7 @@ int launch_tc_pair(const TcParams& p, const CUtensorMap& map, const CUtensorMap&
   const int n_clusters = (persist && cap < n_units) ? cap : n_units;
   cfg.gridDim = dim3(static_cast<unsigned>(n_clusters * 2 * p.cs));
   if (resident_ctas) *resident_ctas = (n_clusters < ncl ? n_clusters : ncl) * 2 * p.cs;
-  VG_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, map, map64, p));
+  VG_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, map, map64, mapV64, p));
   return VGAN_B200_OK;
 }
 

@@ -158,7 +158,7 @@ mmd2_xx_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__
     for (int it = 0; it < nq; ++it, w.advance()) {
       const int jrow = w.q * 2 * kTile;
       const int ti = w.ti;
-      for (int kc = 0; kc < p.kchunks; ++kc) {
+      for (int kc = 0; kc < p.gchunks; ++kc) {
         if ((s & 1u) == pj) {
           mbar_wait(&bar->ring_empty[s], ph ^ 1);
           uint8_t* dst = smem + s * kXStageBytes;
@@ -196,7 +196,7 @@ mmd2_xx_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__
       mbar_wait(&bar->s_empty[b], ((it >> 1) & 1) ^ 1);
       tc_fence_after();
       const uint32_t d_tmem = tmem + b * 2 * kTile;
-      for (int kc = 0; kc < p.kchunks; ++kc) {
+      for (int kc = 0; kc < p.gchunks; ++kc) {
         mbar_wait(&bar->ring_full[s], ph);
         tc_fence_after();
         const uint32_t a_lo = ring_lo + s * (kXStageBytes >> 4);
@@ -209,7 +209,7 @@ mmd2_xx_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__
             umma_bf16_ss(d_tmem, adesc, bdesc, idesc, (kc | kk) != 0);
           }
           umma_commit(&bar->ring_empty[s]);
-          if (kc == p.kchunks - 1) umma_commit(&bar->s_full[b]);
+          if (kc == p.gchunks - 1) umma_commit(&bar->s_full[b]);
         }
         __syncwarp();
         if (++s == kXStages) { s = 0; ph ^= 1; }

@@ -13,8 +13,10 @@ struct PackArgs {
   const float* U;   // mask (Y = U*X) when Y == nullptr
   const float* Y;
   int64_t Nx, Ny, D, Dp, Nxp, Nyp;
-  int center, fp32;
+  int center, fp32, split;
   __nv_bfloat16* zq;
+  __nv_bfloat16* zb;    // split operands (BF16X3): zq = row operand [hi | hi | lo], zb = column operand [hi | lo | hi],
+                        // both [rows, 3 Dp]: sum_k zq[i,k] zb[j,k] = hi_i.hi_j + hi_i.lo_j + lo_i.hi_j
   float* zf;
   float* nrm;
   float* mean;
@@ -77,6 +79,15 @@ __global__ void __launch_bounds__(256) pack_kernel(PackArgs a) {
     if (a.fp32) {
       a.zf[r * a.Dp + f] = z;
       nrm = fmaf(z, z, nrm);
+    } else if (a.split) {
+      const __nv_bfloat16 hi = __float2bfloat16_rn(z);
+      const float zh = __bfloat162float(hi);
+      const __nv_bfloat16 lo = __float2bfloat16_rn(z - zh);
+      const float zr = zh + __bfloat162float(lo);          // the value the three products represent (16 bits)
+      const int64_t o = r * 3 * a.Dp + f;
+      a.zq[o] = hi; a.zq[o + a.Dp] = hi; a.zq[o + 2 * a.Dp] = lo;
+      a.zb[o] = hi; a.zb[o + a.Dp] = lo; a.zb[o + 2 * a.Dp] = hi;
+      nrm = fmaf(zr, zr, nrm);
     } else {
       const __nv_bfloat16 q = __float2bfloat16_rn(z);
       a.zq[r * a.Dp + f] = q;
@@ -236,7 +247,9 @@ int run_prologue(const float* X, const float* U, const float* Y, const vgan_b200
   a.Nx = L.Nx; a.Ny = L.Ny; a.D = L.D; a.Dp = L.Dp; a.Nxp = L.Nxp; a.Nyp = L.Nyp;
   a.center = (flags & VGAN_B200_CENTER) ? 1 : 0;
   a.fp32 = (flags & VGAN_B200_PREC_MASK) == VGAN_B200_PREC_FP32;
+  a.split = (!a.fp32 && (flags & VGAN_B200_BF16X3)) ? 1 : 0;
   a.zq = reinterpret_cast<__nv_bfloat16*>(base + L.off_zq);
+  a.zb = a.zq + static_cast<size_t>(L.Nxp + L.Nyp) * 3 * L.Dp;
   a.zf = reinterpret_cast<float*>(base + L.off_zf);
   a.nrm = reinterpret_cast<float*>(base + L.off_nrm);
   a.mean = reinterpret_cast<float*>(base + L.off_mean);
@@ -244,7 +257,7 @@ int run_prologue(const float* X, const float* U, const float* Y, const vgan_b200
   VG_CUDA_CHECK(cudaMemsetAsync(a.stats, 0, sizeof(double) * (2 + L.Dp), st));
   const int64_t n = L.Nx + L.Ny;
   const int rpb = 64;
-  const bool masked_fast = !Y && U && !a.fp32 && L.Nx == L.Ny && (L.D & 3) == 0 &&
+  const bool masked_fast = !Y && U && !a.fp32 && !a.split && L.Nx == L.Ny && (L.D & 3) == 0 &&
                            ((reinterpret_cast<uintptr_t>(X) | reinterpret_cast<uintptr_t>(U)) & 15) == 0;
   if (masked_fast) {
     const int rpb2 = 32;

@@ -10,7 +10,7 @@ template <bool LADDER>
 __device__ __forceinline__ void epi_compute_32(const uint32_t (&v)[32], const float* __restrict__ njp, float ni,
                                                     float m2c0, const float (&cf)[VGAN_B200_MAX_SCALES],
                                                     const float (&ratio)[VGAN_B200_MAX_SCALES], int n_scales,
-                                                    float& ksum, float& rsum, uint4 (&pk)[4]) {
+                                                    float& ksum, float& rsum, uint4 (&pk)[4], bool plo = false) {
   if constexpr (LADDER) {
     // two columns per issue slot (packed f32x2): ~11.5 instead of ~19.5 instructions per pair
     const uint64_t m2 = f2_pack(m2c0, m2c0), ni2 = f2_pack(ni, ni);
@@ -39,6 +39,8 @@ __device__ __forceinline__ void epi_compute_32(const uint32_t (&v)[32], const fl
         float w0, w1;
         f2_unpack(w2, w0, w1);
         pw[q] = pack_bf16x2(w0, w1);
+        if (plo)      // split-operand pass 3: the remainder of P after its bf16 rounding
+          pw[q] = pack_bf16x2(w0 - __uint_as_float(pw[q] << 16), w1 - __uint_as_float(pw[q] & 0xffff0000u));
       }
       pk[c].x = pw[0]; pk[c].y = pw[1]; pk[c].z = pw[2]; pk[c].w = pw[3];
     }
@@ -68,10 +70,14 @@ __device__ __forceinline__ void epi_compute_32(const uint32_t (&v)[32], const fl
       w[e] = ww;
       rsum += w[e];
     }
-    pk[c].x = pack_bf16x2(w[0], w[1]);
-    pk[c].y = pack_bf16x2(w[2], w[3]);
-    pk[c].z = pack_bf16x2(w[4], w[5]);
-    pk[c].w = pack_bf16x2(w[6], w[7]);
+    uint32_t pw[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      pw[q] = pack_bf16x2(w[2 * q], w[2 * q + 1]);
+      if (plo)
+        pw[q] = pack_bf16x2(w[2 * q] - __uint_as_float(pw[q] << 16), w[2 * q + 1] - __uint_as_float(pw[q] & 0xffff0000u));
+    }
+    pk[c].x = pw[0]; pk[c].y = pw[1]; pk[c].z = pw[2]; pk[c].w = pw[3];
   }
   }
 }
@@ -84,11 +90,11 @@ template <bool LADDER>
 __device__ __forceinline__ void epi_half_tile(uint32_t taddr, const float* __restrict__ njp, float ni,
                                               float m2c0, const float (&cf)[VGAN_B200_MAX_SCALES],
                                               const float (&ratio)[VGAN_B200_MAX_SCALES], int n_scales,
-                                              float& ksum, float& rsum, uint4 (&pk)[4]) {
+                                              float& ksum, float& rsum, uint4 (&pk)[4], bool plo = false) {
   uint32_t v[32];
   tmem_ld_32x32(taddr, v);
   tmem_ld_wait();
-  epi_compute_32<LADDER>(v, njp, ni, m2c0, cf, ratio, n_scales, ksum, rsum, pk);
+  epi_compute_32<LADDER>(v, njp, ni, m2c0, cf, ratio, n_scales, ksum, rsum, pk, plo);
 }
 
 // 64 columns: both TMEM loads are issued before the single wait, so their latencies overlap
@@ -96,14 +102,14 @@ template <bool LADDER>
 __device__ __forceinline__ void epi_tile_64(uint32_t taddr, const float* __restrict__ njp, float ni, float m2c0,
                                             const float (&cf)[VGAN_B200_MAX_SCALES],
                                             const float (&ratio)[VGAN_B200_MAX_SCALES], int n_scales,
-                                            float& ksum, float& rsum, uint4 (&pk)[8]) {
+                                            float& ksum, float& rsum, uint4 (&pk)[8], bool plo = false) {
   uint32_t va[32], vb[32];
   tmem_ld_32x32(taddr, va);
   tmem_ld_32x32(taddr + 32, vb);
   tmem_ld_wait();
   uint4 h0[4], h1[4];
-  epi_compute_32<LADDER>(va, njp, ni, m2c0, cf, ratio, n_scales, ksum, rsum, h0);
-  epi_compute_32<LADDER>(vb, njp + 32, ni, m2c0, cf, ratio, n_scales, ksum, rsum, h1);
+  epi_compute_32<LADDER>(va, njp, ni, m2c0, cf, ratio, n_scales, ksum, rsum, h0, plo);
+  epi_compute_32<LADDER>(vb, njp + 32, ni, m2c0, cf, ratio, n_scales, ksum, rsum, h1, plo);
 #pragma unroll
   for (int i = 0; i < 4; ++i) { pk[i] = h0[i]; pk[4 + i] = h1[i]; }
 }
@@ -121,7 +127,11 @@ __device__ __forceinline__ void write_grad_rows(const TcParams& p, uint32_t tmem
   const float ci4 = 4.f * (row_is_x ? 1.f / static_cast<float>(p.Nx) : -1.f / static_cast<float>(p.Ny));
   float* out = (row_is_x ? p.dX : p.dY) + (region_row - p.row_begin) * p.D;
   const float* mul = (!row_is_x && p.dY_mul) ? p.dY_mul + (region_row - p.row_begin) * p.D : nullptr;
-  const __nv_bfloat16* zrow = p.zq + (static_cast<int64_t>(ti) * kTile + row) * p.Dp;
+  const int64_t zoff = (static_cast<int64_t>(ti) * kTile + row) * p.zq_stride;
+  const __nv_bfloat16* zrow = p.zq + zoff;
+  const __nv_bfloat16* zrow_lo = p.zq_lo ? p.zq_lo + zoff : nullptr;
+  if (p.pass_flags & kPassNoRowsum) rtot = 0.f;
+  accumulate = accumulate || (p.pass_flags & kPassAccumulate);
   const int f_slice = slice * p.slice_chunks * kChunk;
   const bool vec_ok = !accumulate && (p.D & 3) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0 &&
                       (!mul || (reinterpret_cast<uintptr_t>(mul) & 15) == 0);
@@ -136,10 +146,14 @@ __device__ __forceinline__ void write_grad_rows(const TcParams& p, uint32_t tmem
       for (int c = 0; c < 4; ++c) {
         const uint4 zz = z4[c];
         const uint32_t zw[4] = {zz.x, zz.y, zz.z, zz.w};
+        uint4 zl = make_uint4(0u, 0u, 0u, 0u);
+        if (zrow_lo) zl = reinterpret_cast<const uint4*>(zrow_lo + f_slice + col)[c];
+        const uint32_t zlw[4] = {zl.x, zl.y, zl.z, zl.w};
         float gv[8];
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
-          const float z = __uint_as_float((e & 1) ? (zw[e >> 1] & 0xffff0000u) : (zw[e >> 1] << 16));
+          const float z = __uint_as_float((e & 1) ? (zw[e >> 1] & 0xffff0000u) : (zw[e >> 1] << 16)) +
+                          __uint_as_float((e & 1) ? (zlw[e >> 1] & 0xffff0000u) : (zlw[e >> 1] << 16));
           gv[e] = ci4 * (__uint_as_float(v[c * 8 + e]) - rtot * z);
         }
         const int f0 = f_slice + col + c * 8;

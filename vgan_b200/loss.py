@@ -63,7 +63,8 @@ _ws_cache = {}
 
 
 def _workspace(Nx, Ny, D, D_u, flags, device) -> _Workspace:
-    key = (Nx, Ny, D, D_u, flags & _lib.PREC_FP32, str(device), torch.cuda.current_stream().cuda_stream)
+    key = (Nx, Ny, D, D_u, flags & (_lib.PREC_FP32 | _lib.BF16X3), str(device),
+           torch.cuda.current_stream().cuda_stream)
     ws = _ws_cache.get(key)
     if ws is None:
         if len(_ws_cache) > 16:
@@ -76,6 +77,19 @@ def default_precision(D: int) -> str:
     """bf16 tensor-core path by default; tiny feature widths (the VGAN encodings,
     latent = D//16) go to the fp32 CUDA-core path where a 64-wide K chunk would be padding."""
     return "fp32" if D < 32 else "bf16"
+
+
+def _precision_flags(precision: str, D: int) -> int:
+    """"bf16": bf16 operands on the tensor cores (2e-3).  "fp32": fp32-class results (1e-4) — the CUDA-core kernel up
+    to D = 256, split bf16 operands on the tensor cores ("bf16x3") above, where the CUDA-core kernel would recompute
+    the Gram once per 64-feature slice.  "simt" / "bf16x3" force one of the two."""
+    if precision == "bf16":
+        return _lib.PREC_BF16
+    if precision == "simt" or (precision == "fp32" and D <= 256):
+        return _lib.PREC_FP32
+    if precision in ("bf16x3", "fp32"):
+        return _lib.PREC_BF16 | _lib.BF16X3
+    raise RuntimeError(f"vgan_b200: unknown precision {precision!r} (bf16, fp32, bf16x3, simt)")
 
 
 def mmd2_eval(X: torch.Tensor, Y: Optional[torch.Tensor], U: Optional[torch.Tensor], *,
@@ -96,12 +110,12 @@ def mmd2_eval(X: torch.Tensor, Y: Optional[torch.Tensor], U: Optional[torch.Tens
     Nx, D = X.shape
     Ny = Nx if masked else Y.shape[0]
     D_u = 0 if U is None else U.shape[1]
-    flags = (_lib.PREC_FP32 if precision == "fp32" else _lib.PREC_BF16)
+    flags = _precision_flags(precision, D)
     if center:
         flags |= _lib.CENTER
     if need_dX:
         flags |= _lib.NEED_DX
-    if precision != "fp32" and _is_ladder(mults):
+    if not (flags & _lib.PREC_FP32) and _is_ladder(mults):
         flags |= _lib.LADDER
     if os.environ.get("VGAN_B200_NO_CLUSTER"):
         flags |= _lib.NO_CLUSTER
