@@ -80,12 +80,13 @@ def default_precision(D: int) -> str:
 
 
 def _precision_flags(precision: str, D: int) -> int:
-    """"bf16": bf16 operands on the tensor cores (2e-3).  "fp32": fp32-class results (1e-4) — the CUDA-core kernel up
-    to D = 256, split bf16 operands on the tensor cores ("bf16x3") above, where the CUDA-core kernel would recompute
-    the Gram once per 64-feature slice.  "simt" / "bf16x3" force one of the two."""
+    """"bf16": bf16 operands on the tensor cores (2e-3).  "fp32": fp32-class results (1e-4) — split bf16 operands on
+    the tensor cores ("bf16x3": 2.5-35x faster than the CUDA-core kernel from D = 16 to 4096, profiles/r1d_sweep.jsonl),
+    the CUDA-core kernel ("simt") only for the tiny widths of the VGAN encodings (D < 32), where a 64-wide K chunk is
+    mostly padding.  "simt" / "bf16x3" force one of the two."""
     if precision == "bf16":
         return _lib.PREC_BF16
-    if precision == "simt" or (precision == "fp32" and D <= 256):
+    if precision == "simt" or (precision == "fp32" and D < 32):
         return _lib.PREC_FP32
     if precision in ("bf16x3", "fp32"):
         return _lib.PREC_BF16 | _lib.BF16X3
