@@ -12,9 +12,12 @@
 //   dZ_I[:, slice p] = 4 c_i (O - rowsum(P) z_i)
 // The pairwise matrix only ever exists as a 128x128 TMEM tile.
 //
-// Warp roles (384 threads): warps 0-7 epilogue (warp%4 = TMEM lane quadrant, warp/4 =
-// column half), warp 8 = TMA producer for the Gram ring, warp 9 = MMA issuer,
-// warp 10 = TMA producer for V slices + column norms, warp 11 = TMEM allocator.
+// Warp roles (640 threads): warps 0-15 epilogue (warp%4 = TMEM lane quadrant, warp/4 = column quarter of 32),
+// warp 16 = TMA producer (Gram operands and V slices), warp 17 = MMA issuer, warp 18 = column norms,
+// warp 19 = TMEM allocator.  This kernel serves D_p <= 256, where the epilogue (FP32 + MUFU issue) is the bound:
+// with 8 epilogue warps (2 per scheduler) the issue slots were 49 % busy (ncu, profiles/r1d_base_d64_summary.txt:
+// fixed-latency dependency stalls with nothing else to issue); 4 warps per scheduler hide them.  setmaxnreg moves
+// registers from the 4 service warps (96 -> 56) to the epilogue warps (96 -> 104).
 #include "common.cuh"
 #include "ptx.cuh"
 #include "tc_epi.cuh"
@@ -24,8 +27,11 @@ namespace vg {
 constexpr int kStages = 5;
 constexpr int kStageBytes = 2 * kChunkBytes;   // Gram: Z_I chunk + Z_J chunk;  PV: two V chunks (128 features)
 constexpr int kPBytes = 2 * kChunkBytes;                     // 128 x 128 bf16
-constexpr int kNumEpiThreads = 256;
-constexpr int kThreads = 384;
+constexpr int kNumEpiWarps = 16;
+constexpr int kNumEpiThreads = kNumEpiWarps * 32;
+constexpr int kThreads = kNumEpiThreads + 128;
+constexpr int kWarpTma = kNumEpiWarps, kWarpMma = kNumEpiWarps + 1, kWarpNorms = kNumEpiWarps + 2,
+              kWarpAlloc = kNumEpiWarps + 3;
 
 struct __align__(8) TcBarriers {
   uint64_t ring_full[kStages], ring_empty[kStages];
@@ -34,7 +40,7 @@ struct __align__(8) TcBarriers {
   uint64_t p_full[2], p_empty[2];
   uint64_t o_full;
   uint32_t tmem_base;
-  float red[8][4];
+  float red[kNumEpiWarps][2];
 };
 
 constexpr int kSmemRing = 0;
@@ -112,11 +118,11 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__
     mbar_init(&bar->o_full, 1);
     fence_barrier_init();
   }
-  if (warp == 11) {
+  if (warp == kWarpAlloc) {
     tmem_alloc(&bar->tmem_base, 512);
     tmem_relinquish();
   }
-  if (warp == 8 && lane == 0) {
+  if (warp == kWarpTma && lane == 0) {
     tma_prefetch_desc(&zmap);
     tma_prefetch_desc(&zmapB);
     tma_prefetch_desc(&zmapV);
@@ -127,7 +133,8 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__
   const uint32_t tmem = bar->tmem_base;
   const uint32_t tmem_o = tmem + 256;
 
-  if (warp == 8) {
+  if (warp >= kNumEpiWarps) setmaxnreg_dec<56>();
+  if (warp == kWarpTma) {
     // ===================== TMA producer: one ring for Gram operands and V slices ==========
     // Stages are issued in exactly the order the MMA thread consumes them:
     //   Gram(0), Gram(1), PV(0), Gram(2), PV(1), ...
@@ -161,7 +168,7 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__
         }
       }
     }
-  } else if (warp == 10) {
+  } else if (warp == kWarpNorms) {
     // ===================== bulk-copy producer: scaled column norms =====================
     if (lane == 0) {
       for (int n = 0; n < n_tiles; ++n) {
@@ -173,7 +180,7 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__
                      &bar->nj_full[b]);
       }
     }
-  } else if (warp == 9) {
+  } else if (warp == kWarpMma) {
     // ===================== MMA issuer =====================
     // The whole warp runs the (warp-uniform) control flow so that addresses and descriptors live
     // in uniform registers; one elected lane issues the tcgen05 instructions.
@@ -243,9 +250,10 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__
     }
     if (u.pv && elect_one()) umma_commit(&bar->o_full);
     __syncwarp();
-  } else if (warp < 8) {
+  } else if (warp < kNumEpiWarps) {
     // ===================== epilogue warps =====================
-    const int q = warp & 3, g = warp >> 2;
+    setmaxnreg_inc<104>();   // 512 x 8 registers <= the 128 x 40 the service warps released
+    const int q = warp & 3, g = warp >> 2;                 // lane quadrant, column quarter
     const int row = q * 32 + lane;
     const uint32_t lane_addr = static_cast<uint32_t>(q * 32) << 16;
     const float c0 = p.par[0], m2c0 = p.par[1];
@@ -272,17 +280,17 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__
       mbar_wait(&bar->nj_full[b], (n >> 1) & 1);
       mbar_wait(&bar->s_full[b], (n >> 1) & 1);
       tc_fence_after();
-      uint8_t* p_row = smem + kSmemP + b * kPBytes + g * kChunkBytes + row * 128;
-      const float* njp = nj_smem + b * kTile + g * 64;
+      uint8_t* p_row = smem + kSmemP + b * kPBytes + (g >> 1) * kChunkBytes + row * 128;
+      const float* njp = nj_smem + b * kTile + g * 32;
       float ksum = 0.f;
-      uint4 pk[8];
-      epi_tile_64<LADDER>(tmem + lane_addr + b * kTile + g * 64, njp, ni, m2c0, cf, ratio, p.n_scales, ksum, rsum, pk,
-                          p.p_lo != 0);
+      uint4 pk[4];
+      epi_half_tile<LADDER>(tmem + lane_addr + b * kTile + g * 32, njp, ni, m2c0, cf, ratio, p.n_scales, ksum, rsum, pk,
+                            p.p_lo != 0);
       if (u.pv) {
         mbar_wait(&bar->p_empty[b], ((n >> 1) & 1) ^ 1);   // PV(n-2) done with P[b]
 #pragma unroll
-        for (int i = 0; i < 8; ++i)                          // 128B-swizzled K-major A operand
-          *reinterpret_cast<uint4*>(p_row + ((i ^ (row & 7)) << 4)) = pk[i];
+        for (int i = 0; i < 4; ++i)                          // 128B-swizzled K-major A operand
+          *reinterpret_cast<uint4*>(p_row + ((((g & 1) * 4 + i) ^ (row & 7)) << 4)) = pk[i];
       }
       tc_fence_before();
       mbar_arrive(&bar->s_empty[b]);
@@ -301,12 +309,10 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__
       bar->red[warp][0] = acc_x;
       bar->red[warp][1] = acc_y;
     }
-    asm volatile("bar.sync 1, 256;" ::: "memory");   // every epilogue warp is done reading the norms
-    nj_smem[g * kTile + row] = rsum;                  // ... so their buffer can carry the row-sum exchange
-    asm volatile("bar.sync 1, 256;" ::: "memory");
+    asm volatile("bar.sync 1, %0;" ::"n"(kNumEpiThreads) : "memory");
     if (threadIdx.x == 0 && u.slice == 0 && !(p.pass_flags & kPassNoSums)) {
       double sx = 0.0, sy = 0.0;
-      for (int wv = 0; wv < 8; ++wv) {
+      for (int wv = 0; wv < kNumEpiWarps; ++wv) {
         sx += bar->red[wv][0];
         sy += bar->red[wv][1];
       }
@@ -320,16 +326,20 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__
 
     // ---- gradient rows: dZ_i[slice] = 4 c_i (O_i - rowsum(P)_i z_i)  (x dY_mul)
     if (u.pv) {
-      const float rtot = nj_smem[row] + nj_smem[kTile + row];
-      mbar_wait(&bar->o_full, 0);
+      mbar_wait(&bar->o_full, 0);                       // every PV has completed: the P buffers are dead
       tc_fence_after();
-      write_grad_rows(p, tmem_o, lane_addr, g, row, u.ti, u.row_is_x, u.slice, slice_chunks, rtot);
+      float* rs_smem = reinterpret_cast<float*>(smem + kSmemP);   // [4 column quarters][128 rows] row sums of P
+      rs_smem[g * kTile + row] = rsum;
+      asm volatile("bar.sync 1, %0;" ::"n"(kNumEpiThreads) : "memory");
+      const float rtot = rs_smem[row] + rs_smem[kTile + row] + rs_smem[2 * kTile + row] + rs_smem[3 * kTile + row];
+      if (g < 2)                                        // two column halves of the slice, as in the other kernels
+        write_grad_rows(p, tmem_o, lane_addr, g, row, u.ti, u.row_is_x, u.slice, slice_chunks, rtot);
     }
   }
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 11) tmem_dealloc(tmem, 512);
+  if (warp == kWarpAlloc) tmem_dealloc(tmem, 512);
 }
 
 int launch_tc(const TcParams& p, const CUtensorMap& map, const CUtensorMap& mapB, const CUtensorMap& mapV, int ladder,
