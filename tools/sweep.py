@@ -8,6 +8,15 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from vgan_b200 import MMDLossConstrained, RBF
 from oracle import torch_eager
 
+def _peak_tf():
+    try:
+        return float(json.load(open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
+                                                 "MEASURED_PEAKS.json")))["bf16_tflops_sustained"])
+    except Exception:
+        return 1399.3
+
+PEAK_TF = _peak_tf()
+
 def timeit(fn, reps):
     for _ in range(2): fn()
     torch.cuda.synchronize()
@@ -19,7 +28,8 @@ def timeit(fn, reps):
 
 def main():
     shapes = [(4096, 784), (4096, 49), (16384, 32), (16384, 128), (16384, 512), (4096, 16), (4096, 64), (4096, 256),
-              (4096, 1024), (4096, 4096), (16384, 1024), (65536, 64), (65536, 256), (65536, 1024), (131072, 128)]
+              (4096, 1024), (4096, 4096), (16384, 1024), (65536, 64), (65536, 256), (65536, 1024), (131072, 128),
+              (262144, 16), (262144, 64)]
     for N, D in shapes:
         g = torch.Generator(device="cuda").manual_seed(0)
         X = torch.randn(N, D, device="cuda", generator=g)
@@ -28,6 +38,7 @@ def main():
         row = {"N": N, "D": D}
         for prec in ("bf16", "bf16x3", "simt"):
             if prec == "simt" and N * N * D > 16384 * 16384 * 512: continue
+            if prec == "bf16x3" and N > 131072: continue
             loss_fn = MMDLossConstrained(10.0, kernel=RBF(), precision=prec)
             U = U0.clone().requires_grad_()
             def step():
@@ -39,6 +50,10 @@ def main():
             row[f"{prec}_evals_per_s"] = round(1e3 / ms, 2)
             if prec == "bf16":
                 row["bf16_tflops_alg"] = round(8.0 * N * N * D / (ms * 1e-3) / 1e12, 1)
+                # fractions of the two rooflines of SURVEY.md 8(d): tensor pipe (measured sustained bf16 peak) and MUFU
+                # (2 N^2 ex2 per evaluation against 16 ex2/clk/SM x 148 SMs x 1.965 GHz); the larger one binds
+                row["tensor_frac"] = round(row["bf16_tflops_alg"] / PEAK_TF, 3)
+                row["mufu_frac"] = round(2.0 * N * N / (ms * 1e-3) / (16 * 148 * 1.965e9), 3)
         if 5 * (2 * N) ** 2 * 4 * 4 < 150e9:      # [5,2N,2N] fp32 + autograd copies must fit
             try:
                 ref = torch_eager.MMDLossConstrained(10.0)

@@ -305,16 +305,13 @@ int vgan_b200_mmd2_fwd_bwd(void* ws, int64_t Nx, int64_t Ny, int64_t D, int64_t 
   // one pass of the tcgen05 kernels over this shard (BF16X3 runs three: see below)
   auto run_pass = [&](TcParams& p, bool zero_outputs) -> int {
   if (p.pv && p.nslices >= 2 && !(flags & VGAN_B200_NO_CLUSTER)) {
-    // D_p > 256: the slice CTAs of a row tile run as one thread-block cluster sharing P over DSMEM;
-    // the S_xx-only units (no gradient GEMM, one slice) stay on the plain kernel.
-    // The S_xx units run concurrently on a side stream: clusters of 4 can only occupy 132 of the
-    // 148 SMs (GPC granularity), and the S_xx work (~1/9 of the total) fills the stranded ones.
-    // Priorities: the cluster kernel runs on a high-priority internal stream, the S_xx kernel on a
-    // low-priority one, so that SMs freed by a finished cluster go to the next cluster and not to pending
-    // S_xx CTAs (which would fragment the GPC and keep the next 8-CTA cluster from launching).
-    // With the persistent pair kernel the order is enforced instead: its CTAs count themselves in at their first
-    // instruction, the side stream holds the S_xx launch (cuStreamWaitValue32, no SM occupied) until all of them
-    // are resident, and the S_xx grid is sized to the SMs they leave free.
+    // D_p > 256: the slice CTAs of two row tiles run as one thread-block cluster (mmd_tc_pair.cu) and share every
+    // P tile; the S_xx-only units (no gradient GEMM) run as their own sums-only kernel (mmd_xx.cu) on a low-priority
+    // side stream, the cluster kernel on a high-priority one.  8-CTA clusters occupy 120 of the 148 SMs; the S_xx
+    // kernel gets the other 28.  The order is enforced: the persistent CTAs count themselves in at their first
+    // instruction, the side stream holds the S_xx launch (cuStreamWaitValue32, no SM occupied) until all of them are
+    // resident, and the S_xx grid is sized to the SMs they leave free.  (Launched freely, the S_xx CTAs were
+    // dispatched first and the clusters started 1-9 ms late: tools/gpu_timeline.py.)
     static cudaStream_t side = nullptr, hi = nullptr;
     static cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_join_hi = nullptr;
     static const int xx_mode = getenv("VGAN_B200_XX_MODE") ? atoi(getenv("VGAN_B200_XX_MODE")) : 0;   // 1: serial (measurement)
