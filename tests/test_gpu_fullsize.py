@@ -23,10 +23,10 @@ def data():
     return X, U
 
 
-def _eval(Xd, Ud, kernel, **kw):
+def _eval(Xd, Ud, kernel, precision="bf16", **kw):
     from vgan_b200.loss import mmd2_eval
     bw, frozen = kernel._bw_state(Xd.device)
-    out = mmd2_eval(Xd, None, Ud, weight=0.0, bw_dev=bw, frozen=frozen, mults=kernel._mults, precision="bf16",
+    out = mmd2_eval(Xd, None, Ud, weight=0.0, bw_dev=bw, frozen=frozen, mults=kernel._mults, precision=precision,
                     masked=True, **kw)
     kernel._freeze()
     torch.cuda.synchronize()
@@ -49,6 +49,30 @@ def test_row_sample_matches_oracle_port(data):
     err = float((dU_rows.double().cpu() - want_dU.double()).norm() / want_dU.double().norm())
     assert err <= 2e-2, err
     assert float((dU[r0:r1] - dU_rows).norm() / dU_rows.norm()) <= 1e-5
+
+
+def test_fp32_class_row_sample_matches_oracle_port(data):
+    """The split-operand (bf16x3) path at the bench shape: three gradient passes accumulating into the same rows
+    through the persistent stream-K kernel; 1e-4 against the port's fp32 blockwise evaluation of the same rows."""
+    from vgan_b200 import RBF
+    X, U = data
+    Xd, Ud = X.cuda(), U.cuda()
+    kernel = RBF()
+    sums, dU = _eval(Xd, Ud, kernel, precision="bf16x3")
+    bw = float(kernel.bandwidth)
+    r0, r1 = 33024, 33280
+    want_sums, want_dU = orc.cpu_blockwise_fwd_bwd(X, U, bw, r0, r1)
+    s_rows, dU_rows = _eval(Xd, Ud, kernel, precision="bf16x3", row_begin=r0, row_end=r1, xx_part=10 ** 6 - 1,
+                            xx_nparts=10 ** 6)
+    assert abs(float(s_rows[1]) - want_sums[1]) <= 1e-4 * want_sums[1]
+    assert abs(float(s_rows[2]) - want_sums[2]) <= 1e-4 * want_sums[2]
+    err = float((dU_rows.double().cpu() - want_dU.double()).norm() / want_dU.double().norm())
+    assert err <= 1e-4, err
+    assert float((dU[r0:r1] - dU_rows).norm() / dU_rows.norm()) <= 1e-5
+    # and the bf16 path agrees with it to bf16 accuracy
+    sums16, dU16 = _eval(Xd, Ud, kernel)
+    assert torch.allclose(sums16[:3], sums[:3], rtol=2e-3)
+    assert float((dU16 - dU).norm() / dU.norm()) <= 2e-2
 
 
 def test_row_shards_add_up(data):
