@@ -77,3 +77,17 @@ def test_product_code_does_not_import_oracle():
             if f.endswith(".py"):
                 src = open(os.path.join(dirpath, f)).read()
                 assert "import oracle" not in src and "from oracle" not in src, f
+
+
+def test_torch_ops_registered_cuda_only():
+    """torch.ops.vgan_b200.* exist with their schemas, and the dispatcher has no CPU kernel for them."""
+    import vgan_b200
+    from vgan_b200 import ops
+    for name in ops.OPS:
+        assert hasattr(torch.ops.vgan_b200, name)
+    bw = torch.zeros(1)
+    with pytest.raises((NotImplementedError, RuntimeError)):
+        torch.ops.vgan_b200.mmd2_masked_fwd_bwd(torch.randn(8, 4), torch.rand(8, 4), bw, False,
+                                                [0.25, 0.5, 1.0, 2.0, 4.0], 10.0, "bf16", True)
+    with pytest.raises((NotImplementedError, RuntimeError)):
+        torch.ops.vgan_b200.mmd2_matrix(torch.randn(8, 4), torch.ones(1), 0.0)

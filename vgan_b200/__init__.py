@@ -7,5 +7,6 @@ from .loss import RBF, MMDLossConstrained, mmd2_eval  # noqa: F401
 from .statistic import MMDStatistic  # noqa: F401
 from .subspace import unique_subspaces  # noqa: F401
 from .vgan import VGAN, VGAN_no_kl  # noqa: F401
+from . import ops  # noqa: F401  (registers torch.ops.vgan_b200.*)
 
 __all__ = ["RBF", "MMDLossConstrained", "MMDStatistic", "VGAN", "VGAN_no_kl", "mmd2_eval", "unique_subspaces"]
