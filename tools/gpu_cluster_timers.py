@@ -1,3 +1,5 @@
+"""Per-role wait timers of the pair kernel (cycles spent waiting on each barrier).  Needs a library built with
+`make -C vgan_b200/csrc clean all TIMERS=1` — the product build compiles the clock reads out."""
 import os, sys
 import numpy as np, torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))

@@ -30,6 +30,14 @@
 #include "ptx.cuh"
 #include "tc_epi.cuh"
 
+// In-kernel wait timers (tools/gpu_cluster_timers.py): compiled in only with -DVGAN_B200_TIMERS (make TIMERS=1);
+// the product build keeps clock reads out of the single-thread issue loops.
+#ifdef VGAN_B200_TIMERS
+#define VG_CLK() clock64()
+#else
+#define VG_CLK() 0ll
+#endif
+
 namespace vg {
 
 constexpr int kGStages = 4;                        // Gram operand ring
@@ -172,7 +180,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
   uint32_t pf_mask = 0, sf_mask = 0, pub_mask = 0;   // per-slot phase parities of p_full / slot_free / pub_full
   uint32_t part = 0;                   // parity of o_full
   long long tm0 = 0, tm1 = 0, tm2 = 0, tm3 = 0;      // debug timers (meaning depends on the role)
-  const long long t_begin = clock64();
+  const long long t_begin = VG_CLK();
   unsigned long long gt_begin;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt_begin));
   // resident now: the host makes the S_xx launch wait until every persistent CTA has counted itself in
@@ -304,16 +312,16 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
       const uint32_t b = kg & 1;
       const uint32_t d_tmem = tmem + b * kTile;
       {
-        const long long t0 = clock64();
+        const long long t0 = VG_CLK();
         mbar_wait(&bar->s_empty[b], ((kg >> 1) & 1) ^ 1);     // both CTAs' epilogues released S[b]
-        tm1 += clock64() - t0;
+        tm1 += VG_CLK() - t0;
       }
       tc_fence_after();
       for (int kc = 0; kc < p.gchunks; ++kc) {
         {
-          const long long t0 = clock64();
+          const long long t0 = VG_CLK();
           mbar_wait(&bar->g_full[rs], rph);
-          tm0 += clock64() - t0;
+          tm0 += VG_CLK() - t0;
         }
         tc_fence_after();
         const uint32_t a_lo = g_lo + rs * (kGStageBytes >> 4);
@@ -345,12 +353,12 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     for (int t = 0; t < TTp; ++t) {
       const int slot = t % kQSlots;
       {
-        const long long t0 = clock64();
+        const long long t0 = VG_CLK();
         mbar_wait(&bar->p_full[slot], (pf_mask >> slot) & 1);   // my P(I0, t)
         if (lane == 0 && t + kQSlots < TTp && (t + kQSlots) % CS != c)
           mbar_arrive_expect_tx(&bar->p_full[slot], pbytes);    // arm the slot for its next (remote) tile
         mbar_wait(&bar->p_pair[slot], (pf_mask >> slot) & 1);   // the peer's P(I1, t)
-        tm2 += clock64() - t0;
+        tm2 += VG_CLK() - t0;
       }
       pf_mask ^= 1u << slot;
       tc_fence_after();
@@ -358,9 +366,9 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
       if (my_chunks > 0) {
         for (int h = 0; h < 2; ++h) {
           {
-            const long long t0 = clock64();
+            const long long t0 = VG_CLK();
             mbar_wait(&bar->v_full[rs], rph);
-            tm3 += clock64() - t0;
+            tm3 += VG_CLK() - t0;
           }
           tc_fence_after();
           const uint32_t v_lo = v_lo0 + rs * (kVStageBytes >> 4);
@@ -422,10 +430,10 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
       float cf[VGAN_B200_MAX_SCALES];
 #pragma unroll
       for (int m = 0; m < VGAN_B200_MAX_SCALES; ++m) cf[m] = valid ? (col_is_x ? coef_x[m] : coef_y[m]) : 0.f;
-      long long tq = clock64();
+      long long tq = VG_CLK();
       mbar_wait(&bar->nj_full[b], (kg >> 1) & 1);
       mbar_wait(&bar->s_full[b], (kg >> 1) & 1);
-      tm0 += clock64() - tq; tq = clock64();
+      tm0 += VG_CLK() - tq; tq = VG_CLK();
       tc_fence_after();
       const float* njp = nj_smem + b * kTile + g * 64;
       float ksum = 0.f;
@@ -438,12 +446,12 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
       if (valid) { if (col_is_x) acc_x += ksum; else acc_y += ksum; }
       // ---- park the P tile in its slot; the publisher warp sends it to the other slices of this row tile
       const int slot = t % kQSlots;
-      tm1 += clock64() - tq; tq = clock64();
+      tm1 += VG_CLK() - tq; tq = VG_CLK();
       if (t >= kQSlots) {
         mbar_wait(&bar->slot_free[slot], (sf_mask >> slot) & 1);   // every CTA finished PV(t - kQSlots)
         sf_mask ^= 1u << slot;
       }
-      tm2 += clock64() - tq; tq = clock64();
+      tm2 += VG_CLK() - tq; tq = VG_CLK();
       uint8_t* p_slot = smem + kQSmemP + slot * kQPBytes;
       uint8_t* p_row = p_slot + g * kChunkBytes + row * 128;
 #pragma unroll
@@ -455,7 +463,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
         mbar_arrive(&bar->p_full[slot]);     // own PV warp / forwarder
         mbar_arrive(&bar->pub_full[slot]);   // publisher warp
       }
-      tm3 += clock64() - tq;
+      tm3 += VG_CLK() - tq;
     }
     // ---- partial sums of this CTA's tiles
     acc_x = warp_sum(acc_x);
@@ -478,7 +486,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     }
 
     // ===================== cluster-wide row sums of P, then the gradient rows of this range =====================
-    const long long tq_tail = clock64();
+    const long long tq_tail = VG_CLK();
     tc_fence_before();
     cluster_sync_all();      // #1: no CTA of the cluster reads a P slot any more
     if (warp < 4) {
@@ -500,7 +508,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     }
     tc_fence_before();
     cluster_sync_all();      // #3: O, the norm buffers and P slot 0 may be reused by the next range
-    tm_tail += clock64() - tq_tail;
+    tm_tail += VG_CLK() - tq_tail;
     }
   }
 
@@ -512,7 +520,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     d[o + 2] = static_cast<float>(tm2);
     d[o + 3] = static_cast<float>(tm3);
     if (warp == 9) {
-      d[12] = static_cast<float>(clock64() - t_begin);
+      d[12] = static_cast<float>(VG_CLK() - t_begin);
       unsigned long long gt_end;
       asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt_end));
       d[13] = static_cast<float>(gt_end - gt_begin);
