@@ -138,3 +138,17 @@ def test_kl_graph_replay_matches_eager_steps(monkeypatch, capsys):
     for key in ("detector_loss", "generator_loss"):
         a, b = np.array(graphed.train_history[key]), np.array(eager.train_history[key])
         np.testing.assert_allclose(a, b, rtol=2e-4, atol=1e-6, equal_nan=True)
+
+
+def test_graph_replay_wide_data_uses_cluster_kernels(monkeypatch, capsys):
+    """D > 256: the captured step contains the pair kernel and the S_xx kernel on their internal streams (fork/join
+    inside the capture); graph and eager training agree."""
+    from vgan_b200 import VGAN_no_kl
+    X = _data(768, 320, seed=4)
+    kw = dict(batch_size=256, epochs=4, lr=0.01, seed=777)
+    graphed = _fit(VGAN_no_kl, None, X, monkeypatch, **kw)
+    assert graphed.used_cuda_graph
+    monkeypatch.setattr(VGAN_no_kl, "cuda_graph", False)
+    eager = _fit(VGAN_no_kl, None, X, monkeypatch, **kw)
+    a, b = np.array(graphed.train_history["generator_loss"]), np.array(eager.train_history["generator_loss"])
+    np.testing.assert_allclose(a, b, rtol=1e-4, atol=1e-6)
