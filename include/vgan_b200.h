@@ -14,6 +14,9 @@
  * pointers are DEVICE pointers borrowed for the call unless a name ends in _host; all
  * work is enqueued on `stream` (a cudaStream_t passed as void*); nothing synchronises
  * the host.  No CPU fallback exists: without an sm_100 device every call fails.
+ * Concurrency: one host thread at a time per device (vgan_b200_mmd2_fwd_bwd forks onto two internal streams per
+ * device for D > 256 and joins them back into `stream` before it returns); different devices are independent —
+ * the intended deployment is one process per GPU.
  */
 #ifndef VGAN_B200_H
 #define VGAN_B200_H

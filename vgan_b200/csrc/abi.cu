@@ -312,8 +312,22 @@ int vgan_b200_mmd2_fwd_bwd(void* ws, int64_t Nx, int64_t Ny, int64_t D, int64_t 
     // instruction, the side stream holds the S_xx launch (cuStreamWaitValue32, no SM occupied) until all of them are
     // resident, and the S_xx grid is sized to the SMs they leave free.  (Launched freely, the S_xx CTAs were
     // dispatched first and the clusters started 1-9 ms late: tools/gpu_timeline.py.)
-    static cudaStream_t side = nullptr, hi = nullptr;
-    static cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_join_hi = nullptr;
+    // internal streams and events, one set per device, created on first use and kept (see the header: calls that
+    // share a device must come from one host thread at a time)
+    struct Aux { cudaStream_t side, hi; cudaEvent_t ev_fork, ev_join, ev_join_hi; };
+    static Aux aux_of_device[64] = {};
+    int dev_id = 0;
+    VG_CUDA_CHECK(cudaGetDevice(&dev_id));
+    if (dev_id < 0 || dev_id >= 64) {
+      set_error("mmd2_fwd_bwd: device ordinal %d out of range", dev_id);
+      return VGAN_B200_ERR_DEVICE;
+    }
+    Aux& aux = aux_of_device[dev_id];
+    cudaStream_t& side = aux.side;
+    cudaStream_t& hi = aux.hi;
+    cudaEvent_t& ev_fork = aux.ev_fork;
+    cudaEvent_t& ev_join = aux.ev_join;
+    cudaEvent_t& ev_join_hi = aux.ev_join_hi;
     static const int xx_mode = getenv("VGAN_B200_XX_MODE") ? atoi(getenv("VGAN_B200_XX_MODE")) : 0;   // 1: serial (measurement)
     const bool overlap = p.n_xx_units > 0 && xx_mode != 1;
     if (overlap && !side) {
