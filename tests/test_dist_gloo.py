@@ -44,3 +44,29 @@ def test_two_rank_shards_reduce_to_single_rank_result():
     ret = mgr.dict()
     mp.spawn(_worker, args=(2, 29533, ret), nprocs=2, join=True)
     assert ret[0] and ret[1]
+
+
+def _gather_worker(rank, world, port, ret):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from vgan_b200.dist import gather_batch, shard_rows
+    rs = np.random.RandomState(1)
+    N, D = 512, 6
+    X, U = torch.tensor(rs.randn(N, D)), torch.tensor(rs.rand(N, D))
+    n = N // world
+    Xg, Ug, off = gather_batch(X[rank * n:(rank + 1) * n], U[rank * n:(rank + 1) * n])
+    ok = torch.equal(Xg, X) and torch.equal(Ug, U) and off == rank * n and shard_rows(N, rank, world) == (off, off + n)
+    try:
+        gather_batch(X[:100], U[:100])
+        ok = False
+    except RuntimeError:
+        pass
+    ret[rank] = bool(ok)
+    dist.destroy_process_group()
+
+
+def test_data_parallel_gather_lines_up_with_row_shards():
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    mp.spawn(_gather_worker, args=(2, 29541, ret), nprocs=2, join=True)
+    assert ret[0] and ret[1]

@@ -58,3 +58,36 @@ def sharded_masked_step(loss_fn, X, U, rank: int = 0, world: int = 1, group=None
     else:
         loss = out["loss"][0]
     return dict(loss=loss, dU=dU, rows=(b, e), dU_colsum=colsum.float(), k1_events=ev, sums=out["sums"])
+
+
+def gather_batch(X_local: torch.Tensor, U_local: torch.Tensor, group=None):
+    """Data-parallel form of the step's input: every rank holds ITS rows of the batch and of the generator output
+    (its own noise); the column operand of the pairwise matrix is the whole batch, so the shards are all-gathered
+    (two ``all_gather_into_tensor`` over NCCL/NVLink; gloo in the CPU tests).  Returns (X, U, row offset of this
+    rank).  All shards must have the same number of rows, a multiple of 128 unless world == 1."""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    if world == 1:
+        return X_local, U_local, 0
+    rank = dist.get_rank(group)
+    n, D = X_local.shape
+    if n % 128:
+        raise RuntimeError("gather_batch: every rank's shard must be a multiple of 128 rows (row-tile aligned)")
+    X = torch.empty((world * n, D), dtype=X_local.dtype, device=X_local.device)
+    U = torch.empty((world * n, D), dtype=U_local.dtype, device=U_local.device)
+    dist.all_gather_into_tensor(X, X_local.contiguous(), group=group)
+    dist.all_gather_into_tensor(U, U_local.contiguous(), group=group)
+    return X, U, rank * n
+
+
+def data_parallel_masked_step(loss_fn, X_local, U_local, group=None):
+    """loss(X, U*X, U) over the global batch whose rows are spread over the ranks; returns this rank's rows of dL/dU
+    (``dU`` lines up with ``U_local``) — all-gather of the inputs, then the row-tile sharded step above."""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    X, U, _ = gather_batch(X_local, U_local, group)
+    out = sharded_masked_step(loss_fn, X, U, rank, world, group)
+    b, e = out["rows"]
+    n = X_local.shape[0]
+    if (b, e) != (rank * n, (rank + 1) * n):
+        raise RuntimeError("data_parallel_masked_step: shard rows do not line up with the row-tile partition")
+    return out
