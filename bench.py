@@ -192,49 +192,66 @@ def main():
     e2e = None
     if not args.no_e2e:
         # Two device input sets: the H2D copy of step i+1 runs on a copy stream under the kernels of step i
-        # (every step still pays for its own 512 MiB of H2D and its D2H read-back inside the timed region).
-        bufs = [(torch.empty_like(X), torch.empty_like(U)) for _ in range(2)]
+        # (every step still pays for its own H2D and its D2H read-back inside the timed region).
+        # N > 1 has two ways to feed the host batch: "replicated" = every rank copies the whole batch (N x the H2D
+        # bytes, no exchange) or "sharded" = every rank copies only ITS rows and the shards are all-gathered over NVLink
+        # inside the step (dist.gather_batch).  Both are probed for 2 steps; the faster one is timed and named.
         res_h = torch.empty(1 + D, dtype=torch.float32).pin_memory()
         copy_st = torch.cuda.Stream(device=dev)
-        ready = [torch.cuda.Event(), torch.cuda.Event()]
-        done = [torch.cuda.Event(), torch.cuda.Event()]
         main_st = torch.cuda.current_stream()
 
-        def h2d(i):
-            Xd, Ud = bufs[i & 1]
-            with torch.cuda.stream(copy_st):
-                copy_st.wait_event(done[i & 1])        # the step that last read this buffer set has finished
-                Xd.copy_(Xh, non_blocking=True)
-                Ud.copy_(Uh, non_blocking=True)
-                ready[i & 1].record(copy_st)
+        def run_e2e(shard, steps):
+            n_loc = N // world if shard else N
+            r0 = rank * n_loc if shard else 0
+            Xsrc, Usrc = Xh[r0:r0 + n_loc], Uh[r0:r0 + n_loc]
+            bufs = [(torch.empty((n_loc, D), device=dev), torch.empty((n_loc, D), device=dev)) for _ in range(2)]
+            ready = [torch.cuda.Event(), torch.cuda.Event()]
+            done = [torch.cuda.Event(), torch.cuda.Event()]
 
-        def e2e_step(i):
-            h2d(i + 1)                                 # next step's inputs, overlapped with this step
-            Xd, Ud = bufs[i & 1]
-            main_st.wait_event(ready[i & 1])
-            o = step(Xd, Ud)
-            done[i & 1].record(main_st)
-            res_h[:1].copy_(o["loss"].reshape(1), non_blocking=True)
-            res_h[1:].copy_(o["dU_colsum"], non_blocking=True)
-            main_st.synchronize()                      # the user reads the loss every step (vgan.py:620)
+            def h2d(i):
+                Xd, Ud = bufs[i & 1]
+                with torch.cuda.stream(copy_st):
+                    copy_st.wait_event(done[i & 1])        # the step that last read this buffer set has finished
+                    Xd.copy_(Xsrc, non_blocking=True)
+                    Ud.copy_(Usrc, non_blocking=True)
+                    ready[i & 1].record(copy_st)
 
-        for e in done:
-            e.record(main_st)
-        h2d(0)
-        for i in range(2):
-            e2e_step(i)
-        barrier()
-        t0 = time.perf_counter()
-        for i in range(2, 2 + args.steps):
-            e2e_step(i)
-        barrier()
-        e_ms = (time.perf_counter() - t0) * 1e3 / args.steps
-        te = torch.tensor([e_ms], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(te, op=dist.ReduceOp.MAX)
-        e2e = {"value": 1e3 / float(te[0]), "unit": "evals/s", "h2d_bytes_per_step": 2 * N * D * 4,
+            def e2e_step(i):
+                h2d(i + 1)                                 # next step's inputs, overlapped with this step
+                Xd, Ud = bufs[i & 1]
+                main_st.wait_event(ready[i & 1])
+                o = data_parallel_masked_step(loss_fn, Xd, Ud) if shard else step(Xd, Ud)
+                done[i & 1].record(main_st)
+                res_h[:1].copy_(o["loss"].reshape(1), non_blocking=True)
+                res_h[1:].copy_(o["dU_colsum"], non_blocking=True)
+                main_st.synchronize()                      # the user reads the loss every step (vgan.py:620)
+
+            for e in done:
+                e.record(main_st)
+            h2d(0)
+            for i in range(2):
+                e2e_step(i)
+            barrier()
+            t0 = time.perf_counter()
+            for i in range(2, 2 + steps):
+                e2e_step(i)
+            barrier()
+            e_ms = (time.perf_counter() - t0) * 1e3 / steps
+            te = torch.tensor([e_ms], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(te, op=dist.ReduceOp.MAX)
+            del bufs
+            return float(te[0])
+
+        shard = False
+        if world > 1 and N % (128 * world) == 0:
+            shard = run_e2e(True, 2) < run_e2e(False, 2)       # same decision on every rank (all-reduced times)
+        e_ms = run_e2e(shard, args.steps)
+        e2e = {"value": 1e3 / e_ms, "unit": "evals/s", "h2d_bytes_per_step": 2 * N * D * 4,
                "d2h_bytes_per_step": (1 + D) * 4,
-               "overlap": "H2D of step i+1 on a copy stream under the kernels of step i; loss + colsum(dU) read every step"}
+               "overlap": "H2D of step i+1 on a copy stream under the kernels of step i; loss + colsum(dU) read every step",
+               "feed": ("sharded: every rank copies its N/%d rows, shards all-gathered over NVLink inside the step" % world)
+                       if shard else "replicated: every rank copies the full batch"}
 
     if rank == 0:
         peak, peak_src = peaks()
