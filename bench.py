@@ -96,10 +96,18 @@ def run_reference(args):
         return
     from oracle import mmd_oracle as orc
     N, D = args.n, args.d
-    rows = args.cpu_rows
     X, U = make_inputs(N, D)
     bw = 2.0 * D   # value is irrelevant for timing; ~ E|zi-zj|^2
     cores = torch.get_num_threads()
+    rows = args.ref_rows
+    if rows <= 0:
+        # size the per-step sample so that the whole --steps/--warmup run takes about two minutes on this host:
+        # a 2048-row probe gives the rate (the cost is linear in the rows), then whole 2048-row blocks up to N/2
+        t0 = time.perf_counter()
+        orc.cpu_blockwise_fwd_bwd(X, U, bw, 0, 2048)
+        per_row = (time.perf_counter() - t0) / 2048
+        rows = int(120.0 / (args.steps + args.warmup) / per_row) // 2048 * 2048
+        rows = max(2048, min(rows, N // 2))
     times = []
     for it in range(args.warmup + args.steps):
         t0 = time.perf_counter()
@@ -128,7 +136,10 @@ def main():
     ap.add_argument("--n", type=int, default=N_DEFAULT)
     ap.add_argument("--d", type=int, default=D_DEFAULT)
     ap.add_argument("--precision", default="bf16")
-    ap.add_argument("--cpu-rows", type=int, default=4096)
+    ap.add_argument("--cpu-rows", type=int, default=16384,
+                    help="gradient rows of the cpu_baseline sample of our arm (16384 rows ~ 10 s on 16 threads)")
+    ap.add_argument("--ref-rows", type=int, default=0,
+                    help="--impl reference: gradient rows per step (0 = sized so the whole run takes ~2 minutes)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--dp-gather", action="store_true",
