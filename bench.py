@@ -87,6 +87,14 @@ class ClockSampler(threading.Thread):
                 "reasons": sorted(self.reasons)}
 
 
+def host_threads():
+    """All host threads for the CPU legs (torchrun exports OMP_NUM_THREADS=1 to its workers)."""
+    n = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    if torch.get_num_threads() < n:
+        torch.set_num_threads(n)
+    return torch.get_num_threads()
+
+
 def run_reference(args):
     """Reference arm: the CPU restatement of the reference path (oracle port; the reference module
     itself cannot hold its [5,2N,2N] tensor at this shape and does not travel to the GPU box),
@@ -98,7 +106,7 @@ def run_reference(args):
     N, D = args.n, args.d
     X, U = make_inputs(N, D)
     bw = 2.0 * D   # value is irrelevant for timing; ~ E|zi-zj|^2
-    cores = torch.get_num_threads()
+    cores = host_threads()
     rows = args.ref_rows
     if rows <= 0:
         # size the per-step sample so that the whole --steps/--warmup run takes about two minutes on this host:
@@ -287,8 +295,9 @@ def main():
                 "clocks": sampler.result()}
         if e2e:
             line["e2e"] = e2e
-        if not args.no_cpu_baseline:
+        if not args.no_cpu_baseline and world == 1:     # reported at N=1 only (rank 0 has the host to itself there)
             from oracle import mmd_oracle as orc
+            host_threads()
             rows = args.cpu_rows
             Xc, Uc = Xh[:], Uh[:]
             t0 = time.perf_counter()
