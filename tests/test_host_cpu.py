@@ -91,3 +91,22 @@ def test_torch_ops_registered_cuda_only():
                                                 [0.25, 0.5, 1.0, 2.0, 4.0], 10.0, "bf16", True)
     with pytest.raises((NotImplementedError, RuntimeError)):
         torch.ops.vgan_b200.mmd2_matrix(torch.randn(8, 4), torch.ones(1), 0.0)
+
+
+def test_bench_reference_arm_line():
+    """bench.py --impl reference (the CPU port of the reference path) prints the contract's JSON line; under torchrun's
+    OMP_NUM_THREADS=1 it still takes every host thread."""
+    import json
+    import subprocess
+    import sys
+    env = dict(os.environ, OMP_NUM_THREADS="1")
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--n", "2048",
+                          "--d", "64", "--steps", "1", "--warmup", "0", "--ref-rows", "512"],
+                         capture_output=True, text=True, env=env, timeout=300)
+    assert out.returncode == 0, out.stderr[-2000:]
+    line = json.loads(out.stdout.strip().splitlines()[-1])
+    assert line["impl"] == "reference" and line["unit"] == "evals/s" and line["higher_is_better"] is True
+    assert line["metric"] == "mmd2_fwd_bwd_evals_per_sec" and line["value"] > 0
+    assert line["cpu_baseline"]["kind"] == "port" and line["cpu_baseline"]["value"] == line["value"]
+    assert line["cpu_baseline"]["cores"] == len(os.sched_getaffinity(0))
+    assert line["e2e"] == {"value": line["value"], "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
