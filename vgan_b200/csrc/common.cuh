@@ -30,7 +30,7 @@ constexpr int kXxMinFreeSms = 8;         // fewer SMs left free by the gradient 
 // P-tile exchange scratch (pair kernel): 3 slots of one bf16 [128,128] tile per SM, indexed by %smid so that a
 // region is only ever rewritten by the CTA resident on that SM (stays in L2, never streams to HBM)
 constexpr int kXchgSms = 256;
-constexpr int kXchgBytesPerSm = 3 * 2 * kChunkBytes;
+constexpr int kXchgBytesPerSm = 4 * 2 * kChunkBytes;   // up to 4 P tiles of 32 KiB per SM
 
 struct TcParams {
   int tiles_x, tiles_y;       // 128-row tiles in the X / Y regions of the stacked operand

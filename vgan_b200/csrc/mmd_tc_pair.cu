@@ -42,34 +42,57 @@ namespace vg {
 
 constexpr int kGStages = 4;                        // Gram operand ring
 constexpr int kGStageBytes = kChunkBytes + kChunkBytes / 2;   // 24 KiB
-constexpr int kGProducers = 2;                     // warps 8 and 11; stage s belongs to producer s % 2
+// G256 variant (template parameter): ONE Gram issue covers the pair's next TWO column tiles (N = 256: the leader holds
+// the 128 rows of tile k, the peer those of tile k + 1; D = both S buffers at once).  The row operand [Z_I0; Z_I1] is
+// then streamed once per two column tiles instead of once per tile (-21 % of all L2 -> SM bytes at D_p = 1024), a Gram
+// instruction runs 128 instead of 64 cycles, and a ring stage (A chunk 16 KiB + B chunk 16 KiB) feeds 512 instead of
+// 256 tensor cycles, so the same 96 KiB in flight cover twice the time.  S is then double-buffered only against the PV
+// stream, not against its own Gram.  Ranges are padded to an even number of rounds with zero-coefficient tiles.
+#ifndef VG_G2_STAGES
+#define VG_G2_STAGES 3
+#endif
+#ifndef VG_G2_SLOTS
+#define VG_G2_SLOTS 3
+#endif
+constexpr int kG2Stages = VG_G2_STAGES;
+constexpr int kG2StageBytes = 2 * kChunkBytes;                // 32 KiB
+constexpr int kGProducers = 2;                     // warps 8 and 11 alternate over the ring stages
 constexpr int kVStages = 2;                        // V ring: half tiles (64 rows of Z_J)
 constexpr int kVStageBytes = kChunkBytes;          // 2 boxes of [64 x 64] bf16
-constexpr int kQSlots = 3;                         // P tiles, 32 KiB each
 constexpr int kQPBytes = 2 * kChunkBytes;
 constexpr int kQThreads = 512;   // warps: 0-7 epilogue (192 registers), 8-15 service (64 registers): 8/11 G producers,
                                  // 9 Gram MMA (peer: P forwarder), 10 PV MMA, 12 V producer, 13 P publisher, 14 norms
 static_assert(kGStages % kGProducers == 0, "each G producer warp owns fixed ring stages");
+// G256 spends the 32 KiB its smaller ring frees on a FOURTH P slot: the loop  P(t) parked -> exchanged -> PV(t) done in
+// every pair -> slot free -> P(t + slots) parked  takes ~8200 cycles (tools/gpu_cluster_timers.py), i.e. 2730 per column
+// tile with 3 slots against the 2048 the tensor pipe needs; with 4 slots (= CS: every pair owns one slot) 2050.
+constexpr int kQSlotsMax = 4;
 
 struct __align__(8) PairBarriers {
   uint64_t g_full[kGStages], g_empty[kGStages];
   uint64_t v_full[kVStages], v_empty[kVStages];
   uint64_t s_full[2], s_empty[2];
-  uint64_t nj_full[2];
-  uint64_t p_full[kQSlots], slot_free[kQSlots], p_pair[kQSlots], pub_full[kQSlots];
+  uint64_t nj_full[2], nj_empty[2];
+  uint64_t p_full[kQSlotsMax], slot_free[kQSlotsMax], p_pair[kQSlotsMax], pub_full[kQSlotsMax], own_free[kQSlotsMax];
   uint64_t o_full;
   uint32_t tmem_base;
   float red[8][4];
 };
 
-constexpr int kQSmemG = 0;
-constexpr int kQSmemV = kQSmemG + kGStages * kGStageBytes;
-constexpr int kQSmemP = kQSmemV + kVStages * kVStageBytes;
-constexpr int kQSmemNj = kQSmemP + kQSlots * kQPBytes;
-constexpr int kQSmemBar = kQSmemNj + 2 * kTile * 4;
-constexpr int kQSmemTotal = kQSmemBar + static_cast<int>(sizeof(PairBarriers));
-static_assert(kQSmemTotal <= 232448, "shared memory budget");
-static_assert(kQSmemV % 1024 == 0 && kQSmemP % 1024 == 0, "operand tiles need 1024-byte alignment");
+template <bool G256> struct PairCfg {
+  static constexpr int GS = G256 ? kG2Stages : kGStages;            // Gram ring stages
+  static constexpr int GSB = G256 ? kG2StageBytes : kGStageBytes;   // bytes per stage
+  static constexpr int QS = G256 ? VG_G2_SLOTS : 3;                 // P slots, 32 KiB each
+  static constexpr int SmemG = 0;
+  static constexpr int SmemV = SmemG + GS * GSB;
+  static constexpr int SmemP = SmemV + kVStages * kVStageBytes;
+  static constexpr int SmemNj = SmemP + QS * kQPBytes;
+  static constexpr int SmemBar = SmemNj + 2 * kTile * 4;
+  static constexpr int SmemTotal = SmemBar + static_cast<int>(sizeof(PairBarriers));
+  static_assert(SmemTotal <= 232448, "shared memory budget");
+  static_assert(SmemV % 1024 == 0 && SmemP % 1024 == 0, "operand tiles need 1024-byte alignment");
+  static_assert(QS * kQPBytes <= kXchgBytesPerSm, "exchange scratch per SM");
+};
 
 #define VG_PAIR_DECODE_RANGE \
     long long w_lo, w_hi; \
@@ -78,9 +101,9 @@ static_assert(kQSmemV % 1024 == 0 && kQSmemP % 1024 == 0, "operand tiles need 10
     else { w_lo = tail_begin; w_hi = w_end; } \
     const int unit_g = static_cast<int>(w_lo / K); \
     const int r0 = static_cast<int>(w_lo - static_cast<long long>(unit_g) * K); \
-    const int Kp = static_cast<int>(w_hi - w_lo); \
- \
-    const bool partial = Kp < K; \
+    const int Kv = static_cast<int>(w_hi - w_lo);      /* rounds that count */ \
+    const int Kp = G256 ? ((Kv + 1) & ~1) : Kv;        /* rounds that run (G256: even, the extra one has zero weights) */ \
+    const bool partial = Kv < K; \
     const int TTp = Kp * CS; \
     const int tile0 = r0 * CS; \
     const int grp = unit_g % p.ngroups; \
@@ -94,7 +117,7 @@ static_assert(kQSmemV % 1024 == 0 && kQSmemP % 1024 == 0, "operand tiles need 10
     const int my_chunks = slice_chunks >> 1; \
     (void)0
 
-template <bool LADDER>
+template <bool LADDER, bool G256>
 __global__ void __launch_bounds__(kQThreads, 1)
 mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__ CUtensorMap zmap64,
                     const __grid_constant__ CUtensorMap vmap64, const TcParams p) {
@@ -102,6 +125,10 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
   // GEMM (64-row boxes); one array on the plain bf16 path, the split arrays of prologue.cu with BF16X3
   extern __shared__ __align__(1024) uint8_t smem[];
   if ((smem_u32(smem) & 1023u) != 0) __trap();
+  using Cfg = PairCfg<G256>;
+  constexpr int kQSlots = Cfg::QS;
+  constexpr int kQSmemG = Cfg::SmemG, kQSmemV = Cfg::SmemV, kQSmemP = Cfg::SmemP, kQSmemNj = Cfg::SmemNj,
+                kQSmemBar = Cfg::SmemBar;
   PairBarriers* bar = reinterpret_cast<PairBarriers*>(smem + kQSmemBar);
   float* nj_smem = reinterpret_cast<float*>(smem + kQSmemNj);
 
@@ -148,12 +175,14 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
       mbar_init(&bar->s_full[b], 1);
       mbar_init(&bar->s_empty[b], hh == 0 ? 512 : 256);   // leader: both epilogues
       mbar_init(&bar->nj_full[b], 1);
+      mbar_init(&bar->nj_empty[b], 256);                  // this CTA's epilogue threads
     }
     for (int s = 0; s < kQSlots; ++s) {
       mbar_init(&bar->p_full[s], 1);
       mbar_init(&bar->slot_free[s], CS);
       mbar_init(&bar->p_pair[s], 1);
       mbar_init(&bar->pub_full[s], 1);
+      mbar_init(&bar->own_free[s], 1);
     }
     mbar_init(&bar->o_full, 1);
     fence_barrier_init();
@@ -177,7 +206,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
   // ---- pipeline state that persists across the work ranges of this CTA (each warp uses its role's part)
   uint32_t rs = 0, rph = 0;            // ring stage / phase: G ring (warps 8, 11, 9), V ring (warps 12, 10)
   uint32_t kg = 0;                     // Gram tiles of this CTA so far: S / norm buffer kg & 1, parity (kg >> 1) & 1
-  uint32_t pf_mask = 0, sf_mask = 0, pub_mask = 0;   // per-slot phase parities of p_full / slot_free / pub_full
+  uint32_t pf_mask = 0, sf_mask = 0, pub_mask = 0, of_mask = 0;   // per-slot phase parities of p_full / slot_free / pub_full / own_free
   uint32_t part = 0;                   // parity of o_full
   long long tm0 = 0, tm1 = 0, tm2 = 0, tm3 = 0;      // debug timers (meaning depends on the role)
   const long long t_begin = VG_CLK();
@@ -193,10 +222,33 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     setmaxnreg_dec<64>();
     for (int pi = 0; pi < n_parts; ++pi, ++part) {
     VG_PAIR_DECODE_RANGE;
-    (void)partial; (void)dup; (void)row_is_x;
+    (void)partial; (void)dup; (void)row_is_x; (void)Kv;
   if (warp == 8 || warp == 11) {
     // ===================== G producers: Gram operand stages, in the Gram warp's order =====================
     const uint32_t pj = warp == 8 ? 0u : 1u;
+    if constexpr (G256) {
+      uint32_t it = 0;
+      for (int k = 0; k < Kp; k += 2) {
+        const int jt = min(tile0 + CS * (k + hh) + c, T - 1);   // leader: column tile of round k, peer: of round k + 1
+        for (int kc = 0; kc < p.gchunks; ++kc, ++it) {
+          if ((it & 1u) == pj) {
+            mbar_wait(&bar->g_empty[rs], rph ^ 1);
+            uint8_t* dst = smem + kQSmemG + rs * kG2StageBytes;
+            if (p.dbg_flags & 2) {            // measurement only: no operand loads
+              if (lane == 0 && hh == 0) mbar_arrive(&bar->g_full[rs]);
+            } else if (lane == 0) {
+              if (hh == 0) mbar_arrive_expect_tx(&bar->g_full[rs], 2 * kG2StageBytes);
+              tma_load_2d_2cta(dst, &zmap, &bar->g_full[rs], kc * kChunk, ti * kTile);
+            } else if (lane <= 2) {           // the 128 rows of this CTA's column tile as two 64-row boxes
+              tma_load_2d_2cta(dst + kChunkBytes + (lane - 1) * (kChunkBytes / 2), &zmap64, &bar->g_full[rs],
+                               kc * kChunk, jt * kTile + 64 * (lane - 1));
+            }
+            __syncwarp();
+          }
+          if (++rs == kG2Stages) { rs = 0; rph ^= 1; }
+        }
+      }
+    } else {
     for (int k = 0; k < Kp; ++k) {
       const int jt = min(tile0 + CS * k + c, T - 1);
       for (int kc = 0; kc < p.gchunks; ++kc) {
@@ -215,6 +267,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
         }
         if (++rs == kGStages) { rs = 0; rph ^= 1; }
       }
+    }
     }
   } else if (warp == 12) {
     // ===================== V producer: half tiles of Z_J[:, this CTA's half of the slice] =====================
@@ -244,7 +297,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
       for (int k = 0; k < Kp; ++k, ++kg) {
         const int jt = min(tile0 + CS * k + c, T - 1);
         const uint32_t b = kg & 1;
-        mbar_wait(&bar->s_empty[b], ((kg >> 1) & 1) ^ 1);
+        mbar_wait(&bar->nj_empty[b], ((kg >> 1) & 1) ^ 1);
         mbar_arrive_expect_tx(&bar->nj_full[b], kTile * 4);
         bulk_load_1d(nj_smem + b * kTile, p.nrms + static_cast<int64_t>(jt) * kTile, kTile * 4,
                      &bar->nj_full[b]);
@@ -269,6 +322,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
         const uint32_t src = smem_u32(smem + kQSmemP + slot * kQPBytes);
         if (p.dbg_flags & 8) {
           // DSMEM route: one bulk copy per peer (~12 B/clk per SM: 3 x 32 KiB take ~8000 cycles)
+          if (t >= kQSlots) mbar_wait(&bar->slot_free[slot], (sf_mask >> slot) & 1);
           for (int d = 0; d < CS; ++d)
             if (d != c) {
               const uint32_t peer = static_cast<uint32_t>(2 * d + hh);
@@ -277,12 +331,17 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
         } else {
           // L2 route: bulk store to this SM's scratch slot, then ONE multicast bulk load into the same slot of
           // every peer.  The scratch slot is free for the same reason the shared-memory slot is (slot_free).
+          // The store to L2 does not wait for the receivers: the tile was parked as soon as THIS pair's PV(t - slots)
+          // had finished (own_free).  Only the multicast load into the peers' slots waits until every pair is done
+          // with the slot's previous tile, so store + commit are off the slot loop's critical path.
           uint8_t* g = xbase + slot * kQPBytes;
           bulk_store_global(g, src, pbytes);
           bulk_commit_wait_all();
+          if (t >= kQSlots) mbar_wait(&bar->slot_free[slot], (sf_mask >> slot) & 1);   // every CTA finished PV(t - kQSlots)
           bulk_load_multicast(src, g, pbytes, smem_u32(&bar->p_full[slot]), peers);
         }
       }
+      if (t >= kQSlots) sf_mask ^= 1u << slot;
       __syncwarp();
     }
   } else if (warp == 9 && hh == 1) {
@@ -308,6 +367,44 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     constexpr uint32_t idesc_gram = make_idesc_bf16(2 * kTile, kTile, 0, 0);
     constexpr uint32_t desc_hi = (1024u >> 4) | (1u << 14) | (2u << 29);
     const uint32_t g_lo = (smem_u32(smem + kQSmemG) & 0x3FFFFu) >> 4;
+    if constexpr (G256) {
+      constexpr uint32_t idesc_gram2 = make_idesc_bf16(2 * kTile, 2 * kTile, 0, 0);
+      for (int k = 0; k < Kp; k += 2, kg += 2) {       // kg is even here: tile k -> S[0], tile k + 1 -> S[1]
+        {
+          const long long t0 = VG_CLK();
+          const uint32_t par = ((kg >> 1) & 1) ^ 1;
+          mbar_wait(&bar->s_empty[0], par);              // both CTAs' epilogues released S[0] and S[1]
+          mbar_wait(&bar->s_empty[1], par);
+          tm1 += VG_CLK() - t0;
+        }
+        tc_fence_after();
+        for (int kc = 0; kc < p.gchunks; ++kc) {
+          {
+            const long long t0 = VG_CLK();
+            mbar_wait(&bar->g_full[rs], rph);
+            tm0 += VG_CLK() - t0;
+          }
+          tc_fence_after();
+          const uint32_t a_lo = g_lo + rs * (kG2StageBytes >> 4);
+          const uint32_t b_lo = a_lo + (kChunkBytes >> 4);
+          if (elect_one()) {
+#pragma unroll
+            for (int kk = 0; kk < kChunk / 16; ++kk) {
+              const uint64_t adesc = (static_cast<uint64_t>(desc_hi) << 32) | (a_lo + kk * 2);
+              const uint64_t bdesc = (static_cast<uint64_t>(desc_hi) << 32) | (b_lo + kk * 2);
+              umma_bf16_ss_2cta(tmem, adesc, bdesc, idesc_gram2, (kc | kk) != 0);
+            }
+            umma_commit_2cta_mc(&bar->g_empty[rs], pair_mask);
+            if (kc == p.gchunks - 1) {
+              umma_commit_2cta_mc(&bar->s_full[0], pair_mask);
+              umma_commit_2cta_mc(&bar->s_full[1], pair_mask);
+            }
+          }
+          __syncwarp();
+          if (++rs == kG2Stages) { rs = 0; rph ^= 1; }
+        }
+      }
+    } else {
     for (int k = 0; k < Kp; ++k, ++kg) {
       const uint32_t b = kg & 1;
       const uint32_t d_tmem = tmem + b * kTile;
@@ -339,6 +436,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
         __syncwarp();
         if (++rs == kGStages) { rs = 0; rph ^= 1; }
       }
+    }
     }
   } else if (warp == 10 && hh == 0) {
     // ===================== leader CTA: PV MMA stream =====================
@@ -387,8 +485,11 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
         }
       }
       // both CTAs of the pair are done with slot: tell the two writers (rows I0 and I1) of tile t + kQSlots
-      if (t + kQSlots < TTp && elect_one())
+      if (t + kQSlots < TTp && elect_one()) {
         umma_commit_2cta_mc(&bar->slot_free[slot], static_cast<uint16_t>(3u << (2 * ((t + kQSlots) % CS))));
+        // the next tile of this slot is written by this pair: its epilogues may park it once OUR PV(t) is done
+        if ((t + kQSlots) % CS == c) umma_commit_2cta_mc(&bar->own_free[slot], pair_mask);
+      }
       __syncwarp();
     }
     if (elect_one()) umma_commit_2cta_mc(&bar->o_full, pair_mask);
@@ -420,36 +521,49 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
       coef_y[m] = p.par[18 + m];
     }
     float acc_x = 0.f, acc_y = 0.f, rsum = 0.f;
-    for (int k = 0; k < Kp; ++k, ++kg) {
-      const int t = CS * k + c;                          // tile index within the range (slot protocol)
-      const int tg = tile0 + t;                          // column tile
-      const bool valid = tg < T;
-      const int jt = min(tg, T - 1);
-      const uint32_t b = kg & 1;
-      const bool col_is_x = jt < p.tiles_x;
+    // One column tile = three steps.  load: wait for S[b] (and the norms), pull this thread's 64 columns into registers
+    // and release S[b] at once (before the math), so the next Gram into the buffer overlaps the tile's whole epilogue;
+    // compute: kernel values, sums, P as bf16; park: P into its shared-memory slot for the PV warp and the publisher.
+    auto load_S = [&](uint32_t b, uint32_t par, uint32_t (&va)[32], uint32_t (&vb)[32]) {
+      const long long tq = VG_CLK();
+      mbar_wait(&bar->nj_full[b], par);
+      mbar_wait(&bar->s_full[b], par);
+      tm0 += VG_CLK() - tq;
+      tc_fence_after();
+      const uint32_t taddr = tmem + lane_addr + b * kTile + g * 64;
+      tmem_ld_32x32(taddr, va);
+      tmem_ld_32x32(taddr + 32, vb);
+      tmem_ld_wait();
+      tc_fence_before();
+      mbar_arrive(&bar->s_empty[b]);
+      if (hh == 1) mbar_remote_arrive(mapa_u32(smem_u32(&bar->s_empty[b]), static_cast<uint32_t>(rank - 1)));
+    };
+    auto compute = [&](int k, uint32_t b, const uint32_t (&va)[32], const uint32_t (&vb)[32], uint4 (&pk)[8]) {
+      const long long tq = VG_CLK();
+      const int tg = tile0 + CS * k + c;                 // column tile
+      const bool valid = tg < T && k < Kv;               // padded rounds (tail of a unit, G256 padding): zero weights
+      const bool col_is_x = min(tg, T - 1) < p.tiles_x;
       float cf[VGAN_B200_MAX_SCALES];
 #pragma unroll
       for (int m = 0; m < VGAN_B200_MAX_SCALES; ++m) cf[m] = valid ? (col_is_x ? coef_x[m] : coef_y[m]) : 0.f;
-      long long tq = VG_CLK();
-      mbar_wait(&bar->nj_full[b], (kg >> 1) & 1);
-      mbar_wait(&bar->s_full[b], (kg >> 1) & 1);
-      tm0 += VG_CLK() - tq; tq = VG_CLK();
-      tc_fence_after();
       const float* njp = nj_smem + b * kTile + g * 64;
       float ksum = 0.f;
-      uint4 pk[8];
-      epi_tile_64<LADDER>(tmem + lane_addr + b * kTile + g * 64, njp, ni, m2c0, cf, ratio, p.n_scales, ksum, rsum, pk,
-                          p.p_lo != 0);
-      tc_fence_before();
-      mbar_arrive(&bar->s_empty[b]);          // S and the norms are free; P is parked in registers
-      if (hh == 1) mbar_remote_arrive(mapa_u32(smem_u32(&bar->s_empty[b]), static_cast<uint32_t>(rank - 1)));
+      uint4 h0[4], h1[4];
+      epi_compute_32<LADDER>(va, njp, ni, m2c0, cf, ratio, p.n_scales, ksum, rsum, h0, p.p_lo != 0);
+      epi_compute_32<LADDER>(vb, njp + 32, ni, m2c0, cf, ratio, p.n_scales, ksum, rsum, h1, p.p_lo != 0);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) { pk[i] = h0[i]; pk[4 + i] = h1[i]; }
+      mbar_arrive(&bar->nj_empty[b]);                    // the column norms of this tile are no longer read
       if (valid) { if (col_is_x) acc_x += ksum; else acc_y += ksum; }
-      // ---- park the P tile in its slot; the publisher warp sends it to the other slices of this row tile
+      tm1 += VG_CLK() - tq;
+    };
+    auto park = [&](int k, const uint4 (&pk)[8]) {
+      long long tq = VG_CLK();
+      const int t = CS * k + c;                          // tile index within the range (slot protocol)
       const int slot = t % kQSlots;
-      tm1 += VG_CLK() - tq; tq = VG_CLK();
       if (t >= kQSlots) {
-        mbar_wait(&bar->slot_free[slot], (sf_mask >> slot) & 1);   // every CTA finished PV(t - kQSlots)
-        sf_mask ^= 1u << slot;
+        mbar_wait(&bar->own_free[slot], (of_mask >> slot) & 1);    // this pair finished PV(t - kQSlots)
+        of_mask ^= 1u << slot;
       }
       tm2 += VG_CLK() - tq; tq = VG_CLK();
       uint8_t* p_slot = smem + kQSmemP + slot * kQPBytes;
@@ -464,6 +578,29 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
         mbar_arrive(&bar->pub_full[slot]);   // publisher warp
       }
       tm3 += VG_CLK() - tq;
+    };
+    if constexpr (G256) {
+      // both S buffers fill together: S[1] is pulled (and released) right after the math of S[0], before P(k) waits
+      // for its slot, so the next two-tile Gram starts one tile's math after s_full instead of a whole tile later
+      for (int k = 0; k < Kp; k += 2, kg += 2) {
+        const uint32_t par = (kg >> 1) & 1;
+        uint4 pk0[8], pk1[8];
+        uint32_t va[32], vb[32];
+        load_S(0, par, va, vb);
+        compute(k, 0, va, vb, pk0);
+        load_S(1, par, va, vb);
+        park(k, pk0);
+        compute(k + 1, 1, va, vb, pk1);
+        park(k + 1, pk1);
+      }
+    } else {
+      for (int k = 0; k < Kp; ++k, ++kg) {
+        uint4 pk[8];
+        uint32_t va[32], vb[32];
+        load_S(kg & 1, (kg >> 1) & 1, va, vb);
+        compute(k, kg & 1, va, vb, pk);
+        park(k, pk);
+      }
     }
     // ---- partial sums of this CTA's tiles
     acc_x = warp_sum(acc_x);
@@ -541,12 +678,16 @@ int launch_tc_pair(const TcParams& p, const CUtensorMap& map, const CUtensorMap&
   if (resident_ctas) *resident_ctas = 0;
   const int ngrad = (p.gx_end - p.gx_begin) + (p.gy_end - p.gy_begin);
   if (ngrad <= 0) return VGAN_B200_OK;
-  auto kern = ladder ? mmd2_tc_pair_kernel<true> : mmd2_tc_pair_kernel<false>;
-  VG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kQSmemTotal));
+  // VGAN_B200_GRAM256=0 selects the one-column-tile-per-issue Gram (the round-1 structure) for A/B measurements
+  static const int gram256 = getenv("VGAN_B200_GRAM256") ? atoi(getenv("VGAN_B200_GRAM256")) : 1;
+  auto kern = gram256 ? (ladder ? mmd2_tc_pair_kernel<true, true> : mmd2_tc_pair_kernel<false, true>)
+                      : (ladder ? mmd2_tc_pair_kernel<true, false> : mmd2_tc_pair_kernel<false, false>);
+  const int smem_bytes = gram256 ? PairCfg<true>::SmemTotal : PairCfg<false>::SmemTotal;
+  VG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
   const int n_units = ((ngrad + 1) / 2) * p.ngroups;
   cudaLaunchConfig_t cfg{};
   cfg.blockDim = dim3(kQThreads);
-  cfg.dynamicSmemBytes = kQSmemTotal;
+  cfg.dynamicSmemBytes = smem_bytes;
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -556,7 +697,7 @@ int launch_tc_pair(const TcParams& p, const CUtensorMap& map, const CUtensorMap&
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   // persistent grid: as many clusters as can be resident at once (cached per cluster size)
-  static int max_clusters[9] = {0};
+  static int max_clusters[9] = {0};   // the same for all four instantiations (same block size and shared memory)
   int& ncl = max_clusters[2 * p.cs];
   if (ncl == 0) {
     cfg.gridDim = dim3(static_cast<unsigned>(2 * p.cs * 64));
