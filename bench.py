@@ -287,8 +287,8 @@ def main():
                 "gpu_launches": KERNELS_PER_STEP * args.steps,
                 "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
                              "frac": achieved / peak,
-                             # DRAM read+write bytes of one pair-kernel launch, ncu --set full (profiles/r1f_pair_k1_summary.txt)
-                             "traffic": (10.73e9 / world) if (N, D) == (N_DEFAULT, D_DEFAULT) else None, "peak_source": peak_src,
+                             # DRAM read+write bytes of one pair-kernel launch, ncu --set full (profiles/r1h_pair_k1_summary.txt)
+                             "traffic": (11.22e9 / world) if (N, D) == (N_DEFAULT, D_DEFAULT) else None, "peak_source": peak_src,
                              "kernel": "mmd2_tc_pair_kernel (gradient units) with mmd2_xx_kernel (S_xx sums) overlapped",
                              "kernel_ms": k1_ms,
                              "algorithmic": "8*N^2*D flops per evaluation (SURVEY.md 8(d))"},

@@ -28,4 +28,4 @@ print(f"persistent pair kernel, cycles per round (4 tiles), {R:.0f} rounds per c
 print("  Gram warp: wait_g_ring %.0f  wait_s_empty %.0f   kernel total %.0f" % (lead[:, 0].mean() / R, lead[:, 1].mean() / R, lead[:, 12].mean() / R))
 print("  PV warp:   wait_p %.0f  wait_v_ring %.0f" % (lead[:, 10].mean() / R, lead[:, 11].mean() / R))
 print("  SM clock %.0f MHz ; tail (syncs + gradient rows) %.0f cycles per round" % (1e3 * lead[:, 12].mean() / lead[:, 13].mean(), d[:, 14].mean() / R))
-print("  epilogue:  wait_s_full %.0f  compute %.0f  wait_slot %.0f  park+sync %.0f" % tuple(d[:, i].mean() / R for i in (4, 5, 6, 7)))
+print("  epilogue:  wait_s_full %.0f  compute %.0f  wait_own_free %.0f  park+sync %.0f  (the TMEM loads are not in these)" % tuple(d[:, i].mean() / R for i in (4, 5, 6, 7)))

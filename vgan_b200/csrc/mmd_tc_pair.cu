@@ -24,6 +24,11 @@
 // unit cut between two clusters accumulates its gradient rows with red.global.add (dY zeroed by the host).
 // Only the leader issues MMAs; the peer's epilogue arrives on the leader's s_empty, the peer's warp 9
 // forwards its p_full to the leader (p_pair), and every tcgen05.commit is multicast to both CTAs.
+// Slot loop of the P tiles (what bounds the kernel: tools/gpu_cluster_timers.py, and 8 820 instead of 11 180 cycles
+// per round when the exchange moves 16 bytes): a tile is PARKED as soon as this pair's own PV of the slot's previous
+// tile is done (own_free) and stored to L2 at once; only the multicast load into the peers' slots waits until every
+// pair has finished with the previous tile (slot_free, waited by the publisher), so the store is off the loop.
+// S[b] is released right after its columns reach registers (the column norms have their own barrier, nj_empty).
 #include <cstdlib>
 
 #include "common.cuh"
