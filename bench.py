@@ -156,6 +156,12 @@ def main():
     if args.impl == "reference":
         return run_reference(args)
 
+    # stdout carries exactly ONE line (the JSON): whatever libraries print there (NCCL's version banner at N > 1)
+    # goes to stderr instead
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
+
     import torch.distributed as dist
     from vgan_b200 import MMDLossConstrained, RBF
     from vgan_b200.dist import data_parallel_masked_step, sharded_masked_step
@@ -307,7 +313,8 @@ def main():
                                     "kind": "port",
                                     "sample": f"gradient rows [0,{rows}) of N={N} vs all 2N columns + matching "
                                               f"share of XxX, {dt:.1f}s of CPU work, scaled by N/rows"}
-        print(json.dumps(line))
+        sys.stdout.flush()
+        os.write(json_fd, (json.dumps(line) + "\n").encode())
     if world > 1:
         dist.destroy_process_group()
 
