@@ -68,9 +68,10 @@ constexpr int kQPBytes = 2 * kChunkBytes;
 constexpr int kQThreads = 512;   // warps: 0-7 epilogue (192 registers), 8-15 service (64 registers): 8/11 G producers,
                                  // 9 Gram MMA (peer: P forwarder), 10 PV MMA, 12 V producer, 13 P publisher, 14 norms
 static_assert(kGStages % kGProducers == 0, "each G producer warp owns fixed ring stages");
-// G256 spends the 32 KiB its smaller ring frees on a FOURTH P slot: the loop  P(t) parked -> exchanged -> PV(t) done in
-// every pair -> slot free -> P(t + slots) parked  takes ~8200 cycles (tools/gpu_cluster_timers.py), i.e. 2730 per column
-// tile with 3 slots against the 2048 the tensor pipe needs; with 4 slots (= CS: every pair owns one slot) 2050.
+// VG_G2_STAGES / VG_G2_SLOTS are tuning knobs of the G256 variant (same shared-memory total either way).  Measured
+// (tools/gpu_cluster_timers.py, cycles per round of 4 column tiles): 3 stages + 3 P slots 10 840; 2 stages + 4 slots
+// 12 710 — the Gram warp then waits 6 600 cycles per round for operands, and the slot wait does not shrink because
+// the in-order PV stream of every pair stalls on whichever pair is late.
 constexpr int kQSlotsMax = 4;
 
 struct __align__(8) PairBarriers {
