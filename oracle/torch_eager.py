@@ -1,40 +1,56 @@
-"""Torch-eager restatement of the reference loss module, line by line
-(/root/reference/src/models/Mmd_loss_constrained.py:5-50), usable on any torch device.
-TEST / MEASUREMENT INFRASTRUCTURE ONLY: it is the "torch-eager on B200" arm of the sweep
- and a checker; the product never imports it."""
+"""Dense torch evaluation of V-GAN's squared-MMD loss on any torch device — the "torch-eager on the same B200"
+arm of tools/sweep.py and a checker.  TEST / MEASUREMENT INFRASTRUCTURE ONLY; nothing under vgan_b200/ imports it.
+
+It materialises what the reference module materialises (the [n, n] distance matrix of the stacked sample and one
+[n, n] kernel layer per bandwidth), so it only runs where that fits; autograd gives the backward.  Follows
+/root/reference/src/models/Mmd_loss_constrained.py: multipliers 2^(m-2) (:12-13), bandwidth = sum of squared
+distances / (n^2 - n) on the first call, then frozen (:16-22), kernel = sum_m exp(-d^2 / (bandwidth * mult_m)) (:24-26),
+biased block means and the column-max penalty (:42-50).  Pinned on CPU against tests/golden/*.npz
+(tests/test_oracle.py::test_torch_eager_matches_golden).
+"""
 import torch
-from torch import nn
 
 
-class RBF(nn.Module):
+def stacked_sq_distances(Z: torch.Tensor) -> torch.Tensor:
+    d = torch.cdist(Z, Z)
+    return d * d
+
+
+def kernel_sum(sq: torch.Tensor, bandwidth: torch.Tensor, multipliers: torch.Tensor) -> torch.Tensor:
+    scales = (bandwidth * multipliers).reshape(-1, 1, 1)
+    return torch.exp(-sq.unsqueeze(0) / scales).sum(0)
+
+
+def column_max_penalty(U: torch.Tensor, weight: float) -> torch.Tensor:
+    top = torch.topk(U, 1, dim=0).values.reshape(-1)
+    return weight * (1.0 - top).mean()
+
+
+class RBF(torch.nn.Module):
     def __init__(self, n_kernels=5, mul_factor=2.0, bandwidth=None, device="cuda"):
         super().__init__()
-        self.bandwidth_multipliers = (mul_factor ** (torch.arange(n_kernels) - n_kernels // 2)).to(device)
+        exponents = torch.arange(n_kernels) - n_kernels // 2
+        self.bandwidth_multipliers = (mul_factor ** exponents).to(device)
         self.bandwidth = bandwidth
 
-    def get_bandwidth(self, L2_distances):
-        if self.bandwidth is None:
-            n_samples = L2_distances.shape[0]
-            self.bandwidth = L2_distances.data.sum() / (n_samples ** 2 - n_samples)
-        return self.bandwidth
-
-    def forward(self, X):
-        L2_distances = torch.cdist(X, X) ** 2
-        return torch.exp(-L2_distances[None, ...] /
-                         (self.get_bandwidth(L2_distances) * self.bandwidth_multipliers)[:, None, None]).sum(dim=0)
+    def forward(self, Z):
+        sq = stacked_sq_distances(Z)
+        if self.bandwidth is None:                       # first call fixes it for good
+            n = sq.shape[0]
+            self.bandwidth = sq.detach().sum() / (n * n - n)
+        return kernel_sum(sq, self.bandwidth, self.bandwidth_multipliers.to(sq.dtype))
 
 
-class MMDLossConstrained(nn.Module):
+class MMDLossConstrained(torch.nn.Module):
     def __init__(self, weight, kernel=None, device="cuda"):
         super().__init__()
-        self.kernel = RBF(device=device) if kernel is None else kernel
+        self.kernel = kernel if kernel is not None else RBF(device=device)
         self.weight = weight
         self.device = device
 
     def forward(self, X, Y, U):
-        K = self.kernel(torch.vstack([X, Y]))
+        nx = X.shape[0]
+        K = self.kernel(torch.cat([X, Y], dim=0))
         self.bandwidth = self.kernel.bandwidth
-        n = X.shape[0]
-        XX, XY, YY = K[:n, :n].mean(), K[:n, n:].mean(), K[n:, n:].mean()
-        return XX - 2 * XY + YY + self.weight * torch.mean(
-            torch.ones(U.shape[1], device=self.device) - torch.topk(U, 1, 0).values)
+        mmd2 = K[:nx, :nx].mean() - 2.0 * K[:nx, nx:].mean() + K[nx:, nx:].mean()
+        return mmd2 + column_max_penalty(U, self.weight)

@@ -121,3 +121,21 @@ def test_oracle_vs_live_reference_fp64():
     g = _golden("unequal_200_328")
     assert out["loss"] == pytest.approx(float(g["loss"]), rel=1e-13)
     np.testing.assert_allclose(out["dY"], g["dY"], rtol=1e-12)
+
+
+@pytest.mark.parametrize("name", ["tiny_8x4", "ragged_37x5", "cfg1_500x20", "unequal_200_328", "dups_96x12"])
+def test_torch_eager_matches_golden(name):
+    """oracle/torch_eager.py (the torch-eager arm of tools/sweep.py) reproduces the reference module's fp64 results."""
+    from oracle import torch_eager
+    g = _golden(name)
+    X, Y, U, weight, kind = build_case(name)
+    Xt = torch.tensor(X, dtype=torch.float64, requires_grad=True)
+    Ut = torch.tensor(U, dtype=torch.float64, requires_grad=True)
+    Yt = torch.tensor(Y, dtype=torch.float64) if kind == "free" else Ut * Xt.detach()
+    fn = torch_eager.MMDLossConstrained(weight, kernel=torch_eager.RBF(device="cpu"), device="cpu")
+    loss = fn(Xt, Yt, Ut)
+    loss.backward()
+    assert float(fn.bandwidth) == pytest.approx(float(g["bandwidth"]), rel=1e-10)
+    assert float(loss) == pytest.approx(float(g["loss"]), rel=1e-8, abs=1e-12)
+    if "dU" in g.files:
+        np.testing.assert_allclose(Ut.grad.numpy(), g["dU"], rtol=1e-6, atol=1e-12)
