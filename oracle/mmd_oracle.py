@@ -302,3 +302,56 @@ def cpu_blockwise_fwd_bwd(X: torch.Tensor, U: torch.Tensor, bandwidth: float,
             sums[0] += float(k.sum())
         dU[i0 - row_begin:i1 - row_begin] = 4.0 * cy * (O - r[:, None] * Yi) * Xi
     return sums, dU
+
+
+def bench_sample_fp64(X: torch.Tensor, U: torch.Tensor, bandwidth: float, row_begin: int, row_end: int,
+                      xx_tile: int, tile: int = 128, block: int = 4096):
+    """fp64 truth for a SAMPLE of one masked evaluation at sizes where the full oracle would take hours
+    (N = 65536, D = 1024): the gradient rows [row_begin, row_end) of Y = U*X against all 2N columns (their S_xy, S_yy
+    share and dL/dU rows, Mmd_loss_constrained.py:46-50 + autograd) and the share of S_xx that the X row tile
+    ``xx_tile`` owns when the symmetric X x X block is walked by its upper triangle: the diagonal tile once, every
+    tile to its right twice.  Also the fp32 port's own dU error on the same rows (the reference-precision yard-stick).
+    """
+    N = X.shape[0]
+    Xd = X.double()
+    Yd = (U.double() * Xd)
+    s = scales(bandwidth, bandwidth_multipliers())
+    cx, cy = 1.0 / N, -1.0 / N
+    nX = (Xd * Xd).sum(1)
+    nY = (Yd * Yd).sum(1)
+    Yi = Yd[row_begin:row_end]
+    O = torch.zeros_like(Yi)
+    r = torch.zeros(row_end - row_begin, dtype=torch.float64)
+    sxy = syy = 0.0
+    for j0 in range(0, N, block):
+        j1 = min(j0 + block, N)
+        for (B, nB, cj, is_x) in ((Xd[j0:j1], nX[j0:j1], cx, True), (Yd[j0:j1], nY[j0:j1], cy, False)):
+            d2 = (nY[row_begin:row_end, None] + nB[None, :] - 2.0 * (Yi @ B.T)).clamp_min_(0)
+            k = torch.zeros_like(d2)
+            w = torch.zeros_like(d2)
+            for sm in s:
+                e = torch.exp(-d2 / sm)
+                k += e
+                w += e / sm
+            if is_x:
+                sxy += float(k.sum())
+            else:
+                syy += float(k.sum())
+            w *= cj
+            O += w @ B
+            r += w.sum(1)
+    dU = 4.0 * cy * (O - r[:, None] * Yi) * Xd[row_begin:row_end]
+    t0, t1 = xx_tile * tile, min((xx_tile + 1) * tile, N)
+    Xi = Xd[t0:t1]
+    sxx = 0.0
+    for j0 in range(t0, N, block):
+        j1 = min(j0 + block, N)
+        d2 = (nX[t0:t1, None] + nX[None, j0:j1] - 2.0 * (Xi @ Xd[j0:j1].T)).clamp_min_(0)
+        k = torch.zeros_like(d2)
+        for sm in s:
+            k += torch.exp(-d2 / sm)
+        wgt = torch.where(torch.arange(j0, j1) < t1, 1.0, 2.0).double()
+        sxx += float((k * wgt[None, :]).sum())
+    _, dU32 = cpu_blockwise_fwd_bwd(X, U, bandwidth, row_begin, row_end)
+    ref32 = float((dU32.double() - dU).norm() / dU.norm())
+    return dict(sxy=sxy, syy=syy, dU=dU, sxx_tile=sxx, ref_fp32_dU=ref32)
