@@ -1,8 +1,10 @@
-// K2 — HBM-bound prologue kernels: stacked column statistics, operand packing
-// (Y = U*X masking, optional centering, bf16 cast, row norms), closed-form bandwidth and
-// the device-side parameter block.  Replaces vstack / the pow-sum prologue of
-// torch.cdist / `fake_subspaces*batch` / RBF.get_bandwidth
-// (/root/reference/src/models/Mmd_loss_constrained.py:16-22,43; src/vgan.py:616).
+// K2 — HBM-bound prologue / epilogue kernels of one evaluation:
+//   stats    per-block column sums and sums of squares of the rows in range (+ column maxima of U)
+//   scales   closed-form bandwidth, 1/scales, parameter block, centring mean, common-mode constants, penalty value
+//   pack     masking Y = U*X, centring, bf16 cast (or hi/lo split), row norms, exp2-scaled norms
+//   finalize loss value, penalty gradient
+// Replaces vstack / the pow-sum prologue of torch.cdist / `fake_subspaces*batch` / RBF.get_bandwidth / topk penalty
+// (/root/reference/src/models/Mmd_loss_constrained.py:16-22,43,50; src/vgan.py:616).
 #include "common.cuh"
 #include "ptx.cuh"
 
@@ -12,70 +14,278 @@ struct PackArgs {
   const float* X;
   const float* U;   // mask (Y = U*X) when Y == nullptr
   const float* Y;
-  int64_t Nx, Ny, D, Dp, Nxp, Nyp;
+  int64_t Nx, Ny, D, Dp, Nxp, Nyp, D_u;
+  int64_t rb, re;   // row range of X and of Y handled by this call
   int center, fp32, split;
   __nv_bfloat16* zq;
   __nv_bfloat16* zb;    // split operands (BF16X3): zq = row operand [hi | hi | lo], zb = column operand [hi | lo | hi],
                         // both [rows, 3 Dp]: sum_k zq[i,k] zb[j,k] = hi_i.hi_j + hi_i.lo_j + lo_i.hi_j
   float* zf;
   float* nrm;
-  float* mean;
-  double* stats;    // [0] sum |z|^2 (raw), [2+f] raw column sums
+  float* nrms;
+  const float* mean;
+  const float* par;
+  double* stats;    // [0] sum |x|^2, [1] sum |y|^2, [2 + f] column sums of X, [2 + Dp + f] column sums of Y (raw)
+  unsigned long long* cmax;   // packed column maxima of U, or nullptr
 };
 
-__device__ __forceinline__ float load_stacked(const PackArgs& a, int64_t zrow, int64_t f) {
-  // zrow indexes the un-padded stack [X ; Y]
-  if (zrow < a.Nx) return a.X[zrow * a.D + f];
-  const int64_t y = zrow - a.Nx;
-  return a.Y ? a.Y[y * a.D + f] : a.U[y * a.D + f] * a.X[y * a.D + f];
+__device__ __forceinline__ uint32_t float_key(float v) {      // order-preserving float -> uint
+  const uint32_t b = __float_as_uint(v);
+  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__device__ __forceinline__ float key_float(uint32_t k) {
+  return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
+}
+// larger value wins; on equal values the LOWER row index wins (CPU torch.topk's choice)
+__device__ __forceinline__ unsigned long long max_key(float v, int64_t row) {
+  return (static_cast<unsigned long long>(float_key(v)) << 32) |
+         static_cast<unsigned long long>(0xffffffffu - static_cast<uint32_t>(row));
 }
 
-// column sums + sum of squares of the raw stacked sample, double accumulation
-__global__ void __launch_bounds__(256) colstats_kernel(PackArgs a, int rows_per_block) {
-  const int64_t n = a.Nx + a.Ny;
-  const int64_t r0 = static_cast<int64_t>(blockIdx.x) * rows_per_block;
-  const int64_t r1 = min(r0 + rows_per_block, n);
-  float sq = 0.f;
-  for (int64_t f = threadIdx.x; f < a.D; f += blockDim.x) {
-    float cs = 0.f;
-    for (int64_t r = r0; r < r1; ++r) {
-      const float v = load_stacked(a, r, f);
-      cs += v;
-      sq = fmaf(v, v, sq);
-    }
-    atomicAdd(&a.stats[2 + f], static_cast<double>(cs));
-  }
-  sq = warp_sum(sq);
-  __shared__ float red[8];
-  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = sq;
+__device__ __forceinline__ float block_sum_256(float v, float* red) {
+  v = warp_sum(v);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
   __syncthreads();
-  if (threadIdx.x == 0) {
-    double t = 0.0;
+  float t = 0.f;
+  if (threadIdx.x == 0)
     for (int w = 0; w < 8; ++w) t += red[w];
-    atomicAdd(&a.stats[0], t);
+  __syncthreads();
+  return t;   // valid in thread 0
+}
+
+// ---- generic statistics: rows q of the range's stack [X rows rb..xe ; Y rows rb..ye)
+__global__ void __launch_bounds__(256) colstats_kernel(PackArgs a, int rows_per_block) {
+  const int64_t xe = min(a.re, a.Nx), ye = min(a.re, a.Ny);
+  const int64_t nX = max(xe - a.rb, static_cast<int64_t>(0)), nY = max(ye - a.rb, static_cast<int64_t>(0));
+  const int64_t q0 = static_cast<int64_t>(blockIdx.x) * rows_per_block;
+  const int64_t q1 = min(q0 + rows_per_block, nX + nY);
+  float sqx = 0.f, sqy = 0.f;
+  for (int64_t f = threadIdx.x; f < a.D; f += blockDim.x) {
+    float cx = 0.f, cy = 0.f;
+    for (int64_t q = q0; q < q1; ++q) {
+      if (q < nX) {
+        const float v = a.X[(a.rb + q) * a.D + f];
+        cx += v;
+        sqx = fmaf(v, v, sqx);
+      } else {
+        const int64_t y = a.rb + (q - nX);
+        const float v = a.Y ? a.Y[y * a.D + f] : a.U[y * a.D + f] * a.X[y * a.D + f];
+        cy += v;
+        sqy = fmaf(v, v, sqy);
+      }
+    }
+    if (q0 < nX) atomicAdd(&a.stats[2 + f], static_cast<double>(cx));
+    if (q1 > nX) atomicAdd(&a.stats[2 + a.Dp + f], static_cast<double>(cy));
+  }
+  __shared__ float red[8];
+  const float tx = block_sum_256(sqx, red);
+  const float ty = block_sum_256(sqy, red);
+  if (threadIdx.x == 0) {
+    if (tx != 0.f) atomicAdd(&a.stats[0], static_cast<double>(tx));
+    if (ty != 0.f) atomicAdd(&a.stats[1], static_cast<double>(ty));
   }
 }
 
-__global__ void __launch_bounds__(256) mean_kernel(PackArgs a) {
-  const int64_t f = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (f >= a.Dp) return;
-  const double n = static_cast<double>(a.Nx + a.Ny);
-  a.mean[f] = (a.center && f < a.D) ? static_cast<float>(a.stats[2 + f] / n) : 0.f;
+__global__ void __launch_bounds__(256)
+colmax_kernel(const float* __restrict__ U, int64_t r_begin, int64_t r_end, int64_t D, int rows_per_block,
+              unsigned long long* __restrict__ cmax) {
+  const int64_t r0 = r_begin + static_cast<int64_t>(blockIdx.x) * rows_per_block;
+  const int64_t r1 = min(r0 + rows_per_block, r_end);
+  for (int64_t d = threadIdx.x; d < D; d += blockDim.x) {
+    unsigned long long best = 0ull;
+    for (int64_t r = r0; r < r1; ++r) {
+      const unsigned long long key = max_key(U[r * D + d], r);
+      best = key > best ? key : best;
+    }
+    atomicMax(&cmax[d], best);
+  }
 }
 
-// one warp per stored (padded) row
-__global__ void __launch_bounds__(256) pack_kernel(PackArgs a) {
+// ---- masked fast path (Y = U*X, Nx == Ny, D % 4 == 0, 16-byte aligned inputs): X and U are read ONCE per pass
+// for both halves of the stack, with 16-byte loads; the column maxima of U ride along.
+__global__ void __launch_bounds__(256) colstats_masked_kernel(PackArgs a, int rows_per_block) {
+  const int64_t r0 = a.rb + static_cast<int64_t>(blockIdx.x) * rows_per_block;
+  const int64_t r1 = min(r0 + rows_per_block, min(a.re, a.Nx));
+  const int64_t D4 = a.D >> 2;
+  float sqx = 0.f, sqy = 0.f;
+  for (int64_t f4 = threadIdx.x; f4 < D4; f4 += blockDim.x) {
+    float4 cx = make_float4(0.f, 0.f, 0.f, 0.f), cy = cx;
+    unsigned long long m0 = 0ull, m1 = 0ull, m2 = 0ull, m3 = 0ull;
+    const float4* xp = reinterpret_cast<const float4*>(a.X) + r0 * D4 + f4;
+    const float4* up = reinterpret_cast<const float4*>(a.U) + r0 * D4 + f4;
+#pragma unroll 4
+    for (int64_t r = r0; r < r1; ++r, xp += D4, up += D4) {
+      const float4 x = __ldg(xp), u = __ldg(up);
+      const float4 y = make_float4(u.x * x.x, u.y * x.y, u.z * x.z, u.w * x.w);
+      cx.x += x.x; cx.y += x.y; cx.z += x.z; cx.w += x.w;
+      cy.x += y.x; cy.y += y.y; cy.z += y.z; cy.w += y.w;
+      sqx = fmaf(x.x, x.x, fmaf(x.y, x.y, fmaf(x.z, x.z, fmaf(x.w, x.w, sqx))));
+      sqy = fmaf(y.x, y.x, fmaf(y.y, y.y, fmaf(y.z, y.z, fmaf(y.w, y.w, sqy))));
+      if (a.cmax) {
+        unsigned long long k;
+        k = max_key(u.x, r); m0 = k > m0 ? k : m0;
+        k = max_key(u.y, r); m1 = k > m1 ? k : m1;
+        k = max_key(u.z, r); m2 = k > m2 ? k : m2;
+        k = max_key(u.w, r); m3 = k > m3 ? k : m3;
+      }
+    }
+    double* sx = a.stats + 2 + 4 * f4;
+    double* sy = a.stats + 2 + a.Dp + 4 * f4;
+    atomicAdd(sx + 0, static_cast<double>(cx.x)); atomicAdd(sx + 1, static_cast<double>(cx.y));
+    atomicAdd(sx + 2, static_cast<double>(cx.z)); atomicAdd(sx + 3, static_cast<double>(cx.w));
+    atomicAdd(sy + 0, static_cast<double>(cy.x)); atomicAdd(sy + 1, static_cast<double>(cy.y));
+    atomicAdd(sy + 2, static_cast<double>(cy.z)); atomicAdd(sy + 3, static_cast<double>(cy.w));
+    if (a.cmax) {
+      atomicMax(a.cmax + 4 * f4 + 0, m0); atomicMax(a.cmax + 4 * f4 + 1, m1);
+      atomicMax(a.cmax + 4 * f4 + 2, m2); atomicMax(a.cmax + 4 * f4 + 3, m3);
+    }
+  }
+  __shared__ float red[8];
+  const float tx = block_sum_256(sqx, red);
+  const float ty = block_sum_256(sqy, red);
+  if (threadIdx.x == 0) {
+    atomicAdd(&a.stats[0], static_cast<double>(tx));
+    atomicAdd(&a.stats[1], static_cast<double>(ty));
+  }
+}
+
+// ------------------------------------------------------------------ scales
+struct ScaleArgs {
+  float mults[VGAN_B200_MAX_SCALES];
+  int n_scales, frozen, center, common_mode;
+  int64_t Nx, Ny, D, Dp, Nxp, Nyp, D_u;
+  float weight;
+  const double* stats;
+  const unsigned long long* cmax;
+  float* bandwidth;
+  float* par;
+  float* mean;
+  float* cm;
+  float* misc;
+};
+
+__device__ __forceinline__ double block_sum_256d(double v, double* red) {
+  red[threadIdx.x] = v;
+  __syncthreads();
+  for (int s = 128; s > 0; s >>= 1) {
+    if (threadIdx.x < s) red[threadIdx.x] += red[threadIdx.x + s];
+    __syncthreads();
+  }
+  const double t = red[0];
+  __syncthreads();
+  return t;   // valid in every thread
+}
+
+// bandwidth = sum_ij |zi-zj|^2 / (n^2-n) = (2n sum|z|^2 - 2 |sum z|^2) / (n^2-n)   (Mmd_loss_constrained.py:16-22)
+__global__ void __launch_bounds__(256) scales_kernel(ScaleArgs a) {
+  __shared__ double red[256];
+  __shared__ float sh[16];
+  const double* csx = a.stats + 2;
+  const double* csy = a.stats + 2 + a.Dp;
+  double axx = 0.0, ayy = 0.0, axy = 0.0;
+  for (int64_t f = threadIdx.x; f < a.D; f += 256) {
+    const double x = csx[f], y = csy[f];
+    axx += x * x; ayy += y * y; axy += x * y;
+  }
+  axx = block_sum_256d(axx, red);
+  ayy = block_sum_256d(ayy, red);
+  axy = block_sum_256d(axy, red);
+  const double nx = static_cast<double>(a.Nx), ny = static_cast<double>(a.Ny), n = nx + ny;
+  const double sqx = a.stats[0], sqy = a.stats[1];
+  if (threadIdx.x == 0) {
+    float bw;
+    if (!a.frozen) {
+      bw = static_cast<float>((2.0 * n * (sqx + sqy) - 2.0 * (axx + 2.0 * axy + ayy)) / (n * n - n));
+      *a.bandwidth = bw;
+    } else {
+      bw = *a.bandwidth;
+    }
+    // the reference multiplies the 0-dim bandwidth with the fp32 multiplier vector -> fp32
+    float inv_s[VGAN_B200_MAX_SCALES];
+    for (int m = 0; m < VGAN_B200_MAX_SCALES; ++m) inv_s[m] = m < a.n_scales ? 1.0f / (bw * a.mults[m]) : 0.f;
+    const int ref = a.n_scales - 1;
+    const float c0 = kLog2e * inv_s[ref];
+    float* par = a.par;
+    for (int t = 0; t < kParFloats; ++t) par[t] = 0.f;
+    par[0] = c0;
+    par[1] = -2.f * c0;
+    const float cx = 1.f / static_cast<float>(a.Nx), cy = -1.f / static_cast<float>(a.Ny);
+    for (int m = 0; m < a.n_scales; ++m) {
+      par[2 + m] = inv_s[m] / inv_s[ref];
+      par[kParCoefX + m] = inv_s[m] * cx;
+      par[kParCoefY + m] = inv_s[m] * cy;
+      par[kParInvS + m] = inv_s[m];
+    }
+    par[kParBw] = bw;
+    // common mode: w0_ab = w(mean squared distance between block a and block b)
+    float w0[2][2] = {{0.f, 0.f}, {0.f, 0.f}};
+    if (a.common_mode) {
+      const double mx = sqx / nx, my = sqy / ny;
+      const double dxy = mx + my - 2.0 * axy / (nx * ny);
+      const double d2[2][2] = {{2.0 * (mx - axx / (nx * nx)), dxy}, {dxy, 2.0 * (my - ayy / (ny * ny))}};
+      for (int r = 0; r < 2; ++r)
+        for (int c = 0; c < 2; ++c) {
+          double w = 0.0;
+          for (int m = 0; m < a.n_scales; ++m) w += exp(-fmax(d2[r][c], 0.0) * inv_s[m]) * inv_s[m];
+          w0[r][c] = static_cast<float>(w);
+        }
+    }
+    const float npx = static_cast<float>(a.Nxp - a.Nx), npy = static_cast<float>(a.Nyp - a.Ny);
+    for (int r = 0; r < 2; ++r) {
+      par[kParCw0 + 2 * r + 0] = cx * w0[r][0];
+      par[kParCw0 + 2 * r + 1] = cy * w0[r][1];
+      par[kParB + r] = (w0[r][0] - w0[r][1]) + cx * w0[r][0] * npx + cy * w0[r][1] * npy;
+    }
+    sh[0] = w0[0][0]; sh[1] = w0[0][1]; sh[2] = w0[1][0]; sh[3] = w0[1][1];
+  }
+  __syncthreads();
+  // centring mean and the common-mode gradient vectors A_a[f] = w0_ax mu_x[f] - w0_ay mu_y[f] (means of the STORED rows)
+  for (int64_t f = threadIdx.x; f < a.Dp; f += 256) {
+    float mean = 0.f, ax = 0.f, ay = 0.f;
+    if (f < a.D) {
+      const double x = csx[f], y = csy[f];
+      const double mu = a.center ? (x + y) / n : 0.0;
+      const double mux = x / nx - mu, muy = y / ny - mu;
+      mean = static_cast<float>(mu);
+      ax = static_cast<float>(sh[0] * mux - sh[1] * muy);
+      ay = static_cast<float>(sh[2] * mux - sh[3] * muy);
+    }
+    a.mean[f] = mean;
+    a.cm[f] = ax;
+    a.cm[a.Dp + f] = ay;
+  }
+  // penalty value  weight * mean_d(1 - max_i U[i,d])   (Mmd_loss_constrained.py:50)
+  double pen = 0.0;
+  const bool has_pen = a.cmax && a.weight != 0.f;
+  if (has_pen)
+    for (int64_t d = threadIdx.x; d < a.D_u; d += 256)
+      pen += 1.0 - static_cast<double>(key_float(static_cast<uint32_t>(a.cmax[d] >> 32)));
+  pen = block_sum_256d(pen, red);
+  if (threadIdx.x == 0)
+    a.misc[kMiscPenalty / 4] = has_pen ? static_cast<float>(a.weight * pen / static_cast<double>(a.D_u)) : 0.f;
+}
+
+// ------------------------------------------------------------------ pack
+// one warp per stored (padded) row of the range's stack: stored X rows [x0, x1), stored Y rows [y0, y1)
+// (indices inside their padded regions)
+__global__ void __launch_bounds__(256) pack_kernel(PackArgs a, int64_t x0, int64_t x1, int64_t y0, int64_t y1) {
   const int lane = threadIdx.x & 31;
-  const int64_t r = static_cast<int64_t>(blockIdx.x) * 8 + (threadIdx.x >> 5);
-  if (r >= a.Nxp + a.Nyp) return;
-  const bool in_x = r < a.Nxp;
-  const int64_t local = in_x ? r : r - a.Nxp;
+  const int64_t q = static_cast<int64_t>(blockIdx.x) * 8 + (threadIdx.x >> 5);
+  const int64_t nX = x1 - x0;
+  if (q >= nX + (y1 - y0)) return;
+  const bool in_x = q < nX;
+  const int64_t local = in_x ? x0 + q : y0 + (q - nX);
+  const int64_t r = in_x ? local : a.Nxp + local;            // stored row
   const bool valid = local < (in_x ? a.Nx : a.Ny);
-  const int64_t zrow = in_x ? local : a.Nx + local;
+  const float c0 = a.par[0];
   float nrm = 0.f;
   for (int64_t f = lane; f < a.Dp; f += 32) {
     float z = 0.f;
-    if (valid && f < a.D) z = load_stacked(a, zrow, f) - a.mean[f];
+    if (valid && f < a.D) {
+      const float raw = in_x ? a.X[local * a.D + f]
+                             : (a.Y ? a.Y[local * a.D + f] : a.U[local * a.D + f] * a.X[local * a.D + f]);
+      z = raw - a.mean[f];
+    }
     if (a.fp32) {
       a.zf[r * a.Dp + f] = z;
       nrm = fmaf(z, z, nrm);
@@ -89,48 +299,17 @@ __global__ void __launch_bounds__(256) pack_kernel(PackArgs a) {
       a.zb[o] = hi; a.zb[o + a.Dp] = lo; a.zb[o + 2 * a.Dp] = hi;
       nrm = fmaf(zr, zr, nrm);
     } else {
-      const __nv_bfloat16 q = __float2bfloat16_rn(z);
-      a.zq[r * a.Dp + f] = q;
-      const float zr = __bfloat162float(q);
+      const __nv_bfloat16 qv = __float2bfloat16_rn(z);
+      a.zq[r * a.Dp + f] = qv;
+      const float zr = __bfloat162float(qv);
       nrm = fmaf(zr, zr, nrm);     // norm of the value the tensor core will see
     }
   }
   nrm = warp_sum(nrm);
-  if (lane == 0) a.nrm[r] = valid ? nrm : kPadNorm;
-}
-
-// ---- masked fast path (Y = U*X, Nx == Ny, D % 4 == 0, 16-byte aligned inputs): X and U are read ONCE per pass
-// for both halves of the stack (the generic kernels read X twice), with 16-byte loads.
-__global__ void __launch_bounds__(256) colstats_masked_kernel(PackArgs a, int rows_per_block) {
-  const int64_t r0 = static_cast<int64_t>(blockIdx.x) * rows_per_block;
-  const int64_t r1 = min(r0 + rows_per_block, a.Nx);
-  const int64_t D4 = a.D >> 2;
-  float sq = 0.f;
-  for (int64_t f4 = threadIdx.x; f4 < D4; f4 += blockDim.x) {
-    float4 cs = make_float4(0.f, 0.f, 0.f, 0.f);
-    const float4* xp = reinterpret_cast<const float4*>(a.X) + r0 * D4 + f4;
-    const float4* up = reinterpret_cast<const float4*>(a.U) + r0 * D4 + f4;
-#pragma unroll 4
-    for (int64_t r = r0; r < r1; ++r, xp += D4, up += D4) {
-      const float4 x = __ldg(xp), u = __ldg(up);
-      const float4 y = make_float4(u.x * x.x, u.y * x.y, u.z * x.z, u.w * x.w);
-      cs.x += x.x + y.x; cs.y += x.y + y.y; cs.z += x.z + y.z; cs.w += x.w + y.w;
-      sq = fmaf(x.x, x.x, fmaf(x.y, x.y, fmaf(x.z, x.z, fmaf(x.w, x.w, sq))));
-      sq = fmaf(y.x, y.x, fmaf(y.y, y.y, fmaf(y.z, y.z, fmaf(y.w, y.w, sq))));
-    }
-    atomicAdd(&a.stats[2 + 4 * f4 + 0], static_cast<double>(cs.x));
-    atomicAdd(&a.stats[2 + 4 * f4 + 1], static_cast<double>(cs.y));
-    atomicAdd(&a.stats[2 + 4 * f4 + 2], static_cast<double>(cs.z));
-    atomicAdd(&a.stats[2 + 4 * f4 + 3], static_cast<double>(cs.w));
-  }
-  sq = warp_sum(sq);
-  __shared__ float red[8];
-  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = sq;
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    double t = 0.0;
-    for (int w = 0; w < 8; ++w) t += red[w];
-    atomicAdd(&a.stats[0], t);
+  if (lane == 0) {
+    nrm = valid ? nrm : kPadNorm;
+    a.nrm[r] = nrm;
+    a.nrms[r] = c0 * nrm;
   }
 }
 
@@ -145,13 +324,14 @@ __device__ __forceinline__ uint2 pack4_bf16(float a, float b, float c, float d, 
   return o;
 }
 
-// one warp per sample row r: writes stored rows r (X half) and Nxp + r (Y half), bf16 path
-__global__ void __launch_bounds__(256) pack_masked_kernel(PackArgs a) {
+// masked fast path: one warp per sample row r in [r0, r1): writes stored rows r (X half) and Nxp + r (Y half), bf16
+__global__ void __launch_bounds__(256) pack_masked_kernel(PackArgs a, int64_t r0, int64_t r1) {
   const int lane = threadIdx.x & 31;
-  const int64_t r = static_cast<int64_t>(blockIdx.x) * 8 + (threadIdx.x >> 5);
-  if (r >= a.Nxp) return;
+  const int64_t r = r0 + static_cast<int64_t>(blockIdx.x) * 8 + (threadIdx.x >> 5);
+  if (r >= r1) return;
   const bool valid = r < a.Nx;
   const int64_t D4 = a.D >> 2, Dp4 = a.Dp >> 2;
+  const float c0 = a.par[0];
   float nx = 0.f, ny = 0.f;
   uint2* zx = reinterpret_cast<uint2*>(a.zq + r * a.Dp);
   uint2* zy = reinterpret_cast<uint2*>(a.zq + (a.Nxp + r) * a.Dp);
@@ -170,131 +350,135 @@ __global__ void __launch_bounds__(256) pack_masked_kernel(PackArgs a) {
   nx = warp_sum(nx);
   ny = warp_sum(ny);
   if (lane == 0) {
-    a.nrm[r] = valid ? nx : kPadNorm;
-    a.nrm[a.Nxp + r] = valid ? ny : kPadNorm;
+    nx = valid ? nx : kPadNorm;
+    ny = valid ? ny : kPadNorm;
+    a.nrm[r] = nx;
+    a.nrm[a.Nxp + r] = ny;
+    a.nrms[r] = c0 * nx;
+    a.nrms[a.Nxp + r] = c0 * ny;
   }
 }
 
-struct ScaleArgs {
-  float mults[VGAN_B200_MAX_SCALES];
-  int n_scales, frozen;
-  int64_t n, D;
-  const double* stats;
-  float* bandwidth;
-  float* inv_scales;
-};
-
-// bandwidth = sum_ij |zi-zj|^2 / (n^2-n) = (2n sum|z|^2 - 2 |sum z|^2) / (n^2-n)
-__global__ void __launch_bounds__(256) scales_kernel(ScaleArgs a) {
-  __shared__ double red[256];
-  double acc = 0.0;
-  if (!a.frozen) {
-    for (int64_t f = threadIdx.x; f < a.D; f += 256) acc += a.stats[2 + f] * a.stats[2 + f];
+// ------------------------------------------------------------------ finalize
+// loss = S_xx/Nx^2 - 2 S_xy/(Nx Ny) + S_yy/Ny^2 + penalty; penalty gradient -weight/D_u at (argmax row, d)
+__global__ void __launch_bounds__(256)
+finalize_kernel(const double* __restrict__ sums, double nx, double ny, const unsigned long long* __restrict__ cmax,
+                int64_t D_u, float weight, float* __restrict__ dU, int64_t row_begin, int64_t rows,
+                double* __restrict__ colsum, float* __restrict__ misc, float* __restrict__ loss) {
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    const double mmd2 = sums[0] / (nx * nx) - 2.0 * sums[1] / (nx * ny) + sums[2] / (ny * ny);
+    const float l = static_cast<float>(mmd2 + static_cast<double>(misc[kMiscPenalty / 4]));
+    misc[kMiscLoss / 4] = l;
+    if (loss) loss[0] = l;
   }
-  red[threadIdx.x] = acc;
-  __syncthreads();
-  for (int s = 128; s > 0; s >>= 1) {
-    if (threadIdx.x < s) red[threadIdx.x] += red[threadIdx.x + s];
-    __syncthreads();
+  if (!cmax || weight == 0.f) return;
+  const float g = -weight / static_cast<float>(D_u);
+  for (int64_t d = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; d < D_u;
+       d += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const int64_t row = 0xffffffffu - static_cast<uint32_t>(cmax[d] & 0xffffffffu);
+    if (dU && row >= row_begin && row < row_begin + rows) atomicAdd(&dU[(row - row_begin) * D_u + d], g);
+    if (colsum) colsum[d] += static_cast<double>(g);
   }
-  if (threadIdx.x == 0) {
-    float bw;
-    if (!a.frozen) {
-      const double n = static_cast<double>(a.n);
-      bw = static_cast<float>((2.0 * n * a.stats[0] - 2.0 * red[0]) / (n * n - n));
-      *a.bandwidth = bw;
-    } else {
-      bw = *a.bandwidth;
-    }
-    // the reference multiplies the 0-dim bandwidth with the fp32 multiplier vector -> fp32
-    for (int m = 0; m < a.n_scales; ++m) a.inv_scales[m] = 1.0f / (bw * a.mults[m]);
-  }
-}
-
-struct SetupArgs {
-  const float* inv_scales;
-  int n_scales;
-  int64_t Nx, Ny, rows;
-  const float* nrm;
-  float* nrms;
-  float* par;
-};
-
-// parameter block + norms scaled for the exp2 argument (see common.cuh)
-__global__ void __launch_bounds__(256) setup_kernel(SetupArgs a) {
-  const int ref = a.n_scales - 1;
-  const float c0 = kLog2e * a.inv_scales[ref];
-  if (blockIdx.x == 0 && threadIdx.x < kParFloats) {
-    const int t = threadIdx.x;
-    float v = 0.f;
-    if (t == 0) v = c0;
-    else if (t == 1) v = -2.f * c0;
-    else if (t >= 2 && t < 10) v = (t - 2 < a.n_scales) ? a.inv_scales[t - 2] / a.inv_scales[ref] : 0.f;
-    else if (t >= 10 && t < 18) v = (t - 10 < a.n_scales) ? a.inv_scales[t - 10] / static_cast<float>(a.Nx) : 0.f;
-    else if (t >= 18 && t < 26) v = (t - 18 < a.n_scales) ? -a.inv_scales[t - 18] / static_cast<float>(a.Ny) : 0.f;
-    a.par[t] = v;
-  }
-  const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (i < a.rows) a.nrms[i] = c0 * a.nrm[i];
 }
 
 // ------------------------------------------------------------------ host launchers
-int run_prologue(const float* X, const float* U, const float* Y, const vgan_b200_layout_t& L,
-                 int flags, void* ws, cudaStream_t st) {
+static PackArgs make_pack_args(const vgan_b200_layout_t& L, void* ws, const float* X, const float* U, const float* Y,
+                               int64_t rb, int64_t re) {
   uint8_t* base = static_cast<uint8_t*>(ws);
   PackArgs a;
   a.X = X; a.U = U; a.Y = Y;
-  a.Nx = L.Nx; a.Ny = L.Ny; a.D = L.D; a.Dp = L.Dp; a.Nxp = L.Nxp; a.Nyp = L.Nyp;
-  a.center = (flags & VGAN_B200_CENTER) ? 1 : 0;
-  a.fp32 = (flags & VGAN_B200_PREC_MASK) == VGAN_B200_PREC_FP32;
-  a.split = (!a.fp32 && (flags & VGAN_B200_BF16X3)) ? 1 : 0;
+  a.Nx = L.Nx; a.Ny = L.Ny; a.D = L.D; a.Dp = L.Dp; a.Nxp = L.Nxp; a.Nyp = L.Nyp; a.D_u = L.D_u;
+  a.rb = rb; a.re = re;
+  a.center = (L.flags & VGAN_B200_CENTER) ? 1 : 0;
+  a.fp32 = (L.flags & VGAN_B200_PREC_MASK) == VGAN_B200_PREC_FP32;
+  a.split = (!a.fp32 && (L.flags & VGAN_B200_BF16X3)) ? 1 : 0;
   a.zq = reinterpret_cast<__nv_bfloat16*>(base + L.off_zq);
   a.zb = a.zq + static_cast<size_t>(L.Nxp + L.Nyp) * 3 * L.Dp;
   a.zf = reinterpret_cast<float*>(base + L.off_zf);
   a.nrm = reinterpret_cast<float*>(base + L.off_nrm);
-  a.mean = reinterpret_cast<float*>(base + L.off_mean);
+  a.nrms = reinterpret_cast<float*>(base + L.off_nrms);
+  a.mean = reinterpret_cast<const float*>(base + L.off_mean);
+  a.par = reinterpret_cast<const float*>(base + L.off_par);
   a.stats = reinterpret_cast<double*>(base + L.off_stats);
-  VG_CUDA_CHECK(cudaMemsetAsync(a.stats, 0, sizeof(double) * (2 + L.Dp), st));
-  const int64_t n = L.Nx + L.Ny;
-  const int rpb = 64;
-  const bool masked_fast = !Y && U && !a.fp32 && !a.split && L.Nx == L.Ny && (L.D & 3) == 0 &&
-                           ((reinterpret_cast<uintptr_t>(X) | reinterpret_cast<uintptr_t>(U)) & 15) == 0;
-  if (masked_fast) {
-    const int rpb2 = 32;
-    colstats_masked_kernel<<<static_cast<unsigned>((L.Nx + rpb2 - 1) / rpb2), 256, 0, st>>>(a, rpb2);
-    mean_kernel<<<static_cast<unsigned>((L.Dp + 255) / 256), 256, 0, st>>>(a);
-    pack_masked_kernel<<<static_cast<unsigned>((L.Nxp + 7) / 8), 256, 0, st>>>(a);
+  a.cmax = (L.D_u > 0 && U) ? reinterpret_cast<unsigned long long*>(base + L.off_cmax) : nullptr;
+  return a;
+}
+
+static bool masked_fast(const PackArgs& a) {
+  return !a.Y && a.U && !a.fp32 && !a.split && a.Nx == a.Ny && (a.D & 3) == 0 && (a.D_u == 0 || a.D_u == a.D) &&
+         ((reinterpret_cast<uintptr_t>(a.X) | reinterpret_cast<uintptr_t>(a.U)) & 15) == 0;
+}
+
+int run_stats(const vgan_b200_layout_t& L, void* ws, const float* X, const float* U, const float* Y, int64_t rb,
+              int64_t re, cudaStream_t st) {
+  PackArgs a = make_pack_args(L, ws, X, U, Y, rb, re);
+  VG_CUDA_CHECK(cudaMemsetAsync(static_cast<uint8_t*>(ws) + L.off_acc, 0, L.acc_bytes, st));
+  int64_t nX = (re < L.Nx ? re : L.Nx) - rb, nY = (re < L.Ny ? re : L.Ny) - rb;
+  if (nX < 0) nX = 0;
+  if (nY < 0) nY = 0;
+  const int64_t rows = nX + nY;
+  if (rows <= 0) return VGAN_B200_OK;       // an empty shard only takes part in the exchanges
+  if (masked_fast(a)) {
+    const int rpb = nX >= 32768 ? 64 : 32;
+    colstats_masked_kernel<<<static_cast<unsigned>((nX + rpb - 1) / rpb), 256, 0, st>>>(a, rpb);
   } else {
-    colstats_kernel<<<static_cast<unsigned>((n + rpb - 1) / rpb), 256, 0, st>>>(a, rpb);
-    mean_kernel<<<static_cast<unsigned>((L.Dp + 255) / 256), 256, 0, st>>>(a);
-    pack_kernel<<<static_cast<unsigned>((L.Nxp + L.Nyp + 7) / 8), 256, 0, st>>>(a);
+    const int rpb = 64;
+    colstats_kernel<<<static_cast<unsigned>((rows + rpb - 1) / rpb), 256, 0, st>>>(a, rpb);
+    if (a.cmax && nX > 0)
+      colmax_kernel<<<static_cast<unsigned>((nX + rpb - 1) / rpb), 256, 0, st>>>(U, rb, rb + nX, L.D_u, rpb, a.cmax);
   }
   VG_CUDA_CHECK(cudaGetLastError());
   return VGAN_B200_OK;
 }
 
-int run_scales(const vgan_b200_layout_t& L, void* ws, float* bandwidth, int frozen,
-               const float* mults_host, int n_scales, float* inv_scales, cudaStream_t st) {
+int run_scales(const vgan_b200_layout_t& L, void* ws, float* bandwidth, int frozen, const float* mults_host,
+               float weight, cudaStream_t st) {
+  uint8_t* base = static_cast<uint8_t*>(ws);
   ScaleArgs a;
-  for (int m = 0; m < VGAN_B200_MAX_SCALES; ++m) a.mults[m] = m < n_scales ? mults_host[m] : 1.f;
-  a.n_scales = n_scales; a.frozen = frozen; a.n = L.Nx + L.Ny; a.D = L.D;
-  a.stats = reinterpret_cast<const double*>(static_cast<uint8_t*>(ws) + L.off_stats);
-  a.bandwidth = bandwidth; a.inv_scales = inv_scales;
+  for (int m = 0; m < VGAN_B200_MAX_SCALES; ++m) a.mults[m] = m < L.n_scales ? mults_host[m] : 1.f;
+  a.n_scales = L.n_scales; a.frozen = frozen;
+  a.center = (L.flags & VGAN_B200_CENTER) ? 1 : 0;
+  a.common_mode = (L.flags & VGAN_B200_PREC_MASK) == VGAN_B200_PREC_BF16;   // the tcgen05 kernels (bf16, bf16x3)
+  a.Nx = L.Nx; a.Ny = L.Ny; a.D = L.D; a.Dp = L.Dp; a.Nxp = L.Nxp; a.Nyp = L.Nyp; a.D_u = L.D_u;
+  a.weight = weight;
+  a.stats = reinterpret_cast<const double*>(base + L.off_stats);
+  a.cmax = L.D_u > 0 ? reinterpret_cast<const unsigned long long*>(base + L.off_cmax) : nullptr;
+  a.bandwidth = bandwidth;
+  a.par = reinterpret_cast<float*>(base + L.off_par);
+  a.mean = reinterpret_cast<float*>(base + L.off_mean);
+  a.cm = reinterpret_cast<float*>(base + L.off_cm);
+  a.misc = reinterpret_cast<float*>(base + L.off_misc);
   scales_kernel<<<1, 256, 0, st>>>(a);
   VG_CUDA_CHECK(cudaGetLastError());
   return VGAN_B200_OK;
 }
 
-int run_setup(const vgan_b200_layout_t& L, void* ws, const float* inv_scales, int n_scales,
-              float* par, cudaStream_t st) {
+int run_pack(const vgan_b200_layout_t& L, void* ws, const float* X, const float* U, const float* Y, int64_t rb,
+             int64_t re, cudaStream_t st) {
+  PackArgs a = make_pack_args(L, ws, X, U, Y, rb, re);
+  // stored rows of each block in range; the call that reaches the end of a block also writes its zero padding
+  const int64_t x0 = rb < L.Nxp ? rb : L.Nxp, x1 = re >= L.Nx ? L.Nxp : (re > x0 ? re : x0);
+  const int64_t y0 = rb < L.Nyp ? rb : L.Nyp, y1 = re >= L.Ny ? L.Nyp : (re > y0 ? re : y0);
+  if (masked_fast(a)) {
+    if (x1 > x0) pack_masked_kernel<<<static_cast<unsigned>((x1 - x0 + 7) / 8), 256, 0, st>>>(a, x0, x1);
+  } else {
+    const int64_t rows = (x1 - x0) + (y1 - y0);
+    if (rows > 0) pack_kernel<<<static_cast<unsigned>((rows + 7) / 8), 256, 0, st>>>(a, x0, x1, y0, y1);
+  }
+  VG_CUDA_CHECK(cudaGetLastError());
+  return VGAN_B200_OK;
+}
+
+int run_finalize(const vgan_b200_layout_t& L, void* ws, float weight, float* dU, int64_t row_begin, int64_t rows,
+                 int colsum_penalty, float* loss, cudaStream_t st) {
   uint8_t* base = static_cast<uint8_t*>(ws);
-  SetupArgs a;
-  a.inv_scales = inv_scales; a.n_scales = n_scales; a.Nx = L.Nx; a.Ny = L.Ny;
-  a.rows = L.Nxp + L.Nyp;
-  a.nrm = reinterpret_cast<const float*>(base + L.off_nrm);
-  a.nrms = reinterpret_cast<float*>(base + L.off_nrms);
-  a.par = par;
-  setup_kernel<<<static_cast<unsigned>((a.rows + 255) / 256), 256, 0, st>>>(a);
+  const bool pen = L.D_u > 0 && weight != 0.f;
+  const unsigned blocks = pen ? static_cast<unsigned>((L.D_u + 255) / 256 < 64 ? (L.D_u + 255) / 256 : 64) : 1u;
+  finalize_kernel<<<blocks, 256, 0, st>>>(
+      reinterpret_cast<const double*>(base + L.off_sums), static_cast<double>(L.Nx), static_cast<double>(L.Ny),
+      pen ? reinterpret_cast<const unsigned long long*>(base + L.off_cmax) : nullptr, L.D_u, weight, dU, row_begin, rows,
+      (pen && colsum_penalty) ? reinterpret_cast<double*>(base + L.off_colsum) : nullptr,
+      reinterpret_cast<float*>(base + L.off_misc), loss);
   VG_CUDA_CHECK(cudaGetLastError());
   return VGAN_B200_OK;
 }
