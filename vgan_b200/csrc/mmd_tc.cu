@@ -262,9 +262,12 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__
 #pragma unroll
     for (int m = 0; m < VGAN_B200_MAX_SCALES; ++m) {
       ratio[m] = p.par[2 + m];
-      coef_x[m] = p.par[10 + m];
-      coef_y[m] = p.par[18 + m];
+      coef_x[m] = p.par[kParCoefX + m];
+      coef_y[m] = p.par[kParCoefY + m];
     }
+    // common-mode level c_j w0 of (this row block, X columns) / (this row block, Y columns); unused without PV
+    const float cw0_x = u.pv ? p.par[kParCw0 + (u.row_is_x ? 0 : 2)] : 0.f;
+    const float cw0_y = u.pv ? p.par[kParCw0 + (u.row_is_x ? 0 : 2) + 1] : 0.f;
     (void)c0;
     float acc_x = 0.f, acc_y = 0.f;   // sum of k over X / Y columns (weighted by symmetry)
     float rsum = 0.f;                 // sum_j P_ij over this thread's column half
@@ -285,7 +288,7 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__
       float ksum = 0.f;
       uint4 pk[4];
       epi_half_tile<LADDER>(tmem + lane_addr + b * kTile + g * 32, njp, ni, m2c0, cf, ratio, p.n_scales, ksum, rsum, pk,
-                            p.p_lo != 0);
+                            p.p_lo != 0, col_is_x ? cw0_x : cw0_y);
       if (u.pv) {
         mbar_wait(&bar->p_empty[b], ((n >> 1) & 1) ^ 1);   // PV(n-2) done with P[b]
 #pragma unroll
@@ -299,7 +302,9 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__
         mbar_arrive(&bar->p_full[b]);
       }
       if (col_is_x) acc_x = fmaf(ksum, fac, acc_x); else acc_y += ksum;
+#ifdef VGAN_B200_DEBUG
       if (p.dbg) atomicAdd(&p.dbg[static_cast<int64_t>(blockIdx.x) * p.dbg_stride + n], ksum);
+#endif
     }
 
     // ---- block sums (only slice 0 owns them)
@@ -333,7 +338,7 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__
       asm volatile("bar.sync 1, %0;" ::"n"(kNumEpiThreads) : "memory");
       const float rtot = rs_smem[row] + rs_smem[kTile + row] + rs_smem[2 * kTile + row] + rs_smem[3 * kTile + row];
       if (g < 2)                                        // two column halves of the slice, as in the other kernels
-        write_grad_rows(p, tmem_o, lane_addr, g, row, u.ti, u.row_is_x, u.slice, slice_chunks, rtot);
+        write_grad_rows(p, tmem_o, lane_addr, g, row, u.ti, u.row_is_x, u.slice, slice_chunks, rtot, false, true);
     }
   }
 

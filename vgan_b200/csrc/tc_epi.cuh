@@ -10,10 +10,14 @@ template <bool LADDER>
 __device__ __forceinline__ void epi_compute_32(const uint32_t (&v)[32], const float* __restrict__ njp, float ni,
                                                     float m2c0, const float (&cf)[VGAN_B200_MAX_SCALES],
                                                     const float (&ratio)[VGAN_B200_MAX_SCALES], int n_scales,
-                                                    float& ksum, float& rsum, uint4 (&pk)[4], bool plo = false) {
+                                                    float& ksum, float& rsum, uint4 (&pk)[4], bool plo = false,
+                                                    float cw0 = 0.f) {
+  // cw0 = c_j w0: the common-mode level of this (row block, column block) pair.  P' = c_j (w - w0) is what gets rounded
+  // to bf16 and multiplied; the closed-form remainder is added back in write_grad_rows.  It rides in the last FMA of
+  // the weight sum, so it costs no instruction.
   if constexpr (LADDER) {
     // two columns per issue slot (packed f32x2): ~11.5 instead of ~19.5 instructions per pair
-    const uint64_t m2 = f2_pack(m2c0, m2c0), ni2 = f2_pack(ni, ni);
+    const uint64_t m2 = f2_pack(m2c0, m2c0), ni2 = f2_pack(ni, ni), mcw = f2_pack(-cw0, -cw0);
     const uint64_t c0 = f2_pack(cf[0], cf[0]), c1 = f2_pack(cf[1], cf[1]), c2 = f2_pack(cf[2], cf[2]),
                    c3 = f2_pack(cf[3], cf[3]), c4 = f2_pack(cf[4], cf[4]);
     uint64_t ks2 = f2_pack(0.f, 0.f), rs2 = f2_pack(0.f, 0.f);
@@ -35,7 +39,7 @@ __device__ __forceinline__ void epi_compute_32(const uint32_t (&v)[32], const fl
         const uint64_t t2 = f2_mul(t1, t1), t4 = f2_mul(t2, t2), t8 = f2_mul(t4, t4), t16 = f2_mul(t8, t8);
         ks2 = f2_add(ks2, f2_add(f2_add(t1, t2), f2_add(f2_add(t4, t8), t16)));
         // scale index 4 is the widest kernel (t1), index 0 the narrowest (t16)
-        const uint64_t w2 = f2_fma(t16, c0, f2_fma(t8, c1, f2_fma(t4, c2, f2_fma(t2, c3, f2_mul(t1, c4)))));
+        const uint64_t w2 = f2_fma(t16, c0, f2_fma(t8, c1, f2_fma(t4, c2, f2_fma(t2, c3, f2_fma(t1, c4, mcw)))));
         rs2 = f2_add(rs2, w2);
         float w0, w1;
         f2_unpack(w2, w0, w1);
@@ -61,7 +65,7 @@ __device__ __forceinline__ void epi_compute_32(const uint32_t (&v)[32], const fl
     for (int e = 0; e < 8; ++e) {
       float uarg = fmaf(__uint_as_float(v[c * 8 + e]), m2c0, ni + njv[e]);
       uarg = fmaxf(uarg, 0.f);
-      float kk = 0.f, ww = 0.f;
+      float kk = 0.f, ww = -cw0;
       for (int m = 0; m < n_scales; ++m) {
         const float em = ex2_approx(-uarg * ratio[m]);
         kk += em;
@@ -91,36 +95,40 @@ template <bool LADDER>
 __device__ __forceinline__ void epi_half_tile(uint32_t taddr, const float* __restrict__ njp, float ni,
                                               float m2c0, const float (&cf)[VGAN_B200_MAX_SCALES],
                                               const float (&ratio)[VGAN_B200_MAX_SCALES], int n_scales,
-                                              float& ksum, float& rsum, uint4 (&pk)[4], bool plo = false) {
+                                              float& ksum, float& rsum, uint4 (&pk)[4], bool plo = false,
+                                              float cw0 = 0.f) {
   uint32_t v[32];
   tmem_ld_32x32(taddr, v);
   tmem_ld_wait();
-  epi_compute_32<LADDER>(v, njp, ni, m2c0, cf, ratio, n_scales, ksum, rsum, pk, plo);
+  epi_compute_32<LADDER>(v, njp, ni, m2c0, cf, ratio, n_scales, ksum, rsum, pk, plo, cw0);
 }
 
-// 64 columns: both TMEM loads are issued before the single wait, so their latencies overlap
-template <bool LADDER>
-__device__ __forceinline__ void epi_tile_64(uint32_t taddr, const float* __restrict__ njp, float ni, float m2c0,
-                                            const float (&cf)[VGAN_B200_MAX_SCALES],
-                                            const float (&ratio)[VGAN_B200_MAX_SCALES], int n_scales,
-                                            float& ksum, float& rsum, uint4 (&pk)[8], bool plo = false) {
-  uint32_t va[32], vb[32];
-  tmem_ld_32x32(taddr, va);
-  tmem_ld_32x32(taddr + 32, vb);
-  tmem_ld_wait();
-  uint4 h0[4], h1[4];
-  epi_compute_32<LADDER>(va, njp, ni, m2c0, cf, ratio, n_scales, ksum, rsum, h0, plo);
-  epi_compute_32<LADDER>(vb, njp + 32, ni, m2c0, cf, ratio, n_scales, ksum, rsum, h1, plo);
+// Column sums over the 32 lanes of a warp of 32 per-lane values: lane l returns sum over lanes of v[l].
+// Butterfly: each step halves the values a lane holds (16 + 8 + 4 + 2 + 1 = 31 shuffles).
+__device__ __forceinline__ float warp_transpose_sum(float (&v)[32], int lane) {
 #pragma unroll
-  for (int i = 0; i < 4; ++i) { pk[i] = h0[i]; pk[4 + i] = h1[i]; }
+  for (int s = 16; s >= 1; s >>= 1) {
+    const bool up = (lane & s) != 0;
+#pragma unroll
+    for (int i = 0; i < s; ++i) {
+      const float send = up ? v[i] : v[i + s];
+      const float keep = up ? v[i + s] : v[i];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, s);
+    }
+  }
+  return v[0];
 }
 
-// dZ rows of one unit: out[row, f] = 4 c_i (O[row, f] - rtot z[row, f]) (x mul), f in the slice.
-// The expression is linear in (O, rtot): a unit cut into column ranges adds the ranges' results (accumulate).
-// Thread = (row, column half g); O columns of the slice live at tmem_o.
+// dZ rows of one unit: out[row, f] = 4 c_i (O'[row, f] + A[f] - (rtot' + B) z[row, f]) (x mul), f in the slice, where
+// O' and rtot' come from P' = c_j (w_ij - w0) and A, B (scales_kernel) are the closed-form common-mode remainder
+// sum_j c_j w0 (z_j - z_i).  The expression is linear in (O', rtot'): a unit cut into column ranges adds the ranges'
+// results (accumulate), and only the range that starts at column round 0 (`first_range`) adds A and B.
+// Thread = (row, column half g); O columns of the slice live at tmem_o.  Column sums of the Y rows written go to
+// p.colsum (the D-vector of the step: colsum_i dL/dU[i,:] on the masked path).
 __device__ __forceinline__ void write_grad_rows(const TcParams& p, uint32_t tmem_o, uint32_t lane_addr, int g,
                                                 int row, int ti, int row_is_x, int slice, int slice_chunks,
-                                                float rtot, bool accumulate = false) {
+                                                float rtot, bool accumulate, bool first_range) {
+  const int lane = threadIdx.x & 31;
   const int slice_w = slice_chunks * kChunk;
   const int64_t region_row = static_cast<int64_t>(row_is_x ? ti : ti - p.tiles_x) * kTile + row;
   const int64_t n_region = row_is_x ? p.Nx : p.Ny;
@@ -132,15 +140,22 @@ __device__ __forceinline__ void write_grad_rows(const TcParams& p, uint32_t tmem
   const __nv_bfloat16* zrow = p.zq + zoff;
   const __nv_bfloat16* zrow_lo = p.zq_lo ? p.zq_lo + zoff : nullptr;
   if (p.pass_flags & kPassNoRowsum) rtot = 0.f;
+  const bool cmode = first_range && !(p.pass_flags & kPassNoRowsum);
+  if (cmode) rtot += p.par[kParB + (row_is_x ? 0 : 1)];
+  const float* cmv = p.cm + (row_is_x ? 0 : p.Dp);
   accumulate = accumulate || (p.pass_flags & kPassAccumulate);
   const int f_slice = slice * p.slice_chunks * kChunk;
   const bool vec_ok = !accumulate && (p.D & 3) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0 &&
                       (!mul || (reinterpret_cast<uintptr_t>(mul) & 15) == 0);
+  const bool want_colsum = p.colsum != nullptr && !row_is_x;       // warp-uniform
   for (int cc = 0; cc < slice_chunks; ++cc) {
     const int col = g * (slice_w / 2) + cc * 32;
     uint32_t v[32];
     tmem_ld_32x32(tmem_o + lane_addr + col, v);
     tmem_ld_wait();
+    float cs[32];
+#pragma unroll
+    for (int e = 0; e < 32; ++e) cs[e] = 0.f;
     if (row_ok) {
       const uint4* z4 = reinterpret_cast<const uint4*>(zrow + f_slice + col);
 #pragma unroll
@@ -150,14 +165,19 @@ __device__ __forceinline__ void write_grad_rows(const TcParams& p, uint32_t tmem
         uint4 zl = make_uint4(0u, 0u, 0u, 0u);
         if (zrow_lo) zl = reinterpret_cast<const uint4*>(zrow_lo + f_slice + col)[c];
         const uint32_t zlw[4] = {zl.x, zl.y, zl.z, zl.w};
+        const int f0 = f_slice + col + c * 8;
+        float av[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        if (cmode) {
+          const float4 a0 = *reinterpret_cast<const float4*>(cmv + f0), a1 = *reinterpret_cast<const float4*>(cmv + f0 + 4);
+          av[0] = a0.x; av[1] = a0.y; av[2] = a0.z; av[3] = a0.w; av[4] = a1.x; av[5] = a1.y; av[6] = a1.z; av[7] = a1.w;
+        }
         float gv[8];
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
           const float z = __uint_as_float((e & 1) ? (zw[e >> 1] & 0xffff0000u) : (zw[e >> 1] << 16)) +
                           __uint_as_float((e & 1) ? (zlw[e >> 1] & 0xffff0000u) : (zlw[e >> 1] << 16));
-          gv[e] = ci4 * (__uint_as_float(v[c * 8 + e]) - rtot * z);
+          gv[e] = ci4 * ((__uint_as_float(v[c * 8 + e]) + av[e]) - rtot * z);
         }
-        const int f0 = f_slice + col + c * 8;
         if (vec_ok && f0 + 8 <= p.D) {
           // 16-byte accesses (rows are 16-byte aligned when D % 4 == 0)
           if (mul) {
@@ -167,6 +187,8 @@ __device__ __forceinline__ void write_grad_rows(const TcParams& p, uint32_t tmem
           }
           *reinterpret_cast<float4*>(out + f0) = make_float4(gv[0], gv[1], gv[2], gv[3]);
           *reinterpret_cast<float4*>(out + f0 + 4) = make_float4(gv[4], gv[5], gv[6], gv[7]);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) cs[c * 8 + e] = gv[e];
         } else {
 #pragma unroll
           for (int e = 0; e < 8; ++e) {
@@ -174,12 +196,18 @@ __device__ __forceinline__ void write_grad_rows(const TcParams& p, uint32_t tmem
             if (f < p.D) {
               float gval = gv[e];
               if (mul) gval *= mul[f];
-              if (accumulate) atomicAdd(out + f, gval);   // unit shared between clusters (stream-K cut)
+              if (accumulate) atomicAdd(out + f, gval);   // unit shared between clusters (stream-K cut) / BF16X3 pass
               else out[f] = gval;
+              cs[c * 8 + e] = gval;
             }
           }
         }
       }
+    }
+    if (want_colsum) {
+      const float tot = warp_transpose_sum(cs, lane);
+      const int f = f_slice + col + lane;
+      if (f < p.D) atomicAdd(p.colsum + f, static_cast<double>(tot));
     }
   }
 }
