@@ -25,6 +25,7 @@ struct SimtParams {
   const float* nrm;         // unscaled |z|^2 (1e30 on pads)
   const float* inv_scales;
   double* sums;
+  double* colsum;           // [D] column sums of the dY rows written (after dY_mul), or nullptr
   float* dY;
   const float* dY_mul;
   float* dX;
@@ -157,6 +158,7 @@ __global__ void __launch_bounds__(256) mmd2_simt_kernel(const SimtParams p) {
     for (int o = 8; o > 0; o >>= 1) rs[i] += __shfl_xor_sync(0xffffffffu, rs[i], o);
   const float ci4 = 4.f * (row_is_x ? cx : cy);
   const int64_t n_region = row_is_x ? p.Nx : p.Ny;
+  float csum[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     const int64_t rr = static_cast<int64_t>(row_is_x ? ti : ti - p.tiles_x) * kST + ty * 4 + i;
@@ -171,7 +173,17 @@ __global__ void __launch_bounds__(256) mmd2_simt_kernel(const SimtParams p) {
         float g = ci4 * (O[i][f] - rs[i] * zrow[ff]);
         if (mul) g *= mul[ff];
         out[ff] = g;
+        csum[f] += g;
       }
+    }
+  }
+  // column sums of the Y rows written: the two ty halves of a warp first, then one atomic per (warp, column)
+  if (p.colsum && !row_is_x) {
+#pragma unroll
+    for (int f = 0; f < 4; ++f) {
+      const float t = csum[f] + __shfl_xor_sync(0xffffffffu, csum[f], 16);
+      const int64_t ff = static_cast<int64_t>(slice) * kST + tx * 4 + f;
+      if ((tid & 16) == 0 && ff < p.D) atomicAdd(p.colsum + ff, static_cast<double>(t));
     }
   }
 }
@@ -228,12 +240,11 @@ int launch_matrix(const float* Z, int64_t n, int64_t D, const float* inv_scales,
 
 namespace vg {
 int launch_simt_from_abi(const vgan_b200_layout_t& L, void* ws, int64_t row_begin, int64_t row_end, int xx_part,
-                         int xx_nparts, const float* inv_scales, int n_scales, int flags, double* sums,
-                         float* dY, const float* dY_mul, float* dX, cudaStream_t st) {
+                         int xx_nparts, float* dY, const float* dY_mul, float* dX, cudaStream_t st) {
   uint8_t* base = static_cast<uint8_t*>(ws);
   SimtParams p;
   memset(&p, 0, sizeof(p));
-  const bool need_dx = (flags & VGAN_B200_NEED_DX) != 0;
+  const bool need_dx = (L.flags & VGAN_B200_NEED_DX) != 0 && dX != nullptr;
   p.tiles_x = static_cast<int>(L.Nxp / kST);
   p.tiles_y = static_cast<int>(L.Nyp / kST);
   p.pv = dY ? 1 : 0;
@@ -248,12 +259,14 @@ int launch_simt_from_abi(const vgan_b200_layout_t& L, void* ws, int64_t row_begi
   } else {
     p.n_xx_units = xx_part < p.tiles_x ? (p.tiles_x - xx_part + xx_nparts - 1) / xx_nparts : 0;
   }
-  p.xx_part = xx_part; p.xx_nparts = xx_nparts; p.n_scales = n_scales;
+  p.xx_part = xx_part; p.xx_nparts = xx_nparts; p.n_scales = L.n_scales;
   p.Nx = L.Nx; p.Ny = L.Ny; p.D = L.D; p.Dp = L.Dp; p.row_begin = row_begin; p.row_end = row_end;
   p.zf = reinterpret_cast<const float*>(base + L.off_zf);
   p.nrm = reinterpret_cast<const float*>(base + L.off_nrm);
-  p.inv_scales = inv_scales;
-  p.sums = sums; p.dY = dY; p.dY_mul = dY_mul; p.dX = dX;
+  p.inv_scales = reinterpret_cast<const float*>(base + L.off_par) + kParInvS;
+  p.sums = reinterpret_cast<double*>(base + L.off_sums);
+  p.colsum = p.pv ? reinterpret_cast<double*>(base + L.off_colsum) : nullptr;
+  p.dY = dY; p.dY_mul = dY_mul; p.dX = dX;
   return launch_simt(p, st);
 }
 }  // namespace vg

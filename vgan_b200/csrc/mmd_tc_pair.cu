@@ -10,7 +10,7 @@
 // single thread that feeds the tensor pipe (tools/gpu_cluster_timers.py, gpu_mma_rate.py,
 // gpu_tma_rate.py): a tcgen05.mma costs ~48 issue cycles against 64 execution cycles at N=128,
 // every mbarrier wait ~100 more.  Hence TWO issuing warps with independent operand rings:
-//   warp 9  (leader)  Gram stream   G ring: kGStages x 24 KiB (A chunk 16 KiB + B half chunk 8 KiB)
+//   warp 9  (leader)  Gram stream   G ring: kG2Stages x 32 KiB (A chunk 16 KiB + B chunk 16 KiB, N = 256)
 //   warp 10 (leader)  PV stream     V ring: kVStages x 16 KiB (64 rows of Z_J x this CTA's half slice)
 // The two streams only meet through the S buffers, the P slots and TMEM; the tensor pipe interleaves
 // them in arrival order, so no static Gram/PV schedule (and no "lag") is needed.
@@ -45,9 +45,8 @@
 
 namespace vg {
 
-constexpr int kGStages = 4;                        // Gram operand ring
-constexpr int kGStageBytes = kChunkBytes + kChunkBytes / 2;   // 24 KiB
-// G256 variant (template parameter): ONE Gram issue covers the pair's next TWO column tiles (N = 256: the leader holds
+constexpr int kGStagesMax = 4;                     // barrier slots of the Gram operand ring
+// ONE Gram issue covers the pair's next TWO column tiles (N = 256: the leader holds
 // the 128 rows of tile k, the peer those of tile k + 1; D = both S buffers at once).  The row operand [Z_I0; Z_I1] is
 // then streamed once per two column tiles instead of once per tile (-21 % of all L2 -> SM bytes at D_p = 1024), a Gram
 // instruction runs 128 instead of 64 cycles, and a ring stage (A chunk 16 KiB + B chunk 16 KiB) feeds 512 instead of
@@ -61,21 +60,19 @@ constexpr int kGStageBytes = kChunkBytes + kChunkBytes / 2;   // 24 KiB
 #endif
 constexpr int kG2Stages = VG_G2_STAGES;
 constexpr int kG2StageBytes = 2 * kChunkBytes;                // 32 KiB
-constexpr int kGProducers = 2;                     // warps 8 and 11 alternate over the ring stages
 constexpr int kVStages = 2;                        // V ring: half tiles (64 rows of Z_J)
 constexpr int kVStageBytes = kChunkBytes;          // 2 boxes of [64 x 64] bf16
 constexpr int kQPBytes = 2 * kChunkBytes;
 constexpr int kQThreads = 512;   // warps: 0-7 epilogue (192 registers), 8-15 service (64 registers): 8/11 G producers,
                                  // 9 Gram MMA (peer: P forwarder), 10 PV MMA, 12 V producer, 13 P publisher, 14 norms
-static_assert(kGStages % kGProducers == 0, "each G producer warp owns fixed ring stages");
-// VG_G2_STAGES / VG_G2_SLOTS are tuning knobs of the G256 variant (same shared-memory total either way).  Measured
+// VG_G2_STAGES / VG_G2_SLOTS are compile-time tuning knobs (same shared-memory total either way).  Measured
 // (tools/gpu_cluster_timers.py, cycles per round of 4 column tiles): 3 stages + 3 P slots 10 840; 2 stages + 4 slots
 // 12 710 — the Gram warp then waits 6 600 cycles per round for operands, and the slot wait does not shrink because
 // the in-order PV stream of every pair stalls on whichever pair is late.
 constexpr int kQSlotsMax = 4;
 
 struct __align__(8) PairBarriers {
-  uint64_t g_full[kGStages], g_empty[kGStages];
+  uint64_t g_full[kGStagesMax], g_empty[kGStagesMax];
   uint64_t v_full[kVStages], v_empty[kVStages];
   uint64_t s_full[2], s_empty[2];
   uint64_t nj_full[2], nj_empty[2];
@@ -85,10 +82,10 @@ struct __align__(8) PairBarriers {
   float red[8][4];
 };
 
-template <bool G256> struct PairCfg {
-  static constexpr int GS = G256 ? kG2Stages : kGStages;            // Gram ring stages
-  static constexpr int GSB = G256 ? kG2StageBytes : kGStageBytes;   // bytes per stage
-  static constexpr int QS = G256 ? VG_G2_SLOTS : 3;                 // P slots, 32 KiB each
+struct PairCfg {
+  static constexpr int GS = kG2Stages;              // Gram ring stages
+  static constexpr int GSB = kG2StageBytes;         // bytes per stage
+  static constexpr int QS = VG_G2_SLOTS;            // P slots, 32 KiB each
   static constexpr int SmemG = 0;
   static constexpr int SmemV = SmemG + GS * GSB;
   static constexpr int SmemP = SmemV + kVStages * kVStageBytes;
@@ -108,7 +105,7 @@ template <bool G256> struct PairCfg {
     const int unit_g = static_cast<int>(w_lo / K); \
     const int r0 = static_cast<int>(w_lo - static_cast<long long>(unit_g) * K); \
     const int Kv = static_cast<int>(w_hi - w_lo);      /* rounds that count */ \
-    const int Kp = G256 ? ((Kv + 1) & ~1) : Kv;        /* rounds that run (G256: even, the extra one has zero weights) */ \
+    const int Kp = (Kv + 1) & ~1;                      /* rounds that run (even: the extra one has zero weights) */ \
     const bool partial = Kv < K; \
     const int TTp = Kp * CS; \
     const int tile0 = r0 * CS; \
@@ -123,7 +120,7 @@ template <bool G256> struct PairCfg {
     const int my_chunks = slice_chunks >> 1; \
     (void)0
 
-template <bool LADDER, bool G256>
+template <bool LADDER>
 __global__ void __launch_bounds__(kQThreads, 1)
 mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__ CUtensorMap zmap64,
                     const __grid_constant__ CUtensorMap vmap64, const TcParams p) {
@@ -131,7 +128,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
   // GEMM (64-row boxes); one array on the plain bf16 path, the split arrays of prologue.cu with BF16X3
   extern __shared__ __align__(1024) uint8_t smem[];
   if ((smem_u32(smem) & 1023u) != 0) __trap();
-  using Cfg = PairCfg<G256>;
+  using Cfg = PairCfg;
   constexpr int kQSlots = Cfg::QS;
   constexpr int kQSmemG = Cfg::SmemG, kQSmemV = Cfg::SmemV, kQSmemP = Cfg::SmemP, kQSmemNj = Cfg::SmemNj,
                 kQSmemBar = Cfg::SmemBar;
@@ -166,10 +163,16 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
   const long long tail_begin = one_piece ? w_end : u_last * K;
   const bool has_head = head_end > w_begin;
   const int n_parts = n_full + (has_head ? 1 : 0) + (w_end > tail_begin ? 1 : 0);
+#ifdef VGAN_B200_DEBUG
   const uint32_t pbytes = (p.dbg_flags & 1) ? 16u : static_cast<uint32_t>(kQPBytes);   // bit 0: measurement only
+  const int dbg_flags = p.dbg_flags;
+#else
+  constexpr uint32_t pbytes = static_cast<uint32_t>(kQPBytes);
+  constexpr int dbg_flags = 0;
+#endif
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < kGStages; ++s) {
+    for (int s = 0; s < kGStagesMax; ++s) {
       mbar_init(&bar->g_full[s], 1);
       mbar_init(&bar->g_empty[s], 1);
     }
@@ -232,7 +235,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
   if (warp == 8 || warp == 11) {
     // ===================== G producers: Gram operand stages, in the Gram warp's order =====================
     const uint32_t pj = warp == 8 ? 0u : 1u;
-    if constexpr (G256) {
+    {
       uint32_t it = 0;
       for (int k = 0; k < Kp; k += 2) {
         const int jt = min(tile0 + CS * (k + hh) + c, T - 1);   // leader: column tile of round k, peer: of round k + 1
@@ -240,7 +243,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
           if ((it & 1u) == pj) {
             mbar_wait(&bar->g_empty[rs], rph ^ 1);
             uint8_t* dst = smem + kQSmemG + rs * kG2StageBytes;
-            if (p.dbg_flags & 2) {            // measurement only: no operand loads
+            if (dbg_flags & 2) {            // measurement only: no operand loads
               if (lane == 0 && hh == 0) mbar_arrive(&bar->g_full[rs]);
             } else if (lane == 0) {
               if (hh == 0) mbar_arrive_expect_tx(&bar->g_full[rs], 2 * kG2StageBytes);
@@ -254,26 +257,6 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
           if (++rs == kG2Stages) { rs = 0; rph ^= 1; }
         }
       }
-    } else {
-    for (int k = 0; k < Kp; ++k) {
-      const int jt = min(tile0 + CS * k + c, T - 1);
-      for (int kc = 0; kc < p.gchunks; ++kc) {
-        if ((rs & (kGProducers - 1)) == pj) {
-          mbar_wait(&bar->g_empty[rs], rph ^ 1);
-          uint8_t* dst = smem + kQSmemG + rs * kGStageBytes;
-          if (p.dbg_flags & 2) {            // measurement only: no operand loads
-            if (lane == 0 && hh == 0) mbar_arrive(&bar->g_full[rs]);
-          } else if (lane == 0) {
-            if (hh == 0) mbar_arrive_expect_tx(&bar->g_full[rs], 2 * kGStageBytes);
-            tma_load_2d_2cta(dst, &zmap, &bar->g_full[rs], kc * kChunk, ti * kTile);
-          } else if (lane == 1) {
-            tma_load_2d_2cta(dst + kChunkBytes, &zmap64, &bar->g_full[rs], kc * kChunk, jt * kTile + 64 * hh);
-          }
-          __syncwarp();
-        }
-        if (++rs == kGStages) { rs = 0; rph ^= 1; }
-      }
-    }
     }
   } else if (warp == 12) {
     // ===================== V producer: half tiles of Z_J[:, this CTA's half of the slice] =====================
@@ -283,7 +266,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
         for (int h = 0; h < 2; ++h) {
           mbar_wait(&bar->v_empty[rs], rph ^ 1);
           uint8_t* dst = smem + kQSmemV + rs * kVStageBytes;
-          if (p.dbg_flags & 4) {            // measurement only: no V loads
+          if (dbg_flags & 4) {            // measurement only: no V loads
             if (lane == 0 && hh == 0) mbar_arrive(&bar->v_full[rs]);
           } else {
             if (lane == 0 && hh == 0) mbar_arrive_expect_tx(&bar->v_full[rs], slice_chunks * (kChunkBytes / 2));
@@ -326,7 +309,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
       pub_mask ^= 1u << slot;
       if (lane == 0 && peers) {
         const uint32_t src = smem_u32(smem + kQSmemP + slot * kQPBytes);
-        if (p.dbg_flags & 8) {
+        if (dbg_flags & 8) {
           // DSMEM route: one bulk copy per peer (~12 B/clk per SM: 3 x 32 KiB take ~8000 cycles)
           if (t >= kQSlots) mbar_wait(&bar->slot_free[slot], (sf_mask >> slot) & 1);
           for (int d = 0; d < CS; ++d)
@@ -370,10 +353,9 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     }
   } else if (warp == 9) {
     // ===================== leader CTA: Gram MMA stream (warp-uniform; one lane issues) ==========
-    constexpr uint32_t idesc_gram = make_idesc_bf16(2 * kTile, kTile, 0, 0);
     constexpr uint32_t desc_hi = (1024u >> 4) | (1u << 14) | (2u << 29);
     const uint32_t g_lo = (smem_u32(smem + kQSmemG) & 0x3FFFFu) >> 4;
-    if constexpr (G256) {
+    {
       constexpr uint32_t idesc_gram2 = make_idesc_bf16(2 * kTile, 2 * kTile, 0, 0);
       for (int k = 0; k < Kp; k += 2, kg += 2) {       // kg is even here: tile k -> S[0], tile k + 1 -> S[1]
         {
@@ -410,39 +392,6 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
           if (++rs == kG2Stages) { rs = 0; rph ^= 1; }
         }
       }
-    } else {
-    for (int k = 0; k < Kp; ++k, ++kg) {
-      const uint32_t b = kg & 1;
-      const uint32_t d_tmem = tmem + b * kTile;
-      {
-        const long long t0 = VG_CLK();
-        mbar_wait(&bar->s_empty[b], ((kg >> 1) & 1) ^ 1);     // both CTAs' epilogues released S[b]
-        tm1 += VG_CLK() - t0;
-      }
-      tc_fence_after();
-      for (int kc = 0; kc < p.gchunks; ++kc) {
-        {
-          const long long t0 = VG_CLK();
-          mbar_wait(&bar->g_full[rs], rph);
-          tm0 += VG_CLK() - t0;
-        }
-        tc_fence_after();
-        const uint32_t a_lo = g_lo + rs * (kGStageBytes >> 4);
-        const uint32_t b_lo = a_lo + (kChunkBytes >> 4);
-        if (elect_one()) {
-#pragma unroll
-          for (int kk = 0; kk < kChunk / 16; ++kk) {
-            const uint64_t adesc = (static_cast<uint64_t>(desc_hi) << 32) | (a_lo + kk * 2);
-            const uint64_t bdesc = (static_cast<uint64_t>(desc_hi) << 32) | (b_lo + kk * 2);
-            umma_bf16_ss_2cta(d_tmem, adesc, bdesc, idesc_gram, (kc | kk) != 0);
-          }
-          umma_commit_2cta_mc(&bar->g_empty[rs], pair_mask);
-          if (kc == p.gchunks - 1) umma_commit_2cta_mc(&bar->s_full[b], pair_mask);
-        }
-        __syncwarp();
-        if (++rs == kGStages) { rs = 0; rph ^= 1; }
-      }
-    }
     }
   } else if (warp == 10 && hh == 0) {
     // ===================== leader CTA: PV MMA stream =====================
@@ -523,9 +472,11 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
 #pragma unroll
     for (int m = 0; m < VGAN_B200_MAX_SCALES; ++m) {
       ratio[m] = p.par[2 + m];
-      coef_x[m] = p.par[10 + m];
-      coef_y[m] = p.par[18 + m];
+      coef_x[m] = p.par[kParCoefX + m];
+      coef_y[m] = p.par[kParCoefY + m];
     }
+    // common-mode level c_j w0 of (this row block, X columns) / (this row block, Y columns)
+    const float cw0_x = p.par[kParCw0 + (row_is_x ? 0 : 2)], cw0_y = p.par[kParCw0 + (row_is_x ? 0 : 2) + 1];
     float acc_x = 0.f, acc_y = 0.f, rsum = 0.f;
     // One column tile = three steps.  load: wait for S[b] (and the norms), pull this thread's 64 columns into registers
     // and release S[b] at once (before the math), so the next Gram into the buffer overlaps the tile's whole epilogue;
@@ -547,16 +498,17 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     auto compute = [&](int k, uint32_t b, const uint32_t (&va)[32], const uint32_t (&vb)[32], uint4 (&pk)[8]) {
       const long long tq = VG_CLK();
       const int tg = tile0 + CS * k + c;                 // column tile
-      const bool valid = tg < T && k < Kv;               // padded rounds (tail of a unit, G256 padding): zero weights
+      const bool valid = tg < T && k < Kv;               // padded rounds (tail of a unit, even-round padding): zero weights
       const bool col_is_x = min(tg, T - 1) < p.tiles_x;
       float cf[VGAN_B200_MAX_SCALES];
 #pragma unroll
       for (int m = 0; m < VGAN_B200_MAX_SCALES; ++m) cf[m] = valid ? (col_is_x ? coef_x[m] : coef_y[m]) : 0.f;
+      const float cw0 = valid ? (col_is_x ? cw0_x : cw0_y) : 0.f;
       const float* njp = nj_smem + b * kTile + g * 64;
       float ksum = 0.f;
       uint4 h0[4], h1[4];
-      epi_compute_32<LADDER>(va, njp, ni, m2c0, cf, ratio, p.n_scales, ksum, rsum, h0, p.p_lo != 0);
-      epi_compute_32<LADDER>(vb, njp + 32, ni, m2c0, cf, ratio, p.n_scales, ksum, rsum, h1, p.p_lo != 0);
+      epi_compute_32<LADDER>(va, njp, ni, m2c0, cf, ratio, p.n_scales, ksum, rsum, h0, p.p_lo != 0, cw0);
+      epi_compute_32<LADDER>(vb, njp + 32, ni, m2c0, cf, ratio, p.n_scales, ksum, rsum, h1, p.p_lo != 0, cw0);
 #pragma unroll
       for (int i = 0; i < 4; ++i) { pk[i] = h0[i]; pk[4 + i] = h1[i]; }
       mbar_arrive(&bar->nj_empty[b]);                    // the column norms of this tile are no longer read
@@ -585,7 +537,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
       }
       tm3 += VG_CLK() - tq;
     };
-    if constexpr (G256) {
+    {
       // both S buffers fill together: S[1] is pulled (and released) right after the math of S[0], before P(k) waits
       // for its slot, so the next two-tile Gram starts one tile's math after s_full instead of a whole tile later
       for (int k = 0; k < Kp; k += 2, kg += 2) {
@@ -598,14 +550,6 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
         park(k, pk0);
         compute(k + 1, 1, va, vb, pk1);
         park(k + 1, pk1);
-      }
-    } else {
-      for (int k = 0; k < Kp; ++k, ++kg) {
-        uint4 pk[8];
-        uint32_t va[32], vb[32];
-        load_S(kg & 1, (kg >> 1) & 1, va, vb);
-        compute(k, kg & 1, va, vb, pk);
-        park(k, pk);
       }
     }
     // ---- partial sums of this CTA's tiles
@@ -647,7 +591,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
       tc_fence_after();
       if (!dup)
         write_grad_rows(p, tmem_o, static_cast<uint32_t>(q * 32) << 16, g, row, ti, row_is_x, slice, slice_chunks,
-                        rtot, partial);
+                        rtot, partial, r0 == 0);
     }
     tc_fence_before();
     cluster_sync_all();      // #3: O, the norm buffers and P slot 0 may be reused by the next range
@@ -655,6 +599,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     }
   }
 
+#ifdef VGAN_B200_DEBUG
   if (p.dbg && lane == 0 && (warp == 0 || ((warp == 9 || warp == 10) && hh == 0))) {
     float* d = p.dbg + static_cast<int64_t>(blockIdx.x) * p.dbg_stride;
     const int o = warp == 0 ? 4 : (warp == 9 ? 0 : 8);
@@ -674,21 +619,19 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     atomicMin(&p.timeline[0], gt_begin);
     atomicMax(&p.timeline[1], global_timer_ns());
   }
+#else
+  (void)tm0; (void)tm1; (void)tm2; (void)tm3; (void)tm_tail; (void)t_begin; (void)gt_begin;
+#endif
   if (warp == 11) tmem_dealloc_2cta(tmem, 512);
 }
 
-int g_pair_variant = 0;   // tuning/measurement: vgan_b200_debug_variant() (bits >= 8 -> TcParams::dbg_flags)
-
-int launch_tc_pair(const TcParams& p, const CUtensorMap& map, const CUtensorMap& map64, const CUtensorMap& mapV64,
-                   int ladder, cudaStream_t st, int* resident_ctas) {
+int launch_tc_pair(vgan_b200_ctx* ctx, const TcParams& p, const CUtensorMap& map, const CUtensorMap& map64,
+                   const CUtensorMap& mapV64, int ladder, cudaStream_t st, int* resident_ctas) {
   if (resident_ctas) *resident_ctas = 0;
   const int ngrad = (p.gx_end - p.gx_begin) + (p.gy_end - p.gy_begin);
   if (ngrad <= 0) return VGAN_B200_OK;
-  // VGAN_B200_GRAM256=0 selects the one-column-tile-per-issue Gram (the round-1 structure) for A/B measurements
-  static const int gram256 = getenv("VGAN_B200_GRAM256") ? atoi(getenv("VGAN_B200_GRAM256")) : 1;
-  auto kern = gram256 ? (ladder ? mmd2_tc_pair_kernel<true, true> : mmd2_tc_pair_kernel<false, true>)
-                      : (ladder ? mmd2_tc_pair_kernel<true, false> : mmd2_tc_pair_kernel<false, false>);
-  const int smem_bytes = gram256 ? PairCfg<true>::SmemTotal : PairCfg<false>::SmemTotal;
+  auto kern = ladder ? mmd2_tc_pair_kernel<true> : mmd2_tc_pair_kernel<false>;
+  const int smem_bytes = PairCfg::SmemTotal;
   VG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
   const int n_units = ((ngrad + 1) / 2) * p.ngroups;
   cudaLaunchConfig_t cfg{};
@@ -702,20 +645,17 @@ int launch_tc_pair(const TcParams& p, const CUtensorMap& map, const CUtensorMap&
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  // persistent grid: as many clusters as can be resident at once (cached per cluster size)
-  static int max_clusters[9] = {0};   // the same for all four instantiations (same block size and shared memory)
-  int& ncl = max_clusters[2 * p.cs];
+  // persistent grid: as many clusters as can be resident at once (cached per cluster size in the context; the same
+  // for both instantiations: same block size and shared memory)
+  int& ncl = ctx->resident_clusters[2 * p.cs];
   if (ncl == 0) {
     cfg.gridDim = dim3(static_cast<unsigned>(2 * p.cs * 64));
     VG_CUDA_CHECK(cudaOccupancyMaxActiveClusters(&ncl, kern, &cfg));
     if (ncl < 1) ncl = 1;
-    if (getenv("VGAN_B200_VERBOSE"))
-      fprintf(stderr, "vgan_b200: pair kernel, cluster %d: %d resident clusters\n", 2 * p.cs, ncl);
   }
-  static const int persist = getenv("VGAN_B200_PERSIST") ? atoi(getenv("VGAN_B200_PERSIST")) : 1;   // 0: one cluster per unit (measurement)
   int cap = ncl;
-  if ((g_pair_variant & 255) > 0 && (g_pair_variant & 255) < cap) cap = g_pair_variant & 255;   // tests: force stream-K cuts
-  const int n_clusters = (persist && cap < n_units) ? cap : n_units;
+  if (p.max_clusters > 0 && p.max_clusters < cap) cap = p.max_clusters;   // vgan_b200_set_cluster_limit
+  const int n_clusters = cap < n_units ? cap : n_units;
   cfg.gridDim = dim3(static_cast<unsigned>(n_clusters * 2 * p.cs));
   if (resident_ctas) *resident_ctas = (n_clusters < ncl ? n_clusters : ncl) * 2 * p.cs;
   VG_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, map, map64, mapV64, p));

@@ -259,25 +259,24 @@ mmd2_xx_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__
   }
   tc_fence_before();
   __syncthreads();
+#ifdef VGAN_B200_DEBUG
   if (p.timeline && threadIdx.x == 0) {
     atomicMin(&p.timeline[2], gt_begin);
     atomicMax(&p.timeline[3], global_timer_ns());
   }
+#else
+  (void)gt_begin;
+#endif
   if (warp == 11) tmem_dealloc(tmem, 512);
 }
 
 // max_ctas > 0 bounds the grid (the SMs a concurrently running kernel leaves free); 0 = one CTA per SM
-int launch_xx(const TcParams& p, const CUtensorMap& map, const CUtensorMap& map256, int ladder, cudaStream_t st,
-              int max_ctas) {
+int launch_xx(vgan_b200_ctx* ctx, const TcParams& p, const CUtensorMap& map, const CUtensorMap& map256, int ladder,
+              cudaStream_t st, int max_ctas) {
   if (p.n_xx_units <= 0) return VGAN_B200_OK;
   auto kern = ladder ? mmd2_xx_kernel<true> : mmd2_xx_kernel<false>;
   VG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kXSmemTotal));
-  static int n_sms = 0;
-  if (n_sms == 0) {
-    int dev = 0;
-    VG_CUDA_CHECK(cudaGetDevice(&dev));
-    VG_CUDA_CHECK(cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev));
-  }
+  const int n_sms = ctx->n_sms;
   const long long total = xx_total_steps(p.xx_part, p.xx_nparts, p.n_xx_units, p.tiles_x);
   long long grid = max_ctas > 0 ? max_ctas : n_sms;
   if (grid > total) grid = total;
