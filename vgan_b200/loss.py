@@ -18,7 +18,6 @@ gradients by ``grad_output``).  There is no CPU implementation here.
 from __future__ import annotations
 
 import ctypes as C
-import os
 from typing import Optional
 
 import torch
@@ -31,8 +30,12 @@ def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
     return None if t is None else t.data_ptr()
 
 
-def _stream() -> int:
-    return torch.cuda.current_stream().cuda_stream
+def _stream(device=None) -> int:
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+def _ctx(device: torch.device):
+    return _lib.ctx(device.index if device.index is not None else torch.cuda.current_device())
 
 
 def _as_input(t: torch.Tensor, device) -> torch.Tensor:
@@ -46,71 +49,75 @@ def _is_ladder(mults) -> bool:
 
 
 class _Workspace:
-    """Device scratch for one problem shape, reused across calls."""
+    """Device scratch for one problem shape, reused across calls; typed views of the parts the host side touches
+    (results, and on several GPUs the blocks that are exchanged — see dist.py)."""
 
-    def __init__(self, Nx, Ny, D, D_u, flags, device):
-        self.layout = _lib.layout(Nx, Ny, D, D_u, flags)
-        self.buf = torch.empty(self.layout.total + 1024, dtype=torch.uint8, device=device)
+    def __init__(self, Nx, Ny, D, D_u, mults, flags, device):
+        self.layout = L = _lib.layout(Nx, Ny, D, D_u, len(mults), flags)
+        self.buf = torch.empty(L.total + 1024, dtype=torch.uint8, device=device)
         base = self.buf.data_ptr()
         self.ptr = (base + 1023) // 1024 * 1024
-        self.sums = torch.zeros(4, dtype=torch.float64, device=device)
-        self.penalty = torch.zeros(1, dtype=torch.float32, device=device)
-        self.loss = torch.zeros(1, dtype=torch.float32, device=device)
-        self.inv_scales = torch.zeros(_lib.MAX_SCALES, dtype=torch.float32, device=device)
+        self._off0 = self.ptr - base
+        self.mults_c = (C.c_float * len(mults))(*[float(v) for v in mults])
+        self.sums = self.view(L.off_sums, 4, torch.float64)
+        self.colsum = self.view(L.off_colsum, L.Dp, torch.float64)[:D]
+        self.reduced = self.view(L.off_sums, 4 + L.Dp, torch.float64)         # [S_xx, S_xy, S_yy, spare | colsum]
+        self.stats = self.view(L.off_stats, 2 + 2 * L.Dp, torch.float64)
+        self.cmax = self.view(L.off_cmax, D_u, torch.int64) if D_u > 0 else None
+        self.penalty = self.view(L.off_misc, 1, torch.float32)
+        self.loss = self.view(L.off_misc + 4, 1, torch.float32)
+        rows = L.Nxp + L.Nyp
+        fp32 = (flags & _lib.PREC_FP32) != 0
+        width = L.Dp * (3 if (flags & _lib.BF16X3) else 1)
+        if fp32:
+            self.operand = [self.view(L.off_zf, rows * L.Dp, torch.float32).view(rows, L.Dp)]
+            self.norms = self.view(L.off_nrm, rows, torch.float32)
+        else:
+            n_arr = 2 if (flags & _lib.BF16X3) else 1
+            z = self.view(L.off_zq, n_arr * rows * width, torch.bfloat16).view(n_arr, rows, width)
+            self.operand = [z[k] for k in range(n_arr)]
+            self.norms = self.view(L.off_nrms, rows, torch.float32)
+        self.layout_ref = C.byref(self.layout)
+
+    def view(self, off: int, count: int, dtype: torch.dtype) -> torch.Tensor:
+        nbytes = count * torch.empty((), dtype=dtype).element_size()
+        return self.buf[self._off0 + off:self._off0 + off + nbytes].view(dtype)
 
 
 _ws_cache = {}
 
 
-def _workspace(Nx, Ny, D, D_u, flags, device) -> _Workspace:
-    key = (Nx, Ny, D, D_u, flags & (_lib.PREC_FP32 | _lib.BF16X3), str(device),
-           torch.cuda.current_stream().cuda_stream)
+def _workspace(Nx, Ny, D, D_u, mults, flags, device) -> _Workspace:
+    key = (Nx, Ny, D, D_u, tuple(float(v) for v in mults), flags, str(device),
+           torch.cuda.current_stream(device).cuda_stream)
     ws = _ws_cache.get(key)
     if ws is None:
         if len(_ws_cache) > 16:
             _ws_cache.clear()
-        ws = _ws_cache[key] = _Workspace(Nx, Ny, D, D_u, flags, device)
+        ws = _ws_cache[key] = _Workspace(Nx, Ny, D, D_u, mults, flags, device)
     return ws
 
 
 def default_precision(D: int) -> str:
-    """bf16 tensor-core path by default; tiny feature widths (the VGAN encodings,
-    latent = D//16) go to the fp32 CUDA-core path where a 64-wide K chunk would be padding."""
+    """bf16 tensor-core path by default (bf16 operands meet the stated 2e-3 from D = 32); narrower inputs (the VGAN
+    encodings, latent = D//16) take the fp32-class path, which is the split-operand tensor-core kernel as well."""
     return "fp32" if D < 32 else "bf16"
 
 
 def _precision_flags(precision: str, D: int) -> int:
     """"bf16": bf16 operands on the tensor cores (2e-3).  "fp32": fp32-class results (1e-4) — split bf16 operands on
-    the tensor cores ("bf16x3": 2.5-35x faster than the CUDA-core kernel from D = 16 to 4096, profiles/r1d_sweep.jsonl),
-    the CUDA-core kernel ("simt") only for the tiny widths of the VGAN encodings (D < 32), where a 64-wide K chunk is
-    mostly padding.  "simt" / "bf16x3" force one of the two."""
+    the tensor cores ("bf16x3") at every width (faster than the CUDA-core kernel wherever both were measured).
+    "simt" forces the CUDA-core fp32 kernel, "bf16x3" the split-operand one."""
     if precision == "bf16":
         return _lib.PREC_BF16
-    if precision == "simt" or (precision == "fp32" and D < 32):
+    if precision == "simt":
         return _lib.PREC_FP32
     if precision in ("bf16x3", "fp32"):
         return _lib.PREC_BF16 | _lib.BF16X3
     raise RuntimeError(f"vgan_b200: unknown precision {precision!r} (bf16, fp32, bf16x3, simt)")
 
 
-def mmd2_eval(X: torch.Tensor, Y: Optional[torch.Tensor], U: Optional[torch.Tensor], *,
-              weight: float, bw_dev: torch.Tensor, frozen: bool, mults, precision: str = "bf16",
-              need_dX: bool = False, need_dY: bool = True, masked: bool = False,
-              penalty_grad: bool = True, row_begin: int = 0, row_end: Optional[int] = None,
-              xx_part: int = 0, xx_nparts: int = 1, center: bool = True, finalize: bool = True,
-              k1_events=None):
-    """Run prologue -> scales -> fused fwd+bwd -> penalty -> finalize on the current stream.
-
-    ``masked=True``: Y is formed as U*X inside the prologue and the returned ``dY`` is already
-    dL/dU = dL/dY * X (+ penalty gradient).  Returns dict(loss, sums, dX, dY, penalty); tensors
-    stay on the device, nothing synchronises."""
-    L = _lib.lib()
-    dev = X.device
-    if dev.type != "cuda":
-        raise RuntimeError("vgan_b200: inputs must live on a CUDA (sm_100) device; there is no CPU path")
-    Nx, D = X.shape
-    Ny = Nx if masked else Y.shape[0]
-    D_u = 0 if U is None else U.shape[1]
+def make_flags(precision: str, D: int, mults, center: bool = True, need_dX: bool = False) -> int:
     flags = _precision_flags(precision, D)
     if center:
         flags |= _lib.CENTER
@@ -118,50 +125,71 @@ def mmd2_eval(X: torch.Tensor, Y: Optional[torch.Tensor], U: Optional[torch.Tens
         flags |= _lib.NEED_DX
     if not (flags & _lib.PREC_FP32) and _is_ladder(mults):
         flags |= _lib.LADDER
-    if os.environ.get("VGAN_B200_NO_CLUSTER"):
-        flags |= _lib.NO_CLUSTER
-    if os.environ.get("VGAN_B200_NO_PAIR"):
-        flags |= _lib.NO_PAIR
-    ws = _workspace(Nx, Ny, D, D_u, flags, dev)
-    st = _stream()
-    row_end = max(Nx, Ny) if row_end is None else row_end
-    n_rows = row_end - row_begin
+    return flags
 
-    _lib.check(L.vgan_b200_prologue(_ptr(X), _ptr(U) if masked else None, None if masked else _ptr(Y),
-                                    Nx, Ny, D, flags, ws.ptr, st), "prologue")
-    m_arr = (C.c_float * len(mults))(*[float(v) for v in mults])
-    _lib.check(L.vgan_b200_scales(ws.ptr, Nx, Ny, D, _ptr(bw_dev), 1 if frozen else 0, m_arr, len(mults),
-                                  _ptr(ws.inv_scales), st), "scales")
-    ws.sums.zero_()
-    ws.penalty.zero_()
-    want_grad = need_dY or need_dX
-    dY = torch.empty((min(row_end, Ny) - row_begin, D), dtype=torch.float32, device=dev) if want_grad else None
-    dX = torch.empty((min(row_end, Nx) - row_begin, D), dtype=torch.float32, device=dev) if need_dX else None
-    mul = X[row_begin:] if (masked and want_grad) else None
-    if k1_events is not None:
-        k1_events[0].record()
-    _lib.check(L.vgan_b200_mmd2_fwd_bwd(ws.ptr, Nx, Ny, D, row_begin, row_end, xx_part, xx_nparts,
-                                        _ptr(ws.inv_scales), len(mults), flags, _ptr(ws.sums), _ptr(dY),
-                                        _ptr(mul), _ptr(dX), st), "mmd2_fwd_bwd")
-    if k1_events is not None:
-        k1_events[1].record()
-    dU_pen = None
-    if U is not None and weight != 0:
-        tgt = None
-        if penalty_grad:
+
+def mmd2_eval(X: torch.Tensor, Y: Optional[torch.Tensor], U: Optional[torch.Tensor], *,
+              weight: float, bw_dev: torch.Tensor, frozen: bool, mults, precision: str = "bf16",
+              need_dX: bool = False, need_dY: bool = True, masked: bool = False,
+              penalty_grad: bool = True, row_begin: int = 0, row_end: Optional[int] = None,
+              xx_part: int = 0, xx_nparts: int = 1, center: bool = True, k1_events=None):
+    """stats -> scales -> pack -> fused fwd+bwd -> finalize on the current stream of X's device.
+
+    ``masked=True``: Y is formed as U*X inside the prologue and the returned ``dY`` is already
+    dL/dU = dL/dY * X (+ penalty gradient).  A row range / S_xx part selects a shard of K1 (the prologue still covers
+    every row: this is the single-process form; dist.py splits the prologue as well).
+    Returns dict(loss, sums, colsum, dX, dY, dU_penalty, penalty, ws); tensors stay on the device, nothing
+    synchronises.  ``loss``, ``sums``, ``colsum`` and ``penalty`` are views of the workspace (valid until the next
+    evaluation of the same shape on the same stream)."""
+    L = _lib.lib()
+    dev = X.device
+    if dev.type != "cuda":
+        raise RuntimeError("vgan_b200: inputs must live on a CUDA (sm_100) device; there is no CPU path")
+    Nx, D = X.shape
+    Ny = Nx if masked else Y.shape[0]
+    use_pen = U is not None and weight != 0
+    D_u = U.shape[1] if use_pen else 0
+    flags = make_flags(precision, D, mults, center, need_dX)
+    with torch.cuda.device(dev):
+        ws = _workspace(Nx, Ny, D, D_u, mults, flags, dev)
+        ctx, st = _ctx(dev), _stream(dev)
+        n_all = max(Nx, Ny)
+        row_end = n_all if row_end is None else row_end
+        want_grad = need_dY or need_dX
+        dY = torch.empty((max(min(row_end, Ny) - row_begin, 0), D), dtype=torch.float32, device=dev) if want_grad else None
+        dX = torch.empty((max(min(row_end, Nx) - row_begin, 0), D), dtype=torch.float32, device=dev) if need_dX else None
+        mul = X[row_begin:] if (masked and want_grad) else None
+        dU_pen, tgt = None, None
+        if use_pen and penalty_grad:
             if masked and dY is not None:
-                tgt = dY                       # accumulate straight into dL/dU
+                tgt = dY                       # the penalty gradient goes straight into dL/dU
             else:
-                dU_pen = torch.zeros((n_rows if masked else U.shape[0], D_u), dtype=torch.float32, device=dev)
+                dU_pen = torch.zeros((row_end - row_begin if masked else U.shape[0], D_u), dtype=torch.float32, device=dev)
                 tgt = dU_pen
-        rb = row_begin if masked else 0
-        nr = (tgt.shape[0] if tgt is not None else 0)
-        _lib.check(L.vgan_b200_colmax_penalty(_ptr(U), U.shape[0], D_u, float(weight), ws.ptr + ws.layout.off_cmax,
-                                              _ptr(ws.penalty), _ptr(tgt), rb, nr, st), "colmax_penalty")
-    if finalize:
-        _lib.check(L.vgan_b200_finalize_loss(_ptr(ws.sums), Nx, Ny, _ptr(ws.penalty), _ptr(ws.loss), st),
-                   "finalize_loss")
-    return dict(loss=ws.loss, sums=ws.sums, dX=dX, dY=dY, dU_penalty=dU_pen, penalty=ws.penalty, ws=ws)
+        Up = _ptr(U) if (masked or use_pen) else None
+        Yp = None if masked else _ptr(Y)
+        whole = row_begin == 0 and row_end >= n_all and xx_nparts == 1 and k1_events is None
+        if whole:
+            args = _lib.EvalArgs(C.pointer(ws.layout), ws.ptr, _ptr(X), Up, Yp, _ptr(bw_dev), 1 if frozen else 0,
+                                 ws.mults_c, float(weight), _ptr(dY), _ptr(mul), _ptr(dX), _ptr(tgt), None, st)
+            _lib.check(L.vgan_b200_mmd2_eval(ctx, C.byref(args)), "mmd2_eval")
+        else:
+            lay = ws.layout_ref
+            _lib.check(L.vgan_b200_stats(ctx, lay, ws.ptr, _ptr(X), Up, Yp, 0, n_all, st), "stats")
+            _lib.check(L.vgan_b200_scales(ctx, lay, ws.ptr, _ptr(bw_dev), 1 if frozen else 0, ws.mults_c, float(weight),
+                                          st), "scales")
+            _lib.check(L.vgan_b200_pack(ctx, lay, ws.ptr, _ptr(X), Up, Yp, 0, n_all, st), "pack")
+            if k1_events is not None:
+                k1_events[0].record()
+            _lib.check(L.vgan_b200_mmd2_fwd_bwd(ctx, lay, ws.ptr, row_begin, row_end, xx_part, xx_nparts, _ptr(dY),
+                                                _ptr(mul), _ptr(dX), st), "mmd2_fwd_bwd")
+            if k1_events is not None:
+                k1_events[1].record()
+            rb = row_begin if masked else 0
+            nr = tgt.shape[0] if tgt is not None else 0
+            _lib.check(L.vgan_b200_finalize(ctx, lay, ws.ptr, float(weight), _ptr(tgt), rb, nr,
+                                            1 if (tgt is not None and tgt is dY) else 0, None, st), "finalize")
+    return dict(loss=ws.loss, sums=ws.sums, colsum=ws.colsum, dX=dX, dY=dY, dU_penalty=dU_pen, penalty=ws.penalty, ws=ws)
 
 
 class RBF(nn.Module):
@@ -207,19 +235,20 @@ class RBF(nn.Module):
         dev = X.device
         if dev.type != "cuda":
             raise RuntimeError("vgan_b200.RBF: input must be on a CUDA (sm_100) device")
-        Z = _as_input(X, dev)
-        n, D = Z.shape
-        bw, frozen = self._bw_state(dev)
-        st = _stream()
-        if not frozen:
-            # closed form of sum_ij |zi-zj|^2 / (n^2-n)  (Mmd_loss_constrained.py:16-22), on device
-            zs = Z.double()
-            tot = 2.0 * n * (zs * zs).sum() - 2.0 * (zs.sum(0) ** 2).sum()
-            bw.copy_((tot / (n * n - n)).float().reshape(1))
-        inv = 1.0 / (bw * torch.tensor(self._mults, dtype=torch.float32, device=dev))
-        K = torch.empty((n, n), dtype=torch.float32, device=dev)
-        _lib.check(L.vgan_b200_mmd2_matrix(_ptr(Z), n, D, _ptr(inv), len(self._mults), 0.0, _ptr(K), st),
-                   "mmd2_matrix")
+        with torch.cuda.device(dev):
+            Z = _as_input(X, dev)
+            n, D = Z.shape
+            bw, frozen = self._bw_state(dev)
+            st = _stream(dev)
+            if not frozen:
+                # closed form of sum_ij |zi-zj|^2 / (n^2-n)  (Mmd_loss_constrained.py:16-22), on device
+                zs = Z.double()
+                tot = 2.0 * n * (zs * zs).sum() - 2.0 * (zs.sum(0) ** 2).sum()
+                bw.copy_((tot / (n * n - n)).float().reshape(1))
+            inv = 1.0 / (bw * torch.tensor(self._mults, dtype=torch.float32, device=dev))
+            K = torch.empty((n, n), dtype=torch.float32, device=dev)
+            _lib.check(L.vgan_b200_mmd2_matrix(_ctx(dev), _ptr(Z), n, D, _ptr(inv), len(self._mults), 0.0, _ptr(K), st),
+                       "mmd2_matrix")
         self._freeze()
         return K
 
@@ -260,6 +289,9 @@ class _MaskedFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, X, U, module):
+        if ctx.needs_input_grad[0]:
+            raise RuntimeError("forward_masked: a gradient with respect to X is not produced on the fused path; "
+                               "call forward(X, U*X, U) when X requires grad")
         dev = X.device
         Xc, Uc = _as_input(X, dev), _as_input(U, dev)
         kernel = module.kernel
@@ -273,6 +305,7 @@ class _MaskedFn(torch.autograd.Function):
         ctx.dU = out["dY"] if need_dU else None
         ctx.u_dtype = U.dtype
         module.last_sums = out["sums"]
+        module.last_colsum = out["colsum"]
         return out["loss"][0].clone()
 
     @staticmethod
@@ -295,6 +328,7 @@ class MMDLossConstrained(nn.Module):
         self.center = center
         self.device = torch.device('cuda:0' if torch.cuda.is_available() else 'cpu')
         self.last_sums = None
+        self.last_colsum = None
 
     def forward(self, X, Y, U):
         if X.dim() != 2 or Y.dim() != 2 or X.shape[1] != Y.shape[1]:
@@ -309,7 +343,8 @@ class MMDLossConstrained(nn.Module):
         return loss
 
     def forward_masked(self, X, U):
-        """Same value and gradient as ``forward(X, U*X, U)`` (src/vgan.py:615-616) in one fused call."""
+        """Same value and dL/dU as ``forward(X, U*X, U)`` (src/vgan.py:615-616) in one fused call.  X must not
+        require grad (the reference's no-KL step differentiates with respect to U only)."""
         if X.shape != U.shape:
             raise RuntimeError("forward_masked: X and U must have the same shape")
         if X.device.type != "cuda":

@@ -6,9 +6,16 @@ from torch import nn
 
 
 class upper_softmax(nn.Module):
-    """softmax over features; entries >= 1/D become exactly 1 (Generator.py:18-22)."""
+    """softmax over features; entries >= 1/D become exactly 1 (Generator.py:18-22).  float32 CUDA activations take
+    the fused kernels of softmax.py (one launch forward, one backward); everything else (the MLP is plain torch and
+    also runs on the CPU) the torch formula."""
+
+    fused = True
 
     def forward(self, x):
+        if self.fused and x.is_cuda and x.dim() == 2 and x.dtype == torch.float32:
+            from .softmax import upper_softmax_cuda
+            return upper_softmax_cuda(x)
         p = torch.nn.functional.softmax(x, 1)
         thr = 1 / p.shape[1]
         return torch.less(p, thr) * p + torch.greater_equal(p, thr)

@@ -1,5 +1,6 @@
 """``torch.ops.vgan_b200.*`` — the C-ABI entry points registered as PyTorch operators ("torch
-binding"): functional ops with schemas, CUDA implementations only.  Calling one with CPU tensors fails in the
+binding"): functional ops with schemas, CUDA implementations only.  This file is boundary plumbing (schemas over the
+same ctypes calls the nn.Module classes make), not a component of its own.  Calling one with CPU tensors fails in the
 dispatcher (there is no CPU kernel to fall back to), with CUDA tensors on a non-sm_100 device in the C library
 (``VGAN_B200_ERR_DEVICE``).
 
@@ -58,8 +59,10 @@ def _mmd2_matrix(Z, inv_scales, eps):
     Zc, inv = _f32(Z), _f32(inv_scales)
     n, D = Zc.shape
     K = torch.empty((n, n), dtype=torch.float32, device=Zc.device)
-    _lib.check(_lib.lib().vgan_b200_mmd2_matrix(Zc.data_ptr(), n, D, inv.data_ptr(), inv.numel(), float(eps),
-                                                K.data_ptr(), torch.cuda.current_stream().cuda_stream), "mmd2_matrix")
+    with torch.cuda.device(Zc.device):
+        _lib.check(_lib.lib().vgan_b200_mmd2_matrix(_loss._ctx(Zc.device), Zc.data_ptr(), n, D, inv.data_ptr(), inv.numel(),
+                                                    float(eps), K.data_ptr(),
+                                                    torch.cuda.current_stream(Zc.device).cuda_stream), "mmd2_matrix")
     return K
 
 

@@ -17,7 +17,7 @@ from __future__ import annotations
 import torch
 
 from . import _lib
-from .loss import _as_input, _ptr, _stream
+from .loss import _as_input, _ctx, _ptr, _stream
 
 
 class MMDStatistic:
@@ -40,8 +40,10 @@ class MMDStatistic:
         _lib.check(L.vgan_b200_permutation_scratch_bytes(n, C.byref(nbytes)), "permutation_scratch_bytes")
         scratch = torch.empty(nbytes.value, dtype=torch.uint8, device=K.device)
         stats = torch.empty(member_1.shape[0], dtype=torch.float64, device=K.device)
-        _lib.check(L.vgan_b200_permutation_stats(_ptr(K), n, self.n_1, _ptr(member_1), member_1.shape[0],
-                                                 _ptr(scratch), _ptr(stats), _stream()), "permutation_stats")
+        with torch.cuda.device(K.device):
+            _lib.check(L.vgan_b200_permutation_stats(_ctx(K.device), _ptr(K), n, self.n_1, _ptr(member_1),
+                                                     member_1.shape[0], _ptr(scratch), _ptr(stats), _stream(K.device)),
+                       "permutation_stats")
         return stats
 
     def __call__(self, sample_1, sample_2, alphas, ret_matrix=False):
@@ -56,8 +58,9 @@ class MMDStatistic:
         if inv.numel() < 1 or inv.numel() > _lib.MAX_SCALES:
             raise RuntimeError(f"MMDStatistic: between 1 and {_lib.MAX_SCALES} alphas are supported")
         K = torch.empty((n, n), dtype=torch.float32, device=dev)
-        _lib.check(_lib.lib().vgan_b200_mmd2_matrix(_ptr(Z), n, D, _ptr(inv), inv.numel(), 1e-5, _ptr(K),
-                                                    _stream()), "mmd2_matrix")
+        with torch.cuda.device(dev):
+            _lib.check(_lib.lib().vgan_b200_mmd2_matrix(_ctx(dev), _ptr(Z), n, D, _ptr(inv), inv.numel(), 1e-5, _ptr(K),
+                                                        _stream(dev)), "mmd2_matrix")
         member = torch.zeros(1, n, dtype=torch.uint8, device=dev)
         member[0, :self.n_1] = 1
         mmd = self._statistic(K, member)[0].float()

@@ -33,8 +33,10 @@ def unique_subspaces(u: torch.Tensor, threshold: float | None = None):
     uniq = torch.empty((n, D), dtype=torch.uint8, device=u.device)
     counts = torch.empty(n, dtype=torch.int64, device=u.device)
     n_unique = torch.zeros(1, dtype=torch.int32, device=u.device)
-    _lib.check(L.vgan_b200_subspace_dist(src.data_ptr(), is_bool, n, D, thr, scratch.data_ptr(), uniq.data_ptr(),
-                                         counts.data_ptr(), n_unique.data_ptr(),
-                                         torch.cuda.current_stream().cuda_stream), "subspace_dist")
+    with torch.cuda.device(u.device):
+        ctx = _lib.ctx(u.device.index if u.device.index is not None else torch.cuda.current_device())
+        _lib.check(L.vgan_b200_subspace_dist(ctx, src.data_ptr(), is_bool, n, D, thr, scratch.data_ptr(), uniq.data_ptr(),
+                                             counts.data_ptr(), n_unique.data_ptr(),
+                                             torch.cuda.current_stream(u.device).cuda_stream), "subspace_dist")
     m = int(n_unique.item())                # the one host sync: the result shape
     return uniq[:m].bool(), counts[:m]
