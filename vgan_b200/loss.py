@@ -158,7 +158,9 @@ def mmd2_eval(X: torch.Tensor, Y: Optional[torch.Tensor], U: Optional[torch.Tens
         want_grad = need_dY or need_dX
         dY = torch.empty((max(min(row_end, Ny) - row_begin, 0), D), dtype=torch.float32, device=dev) if want_grad else None
         dX = torch.empty((max(min(row_end, Nx) - row_begin, 0), D), dtype=torch.float32, device=dev) if need_dX else None
-        mul = X[row_begin:] if (masked and want_grad) else None
+        if dY is not None and dY.shape[0] == 0 and not need_dX:
+            dY = None                          # empty shard: forward sums of its S_xx tiles only
+        mul = X[row_begin:] if (masked and dY is not None) else None
         dU_pen, tgt = None, None
         if use_pen and penalty_grad:
             if masked and dY is not None:
