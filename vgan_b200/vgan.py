@@ -11,7 +11,8 @@ B200 loss op.  What is re-plumbed and what is kept on purpose
 * kept: seeds (``VGAN`` forces 777, :48), Adadelta + weight decay, the 1-detector/5-generator
   epoch schedule (:251-332), ``weight=temperature`` resp. ``weight=10`` (:214,:571), the
   ``Variable(generator(noise))`` detach in the generator phase of ``VGAN`` which leaves the
-  generator without gradients (:307-310), re-seeding in
+  generator without gradients (:307-310), the encoder that stays frozen after the first
+  generator phase (:266-267 re-enable the decoder only, :319-320 freeze the whole detector), re-seeding in
   ``generate_subspaces`` (:364-366), the unique-rows subspace distribution (:372-382) and the
   ``check_if_myopic`` protocol (:384-431) with ``alphas=[bandwidth]`` passed as-is.
 The generator/detector MLPs stay in torch (models.py)."""
@@ -43,9 +44,13 @@ class _GraphedStep:
 
     def __init__(self, fn, enabled: bool, warmup: int = 3):
         self.fn, self.enabled, self.warmup = fn, enabled, warmup
-        self.graph, self.static, self.calls = None, None, 0
+        self.graph, self.static, self.calls, self.key = None, None, 0, None
 
-    def __call__(self, batch):
+    def __call__(self, batch, key=None):
+        """``key``: anything the captured work depends on besides the batch (e.g. which parameters are trainable);
+        a change drops the graph and starts over with eager warm-up steps."""
+        if key != self.key:
+            self.graph, self.static, self.calls, self.key = None, None, 0, key
         if self.graph is not None:
             self.static.copy_(batch)
             self.graph.replay()
@@ -243,8 +248,10 @@ class VGAN(_SubspaceGAN):
         acc = torch.zeros((), device=self.device)
 
         def detector_step(batch):
-            # maximise MMD(enc, penc) - 0.1 (reconstruction terms)  (:251-291)
-            for p in detector.parameters():
+            # maximise MMD(enc, penc) - 0.1 (reconstruction terms)  (:251-291).  Only the DECODER is re-enabled here
+            # (:266-267): the generator phase freezes every detector parameter (:319-320), so from the second detector
+            # phase on the encoder stays frozen and only the reconstruction terms train the decoder.  Kept.
+            for p in detector.decoder.parameters():
                 p.requires_grad = True
             enc, dec = detector(batch)
             with torch.no_grad():
@@ -283,7 +290,9 @@ class VGAN(_SubspaceGAN):
             acc.zero_()
             if iternum_d <= self.iternum_d:
                 for batch in self._batches(Xd):
-                    run_detector(batch)
+                    # the captured step depends on which parameters are trainable (all of them in the first detector
+                    # phase, the decoder only afterwards): re-captured when that changes
+                    run_detector(batch, key=tuple(p.requires_grad for p in detector.parameters()))
                 self.bandwidth = loss_function.bandwidth
                 detector_loss = float(acc)
                 iternum_d += 1
