@@ -91,8 +91,9 @@ def test_kl_detector_encoder_stays_frozen_after_first_generator_phase(monkeypatc
     m1 = _fit(VGAN, None, X, monkeypatch, batch_size=500, epochs=1)     # after the first detector phase
     m7 = _fit(VGAN, None, X, monkeypatch, batch_size=500, epochs=7)     # after the second detector phase
     for a, b in zip(m1.detector.encoder.parameters(), m7.detector.encoder.parameters()):
-        assert torch.equal(a, b)
-    assert any(not torch.equal(a, b) for a, b in zip(m1.detector.decoder.parameters(), m7.detector.decoder.parameters()))
+        assert torch.allclose(a, b, rtol=1e-4, atol=1e-6)      # equal up to the atomics' summation order in epoch 0
+    assert any(float((a - b).abs().max()) > 1e-4
+               for a, b in zip(m1.detector.decoder.parameters(), m7.detector.decoder.parameters()))
 
 
 def test_kl_training_matches_eager_reference(monkeypatch, capsys):

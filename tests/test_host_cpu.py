@@ -20,17 +20,46 @@ def test_build_and_exports_match_header():
     assert declared == set(_lib.EXPORTS)
     for name in declared:
         assert getattr(lib, name) is not None
+    # the product library exports exactly the documented entry points: no probes, no debug switches, no C++ symbols
+    import subprocess
+    nm = subprocess.run(["nm", "-D", "--defined-only", _lib.LIB_PATH], capture_output=True, text=True).stdout
+    exported = {ln.split()[-1] for ln in nm.splitlines() if " T " in ln}
+    assert exported == declared, exported ^ declared
+    # the measurement entry points live in the debug build only
+    dbg = ctypes.CDLL(_lib.DBG_LIB_PATH)
+    for name in _lib.DEBUG_EXPORTS:
+        assert getattr(dbg, name) is not None and name not in exported
+
+
+def test_context_fails_loudly_without_device():
+    """No GPU here: creating a context must fail with ERR_DEVICE and a message, never fall back."""
+    from vgan_b200 import _lib
+    if torch.cuda.is_available():
+        pytest.skip("needs a machine without CUDA devices")
+    h = ctypes.c_void_p()
+    assert _lib.lib().vgan_b200_create(0, ctypes.byref(h)) == -2 and not h
+    assert b"no CUDA device" in _lib.lib().vgan_b200_last_error()
+    with pytest.raises(RuntimeError, match="no CUDA device"):
+        _lib.ctx(0)
 
 
 def test_layout_is_pure_host_logic():
     from vgan_b200 import _lib
-    L = _lib.layout(500, 500, 20, 20, _lib.PREC_BF16)
+    L = _lib.layout(500, 500, 20, 20, 5, _lib.PREC_BF16)
     assert (L.Dp, L.Nxp, L.Nyp) == (64, 512, 512)
     assert L.off_zq % 1024 == 0 and L.total >= L.off_zq + 1024 * 64 * 2
-    L32 = _lib.layout(500, 500, 20, 20, _lib.PREC_FP32)
+    L32 = _lib.layout(500, 500, 20, 20, 5, _lib.PREC_FP32)
     assert L32.off_nrm == L.off_nrm and L32.off_stats == L.off_stats and L32.off_zf == L.off_zq
+    # one all-reduce serves [S_xx, S_xy, S_yy, - | colsum]: the column sums sit directly behind the four sums, and
+    # everything vgan_b200_stats zeroes is one contiguous block
+    assert L.off_colsum == L.off_sums + 32 and L.off_acc == L.off_sums
+    assert L.off_acc + L.acc_bytes == L.off_misc + 64 and L.off_stats > L.off_colsum and L.off_cmax > L.off_stats
+    wide = _lib.layout(4096, 4096, 784, 784, 5, _lib.PREC_BF16 | _lib.LADDER)
+    assert wide.Dp == 896 and wide.off_zq - wide.off_xchg == 256 * 128 * 1024
     with pytest.raises(RuntimeError):
-        _lib.layout(0, 1, 1, 0, 0)
+        _lib.layout(0, 1, 1, 0, 5, 0)
+    with pytest.raises(RuntimeError):
+        _lib.layout(8, 8, 4, 0, 3, _lib.LADDER)          # the squaring ladder needs exactly 5 scales
 
 
 def test_no_cpu_fallback():
