@@ -106,6 +106,8 @@ VGAN_B200_API int vgan_b200_destroy(vgan_b200_ctx* ctx);
  * many as the device holds).  The work is cut evenly over however many run; results do not depend on the limit
  * beyond the order of fp32 additions on rows shared by two clusters. */
 VGAN_B200_API int vgan_b200_set_cluster_limit(vgan_b200_ctx* ctx, int max_clusters);
+/* Number of kernels this library has launched through `ctx` so far (host counter, incremented at every launch). */
+VGAN_B200_API int vgan_b200_launch_count(vgan_b200_ctx* ctx, unsigned long long* out);
 
 /* Fills *out.  D_u = columns of U (0: no penalty term), n_scales = number of bandwidth multipliers. */
 VGAN_B200_API int vgan_b200_workspace_layout(int64_t Nx, int64_t Ny, int64_t D, int64_t D_u, int n_scales, int flags,
@@ -148,11 +150,14 @@ VGAN_B200_API int vgan_b200_pack(vgan_b200_ctx* ctx, const vgan_b200_layout_t* L
  *                 dL/dU = dL/dY * X directly) for i in [row_begin,row_end); row stride D.  NULL skips the gradient
  *                 GEMM (forward only).  The column sums of the rows written are added to off_colsum.
  *   dX (NEED_DX): dL/dx_i for the same row range of X.
+ *   X, U, Y: the inputs again (the same pointers as in steps 1 and 3; may be NULL when dY is NULL): the gradient's
+ *                 -rowsum(P) z_i term takes z_i from the fp32 inputs, not from the rounded operand.
  * row_begin must be a multiple of 128 (row_end need not be).  Multi-GPU: all-reduce(sum) the 4 + Dp doubles at
  * off_sums before step 5. */
-VGAN_B200_API int vgan_b200_mmd2_fwd_bwd(vgan_b200_ctx* ctx, const vgan_b200_layout_t* L, void* ws, int64_t row_begin,
-                                         int64_t row_end, int xx_part, int xx_nparts, float* dY, const float* dY_mul,
-                                         float* dX, void* stream);
+VGAN_B200_API int vgan_b200_mmd2_fwd_bwd(vgan_b200_ctx* ctx, const vgan_b200_layout_t* L, void* ws, const float* X,
+                                         const float* U, const float* Y, int64_t row_begin, int64_t row_end,
+                                         int xx_part, int xx_nparts, float* dY, const float* dY_mul, float* dX,
+                                         void* stream);
 
 /* 5. loss[0] = S_xx/Nx^2 - 2 S_xy/(Nx Ny) + S_yy/Ny^2 + penalty (device float; also kept at off_misc + 4), and the
  *    penalty's gradient -weight/D_u at (argmax row, d), lowest row on ties (Mmd_loss_constrained.py:50), added to

@@ -91,8 +91,9 @@ def test_kl_detector_encoder_stays_frozen_after_first_generator_phase(monkeypatc
     m1 = _fit(VGAN, None, X, monkeypatch, batch_size=500, epochs=1)     # after the first detector phase
     m7 = _fit(VGAN, None, X, monkeypatch, batch_size=500, epochs=7)     # after the second detector phase
     for a, b in zip(m1.detector.encoder.parameters(), m7.detector.encoder.parameters()):
-        assert torch.allclose(a, b, rtol=1e-4, atol=1e-6)      # equal up to the atomics' summation order in epoch 0
-    assert any(float((a - b).abs().max()) > 1e-4
+        assert float((a - b).abs().max()) <= 2e-6      # equal up to the atomics' summation order in epoch 0
+    # the decoder did train in the second detector phase (two Adadelta steps at lr 0.007: a few 1e-5 per weight)
+    assert any(float((a.detach() - b.detach()).abs().max()) > 1e-5
                for a, b in zip(m1.detector.decoder.parameters(), m7.detector.decoder.parameters()))
 
 

@@ -21,7 +21,7 @@ MAX_SCALES = 8
 
 EXPORTS = [
     "vgan_b200_abi_version", "vgan_b200_last_error", "vgan_b200_create", "vgan_b200_destroy",
-    "vgan_b200_set_cluster_limit", "vgan_b200_workspace_layout", "vgan_b200_stats", "vgan_b200_scales",
+    "vgan_b200_set_cluster_limit", "vgan_b200_launch_count", "vgan_b200_workspace_layout", "vgan_b200_stats", "vgan_b200_scales",
     "vgan_b200_pack", "vgan_b200_mmd2_fwd_bwd", "vgan_b200_finalize", "vgan_b200_mmd2_eval",
     "vgan_b200_upper_softmax", "vgan_b200_upper_softmax_bwd", "vgan_b200_mmd2_matrix",
     "vgan_b200_permutation_scratch_bytes", "vgan_b200_permutation_stats",
@@ -100,11 +100,12 @@ def _declare(L: C.CDLL) -> None:
     L.vgan_b200_create.argtypes = [i, C.POINTER(p)]
     L.vgan_b200_destroy.argtypes = [p]
     L.vgan_b200_set_cluster_limit.argtypes = [p, i]
+    L.vgan_b200_launch_count.argtypes = [p, C.POINTER(C.c_ulonglong)]
     L.vgan_b200_workspace_layout.argtypes = [i64, i64, i64, i64, i, i, LP]
     L.vgan_b200_stats.argtypes = [p, LP, p, p, p, p, i64, i64, p]
     L.vgan_b200_scales.argtypes = [p, LP, p, p, i, C.POINTER(C.c_float), f, p]
     L.vgan_b200_pack.argtypes = [p, LP, p, p, p, p, i64, i64, p]
-    L.vgan_b200_mmd2_fwd_bwd.argtypes = [p, LP, p, i64, i64, i, i, p, p, p, p]
+    L.vgan_b200_mmd2_fwd_bwd.argtypes = [p, LP, p, p, p, p, i64, i64, i, i, p, p, p, p]
     L.vgan_b200_finalize.argtypes = [p, LP, p, f, p, i64, i64, i, p, p]
     L.vgan_b200_mmd2_eval.argtypes = [p, C.POINTER(EvalArgs)]
     L.vgan_b200_upper_softmax.argtypes = [p, p, i64, i64, p, p, p, p]
@@ -179,6 +180,13 @@ def ctx(device_index: int, L: C.CDLL | None = None) -> C.c_void_p:
     if c is None:
         c = table[key] = _Ctx(L, int(device_index))
     return c.handle
+
+
+def launch_count(device_index: int) -> int:
+    """Kernels launched so far through the calling thread's context for `device_index`."""
+    n = C.c_ulonglong()
+    check(lib().vgan_b200_launch_count(ctx(device_index), C.byref(n)), "launch_count")
+    return int(n.value)
 
 
 def check(status: int, what: str, L: C.CDLL | None = None) -> None:

@@ -10,6 +10,7 @@
 namespace vg {
 
 static thread_local char g_err[512] = "";
+thread_local unsigned long long* tl_launch_counter = nullptr;
 
 void set_error(const char* fmt, ...) {
   va_list ap;
@@ -42,7 +43,8 @@ struct DeviceGuard {
   if (!guard_.ok) {                                                                     \
     set_error("cannot make device %d current", (ctx)->device);                          \
     return VGAN_B200_ERR_DEVICE;                                                        \
-  }
+  }                                                                                     \
+  tl_launch_counter = &(ctx)->launches;
 
 int get_tmap_bf16_2d(vgan_b200_ctx* ctx, CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols,
                      uint32_t box_rows) {
@@ -190,8 +192,9 @@ static int ensure_aux(vgan_b200_ctx* ctx) {
 }
 
 // K1 of one shard on the tcgen05 kernels
-static int run_tc(vgan_b200_ctx* ctx, const vgan_b200_layout_t& L, void* ws, int64_t row_begin, int64_t row_end,
-                  int xx_part, int xx_nparts, float* dY, const float* dY_mul, float* dX, cudaStream_t st) {
+static int run_tc(vgan_b200_ctx* ctx, const vgan_b200_layout_t& L, void* ws, const float* X, const float* U,
+                  const float* Y, int64_t row_begin, int64_t row_end, int xx_part, int xx_nparts, float* dY,
+                  const float* dY_mul, float* dX, cudaStream_t st) {
   uint8_t* base = static_cast<uint8_t*>(ws);
   const int flags = L.flags;
   const bool need_dx = (flags & VGAN_B200_NEED_DX) != 0 && dX != nullptr;
@@ -244,7 +247,8 @@ static int run_tc(vgan_b200_ctx* ctx, const vgan_b200_layout_t& L, void* ws, int
   const __nv_bfloat16* zb = split ? p.zq + rows * width : p.zq;
   p.gchunks = split ? 3 * p.kchunks : p.kchunks;
   p.zq_stride = static_cast<int64_t>(width);
-  p.zq_lo = split ? p.zq + 2 * L.Dp : nullptr;
+  p.Xf = X; p.Uf = Y ? nullptr : U; p.Yf = Y;
+  p.mean = reinterpret_cast<const float*>(base + L.off_mean);
   const int ladder = (flags & VGAN_B200_LADDER) ? 1 : 0;
   p.cs = p.nslices < 4 ? p.nslices : 4;
   p.ngroups = (p.nslices + p.cs - 1) / p.cs;
@@ -423,6 +427,15 @@ int vgan_b200_set_cluster_limit(vgan_b200_ctx* ctx, int max_clusters) {
   return VGAN_B200_OK;
 }
 
+int vgan_b200_launch_count(vgan_b200_ctx* ctx, unsigned long long* out) {
+  if (!ctx || !out) {
+    set_error("launch_count: null pointer");
+    return VGAN_B200_ERR_ARG;
+  }
+  *out = ctx->launches;
+  return VGAN_B200_OK;
+}
+
 int vgan_b200_workspace_layout(int64_t Nx, int64_t Ny, int64_t D, int64_t D_u, int n_scales, int flags,
                                vgan_b200_layout_t* out) {
   return fill_layout(Nx, Ny, D, D_u, n_scales, flags, out);
@@ -455,11 +468,13 @@ int vgan_b200_pack(vgan_b200_ctx* ctx, const vgan_b200_layout_t* L, void* ws, co
   return run_pack(*L, ws, X, U, Y, row_begin, row_end, static_cast<cudaStream_t>(stream));
 }
 
-int vgan_b200_mmd2_fwd_bwd(vgan_b200_ctx* ctx, const vgan_b200_layout_t* L, void* ws, int64_t row_begin,
-                           int64_t row_end, int xx_part, int xx_nparts, float* dY, const float* dY_mul, float* dX,
-                           void* stream) {
+int vgan_b200_mmd2_fwd_bwd(vgan_b200_ctx* ctx, const vgan_b200_layout_t* L, void* ws, const float* X, const float* U,
+                           const float* Y, int64_t row_begin, int64_t row_end, int xx_part, int xx_nparts, float* dY,
+                           const float* dY_mul, float* dX, void* stream) {
   VG_ENTER(ctx);
   if (int e = check_call(L, ws, "mmd2_fwd_bwd")) return e;
+  if (dY)
+    if (int e = check_inputs(L, X, U, Y, row_begin, row_end, "mmd2_fwd_bwd")) return e;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (row_begin < 0 || row_begin % kTile || row_end < row_begin || xx_nparts < 1 || xx_part < 0 ||
       xx_part >= xx_nparts) {
@@ -478,7 +493,7 @@ int vgan_b200_mmd2_fwd_bwd(vgan_b200_ctx* ctx, const vgan_b200_layout_t* L, void
   }
   if ((L->flags & VGAN_B200_PREC_MASK) == VGAN_B200_PREC_FP32)
     return launch_simt_from_abi(*L, ws, row_begin, row_end, xx_part, xx_nparts, dY, dY_mul, dX, st);
-  return run_tc(ctx, *L, ws, row_begin, row_end, xx_part, xx_nparts, dY, dY_mul, dX, st);
+  return run_tc(ctx, *L, ws, X, U, Y, row_begin, row_end, xx_part, xx_nparts, dY, dY_mul, dX, st);
 }
 
 int vgan_b200_finalize(vgan_b200_ctx* ctx, const vgan_b200_layout_t* L, void* ws, float weight, float* dU,
@@ -499,7 +514,8 @@ int vgan_b200_mmd2_eval(vgan_b200_ctx* ctx, const vgan_b200_eval_t* a) {
   if (int e = vgan_b200_stats(ctx, L, a->ws, a->X, a->U, a->Y, 0, n_rows, a->stream)) return e;
   if (int e = vgan_b200_scales(ctx, L, a->ws, a->bandwidth, a->frozen, a->mults_host, a->weight, a->stream)) return e;
   if (int e = vgan_b200_pack(ctx, L, a->ws, a->X, a->U, a->Y, 0, n_rows, a->stream)) return e;
-  if (int e = vgan_b200_mmd2_fwd_bwd(ctx, L, a->ws, 0, n_rows, 0, 1, a->dY, a->dY_mul, a->dX, a->stream)) return e;
+  if (int e = vgan_b200_mmd2_fwd_bwd(ctx, L, a->ws, a->X, a->U, a->Y, 0, n_rows, 0, 1, a->dY, a->dY_mul, a->dX, a->stream))
+    return e;
   return vgan_b200_finalize(ctx, L, a->ws, a->weight, a->dU_penalty, 0, L->Nx,
                             (a->dU_penalty != nullptr && a->dU_penalty == a->dY) ? 1 : 0, a->loss, a->stream);
 }

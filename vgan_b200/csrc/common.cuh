@@ -55,9 +55,15 @@ struct TcParams {
   int max_clusters;           // pair kernel: cap on the persistent clusters (0 = none)
   int64_t Nx, Ny, D, Dp;
   int64_t row_begin, row_end; // gradient row range (rows of Y, and of X with NEED_DX)
-  const __nv_bfloat16* zq;    // stacked operand (for the final z_i read), row stride zq_stride
-  const __nv_bfloat16* zq_lo; // split operands: the low halves (z_i = hi + lo), same stride; else nullptr
+  const __nv_bfloat16* zq;    // stacked operand, row stride zq_stride
   int64_t zq_stride;
+  // the UNROUNDED rows for the -rowsum(P) z_i term of the gradient (fp32 inputs, row stride D): z_i = x_i - mean for
+  // X rows, (y_i or u_i * x_i) - mean for Y rows.  Reading z_i in bf16 here was the whole gradient error (1.6e-3 =
+  // the relative L2 error of one bf16-rounded array, profiles/parity_r2_before.json).
+  const float* Xf;
+  const float* Uf;
+  const float* Yf;
+  const float* mean;
   const float* nrms;          // scaled norms
   const float* par;           // parameter block
   const float* cm;            // [2][Dp] common-mode gradient vectors A_x, A_y
@@ -87,6 +93,12 @@ struct TcParams {
   } while (0)
 
 void set_error(const char* fmt, ...);
+// kernels launched through the calling thread's current context (vgan_b200_launch_count): every launcher calls
+// count_launch() after a launch; the entry point that is running points the thread at its context's counter
+extern thread_local unsigned long long* tl_launch_counter;
+inline void count_launch(int n = 1) {
+  if (tl_launch_counter) *tl_launch_counter += static_cast<unsigned long long>(n);
+}
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
@@ -100,6 +112,7 @@ typedef CUresult (*StreamWaitValueFn)(CUstream, CUdeviceptr, cuuint32_t, unsigne
 struct vgan_b200_ctx {
   int device = 0;
   int n_sms = 0;
+  unsigned long long launches = 0;          // kernels launched through this context (vgan_b200_launch_count)
   int cluster_limit = 0;                    // vgan_b200_set_cluster_limit
   int resident_clusters[9] = {0};           // pair kernel: clusters of size i that fit the device (0 = not asked yet)
   vg::EncodeTiledFn encode = nullptr;

@@ -192,7 +192,7 @@ int launch_simt(const SimtParams& p, cudaStream_t st) {
   const int ngrad = (p.gx_end - p.gx_begin) + (p.gy_end - p.gy_begin);
   const int grid = ngrad * p.nslices + p.n_xx_units;
   if (grid <= 0) return VGAN_B200_OK;
-  mmd2_simt_kernel<<<grid, 256, 0, st>>>(p);
+  mmd2_simt_kernel<<<grid, 256, 0, st>>>(p); count_launch();
   VG_CUDA_CHECK(cudaGetLastError());
   return VGAN_B200_OK;
 }
@@ -231,7 +231,7 @@ matrix_kernel(const float* __restrict__ Z, int64_t n, int64_t D, const float* __
 int launch_matrix(const float* Z, int64_t n, int64_t D, const float* inv_scales, int n_scales,
                   float eps, float* K, cudaStream_t st) {
   dim3 grid(static_cast<unsigned>((n + 15) / 16), static_cast<unsigned>((n + 15) / 16));
-  matrix_kernel<<<grid, 256, 0, st>>>(Z, n, D, inv_scales, n_scales, eps, K);
+  matrix_kernel<<<grid, 256, 0, st>>>(Z, n, D, inv_scales, n_scales, eps, K); count_launch();
   VG_CUDA_CHECK(cudaGetLastError());
   return VGAN_B200_OK;
 }

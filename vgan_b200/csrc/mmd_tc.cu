@@ -354,7 +354,7 @@ int launch_tc(const TcParams& p, const CUtensorMap& map, const CUtensorMap& mapB
   if (grid <= 0) return VGAN_B200_OK;
   auto kern = ladder ? mmd2_tc_kernel<true> : mmd2_tc_kernel<false>;
   VG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
-  kern<<<grid, kThreads, kSmemTotal, st>>>(map, mapB, mapV, p);
+  kern<<<grid, kThreads, kSmemTotal, st>>>(map, mapB, mapV, p); count_launch();
   VG_CUDA_CHECK(cudaGetLastError());
   return VGAN_B200_OK;
 }

@@ -659,6 +659,7 @@ int launch_tc_pair(vgan_b200_ctx* ctx, const TcParams& p, const CUtensorMap& map
   cfg.gridDim = dim3(static_cast<unsigned>(n_clusters * 2 * p.cs));
   if (resident_ctas) *resident_ctas = (n_clusters < ncl ? n_clusters : ncl) * 2 * p.cs;
   VG_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, map, map64, mapV64, p));
+  count_launch();
   return VGAN_B200_OK;
 }
 

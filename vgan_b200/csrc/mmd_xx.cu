@@ -281,7 +281,7 @@ int launch_xx(vgan_b200_ctx* ctx, const TcParams& p, const CUtensorMap& map, con
   long long grid = max_ctas > 0 ? max_ctas : n_sms;
   if (grid > total) grid = total;
   if (grid < 1) return VGAN_B200_OK;
-  kern<<<static_cast<unsigned>(grid), kXThreads, kXSmemTotal, st>>>(map, map256, p);
+  kern<<<static_cast<unsigned>(grid), kXThreads, kXSmemTotal, st>>>(map, map256, p); count_launch();
   VG_CUDA_CHECK(cudaGetLastError());
   return VGAN_B200_OK;
 }

@@ -111,7 +111,7 @@ int run_permutation_stats(const float* K, int64_t n, int64_t n1, const uint8_t* 
   VG_CUDA_CHECK(cudaMemsetAsync(tot, 0, 2 * sizeof(double), st));
   const int rows_per_cta = 256 / 32;
   perm_rowstats_kernel<<<static_cast<unsigned>((n + rows_per_cta - 1) / rows_per_cta), 256, 0, st>>>(K, n, rowsum,
-                                                                                                      diag, tot);
+                                                                                                      diag, tot); count_launch();
   VG_CUDA_CHECK(cudaGetLastError());
   const int64_t n2 = n - n1;
   const double a00 = 1.0 / (static_cast<double>(n1) * static_cast<double>(n1 - 1));
@@ -122,7 +122,7 @@ int run_permutation_stats(const float* K, int64_t n, int64_t n1, const uint8_t* 
     VG_CUDA_CHECK(cudaFuncSetAttribute(perm_stat_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        static_cast<int>(smem)));
   perm_stat_kernel<<<static_cast<unsigned>((n_perm + kPermPerCta - 1) / kPermPerCta), kPermThreads, smem, st>>>(
-      K, n, member, n_perm, rowsum, diag, tot, a00, a11, a01, stats);
+      K, n, member, n_perm, rowsum, diag, tot, a00, a11, a01, stats); count_launch();
   VG_CUDA_CHECK(cudaGetLastError());
   return VGAN_B200_OK;
 }

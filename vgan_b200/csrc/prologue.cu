@@ -420,12 +420,14 @@ int run_stats(const vgan_b200_layout_t& L, void* ws, const float* X, const float
   if (rows <= 0) return VGAN_B200_OK;       // an empty shard only takes part in the exchanges
   if (masked_fast(a)) {
     const int rpb = nX >= 32768 ? 64 : 32;
-    colstats_masked_kernel<<<static_cast<unsigned>((nX + rpb - 1) / rpb), 256, 0, st>>>(a, rpb);
+    colstats_masked_kernel<<<static_cast<unsigned>((nX + rpb - 1) / rpb), 256, 0, st>>>(a, rpb); count_launch();
   } else {
     const int rpb = 64;
-    colstats_kernel<<<static_cast<unsigned>((rows + rpb - 1) / rpb), 256, 0, st>>>(a, rpb);
-    if (a.cmax && nX > 0)
+    colstats_kernel<<<static_cast<unsigned>((rows + rpb - 1) / rpb), 256, 0, st>>>(a, rpb); count_launch();
+    if (a.cmax && nX > 0) {
       colmax_kernel<<<static_cast<unsigned>((nX + rpb - 1) / rpb), 256, 0, st>>>(U, rb, rb + nX, L.D_u, rpb, a.cmax);
+      count_launch();
+    }
   }
   VG_CUDA_CHECK(cudaGetLastError());
   return VGAN_B200_OK;
@@ -448,7 +450,7 @@ int run_scales(const vgan_b200_layout_t& L, void* ws, float* bandwidth, int froz
   a.mean = reinterpret_cast<float*>(base + L.off_mean);
   a.cm = reinterpret_cast<float*>(base + L.off_cm);
   a.misc = reinterpret_cast<float*>(base + L.off_misc);
-  scales_kernel<<<1, 256, 0, st>>>(a);
+  scales_kernel<<<1, 256, 0, st>>>(a); count_launch();
   VG_CUDA_CHECK(cudaGetLastError());
   return VGAN_B200_OK;
 }
@@ -460,10 +462,16 @@ int run_pack(const vgan_b200_layout_t& L, void* ws, const float* X, const float*
   const int64_t x0 = rb < L.Nxp ? rb : L.Nxp, x1 = re >= L.Nx ? L.Nxp : (re > x0 ? re : x0);
   const int64_t y0 = rb < L.Nyp ? rb : L.Nyp, y1 = re >= L.Ny ? L.Nyp : (re > y0 ? re : y0);
   if (masked_fast(a)) {
-    if (x1 > x0) pack_masked_kernel<<<static_cast<unsigned>((x1 - x0 + 7) / 8), 256, 0, st>>>(a, x0, x1);
+    if (x1 > x0) {
+      pack_masked_kernel<<<static_cast<unsigned>((x1 - x0 + 7) / 8), 256, 0, st>>>(a, x0, x1);
+      count_launch();
+    }
   } else {
     const int64_t rows = (x1 - x0) + (y1 - y0);
-    if (rows > 0) pack_kernel<<<static_cast<unsigned>((rows + 7) / 8), 256, 0, st>>>(a, x0, x1, y0, y1);
+    if (rows > 0) {
+      pack_kernel<<<static_cast<unsigned>((rows + 7) / 8), 256, 0, st>>>(a, x0, x1, y0, y1);
+      count_launch();
+    }
   }
   VG_CUDA_CHECK(cudaGetLastError());
   return VGAN_B200_OK;
@@ -478,7 +486,7 @@ int run_finalize(const vgan_b200_layout_t& L, void* ws, float weight, float* dU,
       reinterpret_cast<const double*>(base + L.off_sums), static_cast<double>(L.Nx), static_cast<double>(L.Ny),
       pen ? reinterpret_cast<const unsigned long long*>(base + L.off_cmax) : nullptr, L.D_u, weight, dU, row_begin, rows,
       (pen && colsum_penalty) ? reinterpret_cast<double*>(base + L.off_colsum) : nullptr,
-      reinterpret_cast<float*>(base + L.off_misc), loss);
+      reinterpret_cast<float*>(base + L.off_misc), loss); count_launch();
   VG_CUDA_CHECK(cudaGetLastError());
   return VGAN_B200_OK;
 }

@@ -66,7 +66,7 @@ upper_softmax_bwd_kernel(const float* __restrict__ H, const float* __restrict__ 
 int run_upper_softmax(const float* H, int64_t N, int64_t D, float* U, float* row_max, float* row_inv_sum,
                       cudaStream_t st) {
   const float thr = static_cast<float>(1.0 / static_cast<double>(D));
-  upper_softmax_kernel<<<static_cast<unsigned>((N + 7) / 8), 256, 0, st>>>(H, N, D, thr, U, row_max, row_inv_sum);
+  upper_softmax_kernel<<<static_cast<unsigned>((N + 7) / 8), 256, 0, st>>>(H, N, D, thr, U, row_max, row_inv_sum); count_launch();
   VG_CUDA_CHECK(cudaGetLastError());
   return VGAN_B200_OK;
 }
@@ -75,7 +75,7 @@ int run_upper_softmax_bwd(const float* H, const float* row_max, const float* row
                           int64_t D, float* dH, cudaStream_t st) {
   const float thr = static_cast<float>(1.0 / static_cast<double>(D));
   upper_softmax_bwd_kernel<<<static_cast<unsigned>((N + 7) / 8), 256, 0, st>>>(H, row_max, row_inv_sum, dU, N, D, thr,
-                                                                             dH);
+                                                                             dH); count_launch();
   VG_CUDA_CHECK(cudaGetLastError());
   return VGAN_B200_OK;
 }

@@ -84,10 +84,10 @@ int run_subspace_dist(const void* U, int in_is_bool, int64_t n, int64_t D, float
   int* first = reinterpret_cast<int*>(packed + n * W);
   int* cnt = first + n;
   VG_CUDA_CHECK(cudaMemsetAsync(n_unique, 0, sizeof(int), st));
-  subspace_pack_kernel<<<static_cast<unsigned>(n), 64, 0, st>>>(U, in_is_bool, n, D, thr, W, packed);
-  subspace_count_kernel<<<static_cast<unsigned>(n), 128, 0, st>>>(packed, n, W, first, cnt);
+  subspace_pack_kernel<<<static_cast<unsigned>(n), 64, 0, st>>>(U, in_is_bool, n, D, thr, W, packed); count_launch();
+  subspace_count_kernel<<<static_cast<unsigned>(n), 128, 0, st>>>(packed, n, W, first, cnt); count_launch();
   subspace_scatter_kernel<<<static_cast<unsigned>(n), 128, 0, st>>>(packed, n, D, W, first, cnt, unique_out,
-                                                                    counts_out, n_unique);
+                                                                    counts_out, n_unique); count_launch();
   VG_CUDA_CHECK(cudaGetLastError());
   return VGAN_B200_OK;
 }

@@ -136,9 +136,14 @@ __device__ __forceinline__ void write_grad_rows(const TcParams& p, uint32_t tmem
   const float ci4 = 4.f * (row_is_x ? 1.f / static_cast<float>(p.Nx) : -1.f / static_cast<float>(p.Ny));
   float* out = (row_is_x ? p.dX : p.dY) + (region_row - p.row_begin) * p.D;
   const float* mul = (!row_is_x && p.dY_mul) ? p.dY_mul + (region_row - p.row_begin) * p.D : nullptr;
-  const int64_t zoff = (static_cast<int64_t>(ti) * kTile + row) * p.zq_stride;
-  const __nv_bfloat16* zrow = p.zq + zoff;
-  const __nv_bfloat16* zrow_lo = p.zq_lo ? p.zq_lo + zoff : nullptr;
+  // unrounded z_i = input row - centring mean (rows outside the range are never dereferenced: the callers of a
+  // multi-GPU job pass pointers that are only valid for their own rows)
+  const float* xrow = p.Xf + region_row * p.D;
+  const float* yrow = p.Yf ? p.Yf + region_row * p.D : nullptr;
+  const float* urow = p.Uf ? p.Uf + region_row * p.D : nullptr;
+  const bool zvec = (p.D & 3) == 0 && (reinterpret_cast<uintptr_t>(p.Xf) & 15) == 0 &&
+                    (!p.Yf || (reinterpret_cast<uintptr_t>(p.Yf) & 15) == 0) &&
+                    (!p.Uf || (reinterpret_cast<uintptr_t>(p.Uf) & 15) == 0);
   if (p.pass_flags & kPassNoRowsum) rtot = 0.f;
   const bool cmode = first_range && !(p.pass_flags & kPassNoRowsum);
   if (cmode) rtot += p.par[kParB + (row_is_x ? 0 : 1)];
@@ -157,15 +162,37 @@ __device__ __forceinline__ void write_grad_rows(const TcParams& p, uint32_t tmem
 #pragma unroll
     for (int e = 0; e < 32; ++e) cs[e] = 0.f;
     if (row_ok) {
-      const uint4* z4 = reinterpret_cast<const uint4*>(zrow + f_slice + col);
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
-        const uint4 zz = z4[c];
-        const uint32_t zw[4] = {zz.x, zz.y, zz.z, zz.w};
-        uint4 zl = make_uint4(0u, 0u, 0u, 0u);
-        if (zrow_lo) zl = reinterpret_cast<const uint4*>(zrow_lo + f_slice + col)[c];
-        const uint32_t zlw[4] = {zl.x, zl.y, zl.z, zl.w};
         const int f0 = f_slice + col + c * 8;
+        float zv[8];
+        if (zvec && f0 + 8 <= p.D) {
+          float4 a0, a1;
+          if (row_is_x) {
+            a0 = *reinterpret_cast<const float4*>(xrow + f0); a1 = *reinterpret_cast<const float4*>(xrow + f0 + 4);
+          } else if (yrow) {
+            a0 = *reinterpret_cast<const float4*>(yrow + f0); a1 = *reinterpret_cast<const float4*>(yrow + f0 + 4);
+          } else {
+            const float4 x0 = *reinterpret_cast<const float4*>(xrow + f0), x1 = *reinterpret_cast<const float4*>(xrow + f0 + 4);
+            const float4 u0 = *reinterpret_cast<const float4*>(urow + f0), u1 = *reinterpret_cast<const float4*>(urow + f0 + 4);
+            a0 = make_float4(u0.x * x0.x, u0.y * x0.y, u0.z * x0.z, u0.w * x0.w);
+            a1 = make_float4(u1.x * x1.x, u1.y * x1.y, u1.z * x1.z, u1.w * x1.w);
+          }
+          const float4 m0 = *reinterpret_cast<const float4*>(p.mean + f0), m1 = *reinterpret_cast<const float4*>(p.mean + f0 + 4);
+          zv[0] = a0.x - m0.x; zv[1] = a0.y - m0.y; zv[2] = a0.z - m0.z; zv[3] = a0.w - m0.w;
+          zv[4] = a1.x - m1.x; zv[5] = a1.y - m1.y; zv[6] = a1.z - m1.z; zv[7] = a1.w - m1.w;
+        } else {
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            const int f = f0 + e;
+            float raw = 0.f, mu = 0.f;
+            if (f < p.D) {
+              raw = row_is_x ? xrow[f] : (yrow ? yrow[f] : urow[f] * xrow[f]);
+              mu = p.mean[f];
+            }
+            zv[e] = raw - mu;
+          }
+        }
         float av[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
         if (cmode) {
           const float4 a0 = *reinterpret_cast<const float4*>(cmv + f0), a1 = *reinterpret_cast<const float4*>(cmv + f0 + 4);
@@ -174,9 +201,7 @@ __device__ __forceinline__ void write_grad_rows(const TcParams& p, uint32_t tmem
         float gv[8];
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
-          const float z = __uint_as_float((e & 1) ? (zw[e >> 1] & 0xffff0000u) : (zw[e >> 1] << 16)) +
-                          __uint_as_float((e & 1) ? (zlw[e >> 1] & 0xffff0000u) : (zlw[e >> 1] << 16));
-          gv[e] = ci4 * ((__uint_as_float(v[c * 8 + e]) + av[e]) - rtot * z);
+          gv[e] = ci4 * ((__uint_as_float(v[c * 8 + e]) + av[e]) - rtot * zv[e]);
         }
         if (vec_ok && f0 + 8 <= p.D) {
           // 16-byte accesses (rows are 16-byte aligned when D % 4 == 0)

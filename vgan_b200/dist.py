@@ -104,7 +104,7 @@ def sharded_masked_step(loss_fn, X, U, rank: int = 0, world: int = 1, group=None
         _lib.check(L.vgan_b200_pack(ctx, lay, ws.ptr, _ptr(X), _ptr(U), None, 0, N, st), "pack")
         if ev:
             ev[0].record()
-        _lib.check(L.vgan_b200_mmd2_fwd_bwd(ctx, lay, ws.ptr, b, e, rank, world, _ptr(dU),
+        _lib.check(L.vgan_b200_mmd2_fwd_bwd(ctx, lay, ws.ptr, _ptr(X), _ptr(U), None, b, e, rank, world, _ptr(dU),
                                             _ptr(X[b:]) if dU is not None else None, None, st), "mmd2_fwd_bwd")
         if ev:
             ev[1].record()
@@ -157,8 +157,8 @@ def data_parallel_masked_step(loss_fn, X_local, U_local, group=None, time_k1: bo
         gather_rows(ws.norms[N:], rank, world, group)
         if ev:
             ev[0].record()
-        _lib.check(L.vgan_b200_mmd2_fwd_bwd(ctx, lay, ws.ptr, b, e, rank, world, _ptr(dU), _ptr(X_local), None, st),
-                   "mmd2_fwd_bwd")
+        _lib.check(L.vgan_b200_mmd2_fwd_bwd(ctx, lay, ws.ptr, Xv, Uv, None, b, e, rank, world, _ptr(dU), _ptr(X_local),
+                                            None, st), "mmd2_fwd_bwd")
         if ev:
             ev[1].record()
         reduce_results(ws.reduced, group)

@@ -183,8 +183,8 @@ def mmd2_eval(X: torch.Tensor, Y: Optional[torch.Tensor], U: Optional[torch.Tens
             _lib.check(L.vgan_b200_pack(ctx, lay, ws.ptr, _ptr(X), Up, Yp, 0, n_all, st), "pack")
             if k1_events is not None:
                 k1_events[0].record()
-            _lib.check(L.vgan_b200_mmd2_fwd_bwd(ctx, lay, ws.ptr, row_begin, row_end, xx_part, xx_nparts, _ptr(dY),
-                                                _ptr(mul), _ptr(dX), st), "mmd2_fwd_bwd")
+            _lib.check(L.vgan_b200_mmd2_fwd_bwd(ctx, lay, ws.ptr, _ptr(X), Up, Yp, row_begin, row_end, xx_part, xx_nparts,
+                                                _ptr(dY), _ptr(mul), _ptr(dX), st), "mmd2_fwd_bwd")
             if k1_events is not None:
                 k1_events[1].record()
             rb = row_begin if masked else 0
