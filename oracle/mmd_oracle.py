@@ -260,7 +260,7 @@ def permutation_pval(K, n1: int, n2: int, perms: np.ndarray) -> float:
 # --------------------------------------------------------------------------------------
 
 def cpu_blockwise_fwd_bwd(X: torch.Tensor, U: torch.Tensor, bandwidth: float,
-                          row_begin: int, row_end: int, block: int = 2048):
+                          row_begin: int, row_end: int, block: int = 2048, weight: float = 0.0):
     """fp32 blockwise port of one masked fwd+bwd evaluation restricted to gradient rows
     [row_begin, row_end) of Y (and the matching 1/share of the S_xx block), so a bounded
     SAMPLE of the N=65536 workload can be timed on host cores.  Same math as
@@ -301,6 +301,14 @@ def cpu_blockwise_fwd_bwd(X: torch.Tensor, U: torch.Tensor, bandwidth: float,
                 k += torch.exp(d2 * (-1.0 / sm))
             sums[0] += float(k.sum())
         dU[i0 - row_begin:i1 - row_begin] = 4.0 * cy * (O - r[:, None] * Yi) * Xi
+    if weight != 0:
+        # weight * mean_d(1 - max_i U[i,d]) and its gradient (Mmd_loss_constrained.py:50), over the whole mask
+        top = torch.topk(U.float(), 1, dim=0)
+        sums.append(float(weight) * float((1.0 - top.values).mean()))
+        rows = top.indices.reshape(-1)
+        inside = (rows >= row_begin) & (rows < row_end)
+        cols = torch.arange(U.shape[1])[inside]
+        dU[rows[inside] - row_begin, cols] -= float(weight) / U.shape[1]
     return sums, dU
 
 
