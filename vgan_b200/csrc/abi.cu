@@ -138,7 +138,7 @@ static int fill_layout(int64_t Nx, int64_t Ny, int64_t D, int64_t D_u, int n_sca
   L->off_nrm = off;    off = align_up(off + rows * 4, 1024);
   L->off_nrms = off;   off = align_up(off + rows * 4, 1024);
   L->off_xchg = off;
-  if (!fp32 && L->Dp > kSliceMax) off = align_up(off + static_cast<size_t>(kXchgSms) * kXchgBytesPerSm, 1024);
+  if (!fp32 && L->Dp > kSliceMax) off = align_up(off + kXchgTotalBytes, 1024);
   L->off_zq = off;
   const bool split = !fp32 && (flags & VGAN_B200_BF16X3);
   L->off_zf = off;     off = align_up(off + rows * L->Dp * (fp32 ? 4 : (split ? 12 : 2)), 1024);
@@ -278,7 +278,10 @@ static int run_tc(vgan_b200_ctx* ctx, const vgan_b200_layout_t& L, void* ws, con
 #ifdef VGAN_B200_DEBUG
     xx_mode = ctx->xx_mode;             // 1: serial, 2: S_xx kernel dispatched first (measurement)
 #endif
-    const bool overlap = p.n_xx_units > 0 && xx_mode != 1;
+    // the S_xx kernel runs BESIDE the gradient kernel only when that leaves it SMs (cluster limit set, or fewer units
+    // than the device holds pairs); otherwise behind it on the same stream
+    const int pair_ctas = pair_grid_ctas(ctx, p, ladder);
+    const bool overlap = p.n_xx_units > 0 && xx_mode != 1 && pair_ctas > 0 && ctx->n_sms - pair_ctas >= kXxMinFreeSms;
     if (overlap)
       if (int e = ensure_aux(ctx)) return e;
     cudaStream_t main_st = st;

@@ -195,6 +195,34 @@ __device__ __forceinline__ void bulk_load_multicast(uint32_t dst_addr, const voi
       ::"r"(dst_addr), "l"(reinterpret_cast<uint64_t>(gsrc)), "r"(bytes), "r"(bar_addr), "h"(cta_mask)
       : "memory");
 }
+// ------------------------------------------------------------------ flags in global memory (CTA <-> CTA through L2)
+__device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_gpu(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void red_release_gpu_add(uint32_t* p, uint32_t v) {
+  asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+// orders generic-proxy accesses (flags) against async-proxy ones (bulk copies) on global and shared memory
+__device__ __forceinline__ void fence_proxy_async_all() {
+  asm volatile("fence.proxy.async;" ::: "memory");
+}
+// bounded spin until *p >= target (monotonic counters): a protocol bug traps instead of hanging the box
+__device__ __forceinline__ void spin_until_ge(const uint32_t* p, uint32_t target) {
+  uint32_t spins = 0;
+  while (static_cast<int32_t>(ld_acquire_gpu(p) - target) < 0) {
+    __nanosleep(32);
+    if (++spins > (1u << 26)) {
+      printf("vgan_b200: flag timeout block %d thread %d target %u have %u\n", blockIdx.x, threadIdx.x, target,
+             ld_acquire_gpu(p));
+      __trap();
+    }
+  }
+}
 __device__ __forceinline__ unsigned long long global_timer_ns() {
   unsigned long long t;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
