@@ -43,6 +43,14 @@
 #define VG_CLK() 0ll
 #endif
 
+// progress markers (debug build, p.dbg in host-mapped memory): role `w` of this CTA has reached `v`
+#ifdef VGAN_B200_DEBUG
+#define VG_MARK(w, v) do { if (p.dbg && (threadIdx.x & 31) == 0) { \
+  reinterpret_cast<volatile float*>(p.dbg)[static_cast<int64_t>(blockIdx.x) * p.dbg_stride + 16 + (w)] = static_cast<float>(v); } } while (0)
+#else
+#define VG_MARK(w, v) do { } while (0)
+#endif
+
 namespace vg {
 
 constexpr int kGStagesMax = 4;                     // barrier slots of the Gram operand ring
@@ -82,7 +90,7 @@ struct __align__(8) PairBarriers {
   uint64_t v_full[kVStages], v_empty[kVStages];
   uint64_t s_full[2], s_empty[2];
   uint64_t nj_full[2], nj_empty[2];
-  uint64_t p_full[kQSlotsMax], p_pair[kQSlotsMax], pub_full[kQSlotsMax], own_free[kQSlotsMax];
+  uint64_t p_full[kQSlotsMax], p_pair[kQSlotsMax], pub_full[kQSlotsMax], own_free[kQSlotsMax], rem_free[kQSlotsMax];
   uint64_t o_full;
   uint32_t tmem_base;
   float red[8][4];
@@ -207,6 +215,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
       mbar_init(&bar->p_pair[s], 1);
       mbar_init(&bar->pub_full[s], 1);
       mbar_init(&bar->own_free[s], 1);
+      mbar_init(&bar->rem_free[s], 1);
     }
     mbar_init(&bar->o_full, 1);
     fence_barrier_init();
@@ -230,9 +239,10 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
   // ---- pipeline state that persists across the work ranges of this CTA (each warp uses its role's part)
   uint32_t rs = 0, rph = 0;            // ring stage / phase: G ring (warps 8, 11, 9), V ring (warps 12, 10)
   uint32_t kg = 0;                     // Gram tiles of this CTA so far: S / norm buffer kg & 1, parity (kg >> 1) & 1
-  uint32_t pf_mask = 0, pub_mask = 0;  // per-slot phase parities of p_full / pub_full (roles that wait for every phase)
-  uint32_t pf_base[kQSlotsMax] = {0, 0, 0, 0}, of_base[kQSlotsMax] = {0, 0, 0, 0};   // completed phases of p_full /
-                                       // own_free before this range (roles that wait for SOME phases: by index)
+  uint32_t pf_mask = 0, pub_mask = 0, of_mask = 0, rf_mask = 0;   // per-slot phase parities of p_full / pub_full /
+                                       // own_free / rem_free, toggled by roles that wait for EVERY phase of the barrier
+  uint32_t pf_base[kQSlotsMax] = {0, 0, 0, 0};   // completed phases of p_full before this range (the fetcher waits for
+                                       // the phases it armed itself: by index)
   uint32_t seq_base = 0;               // tiles every CTA of the group has published before this range
   uint32_t part = 0;                   // ranges done: parity of o_full, group barrier count, row-sum buffer
   long long tm0 = 0, tm1 = 0, tm2 = 0, tm3 = 0;      // debug timers (meaning depends on the role)
@@ -240,13 +250,10 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
   unsigned long long gt_begin;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt_begin));
   long long tm_tail = 0;
-  // phases of own_free[slot] / p_full[slot] a range of TTp tiles adds (both are completed once per tile of the slot;
-  // own_free only for tiles whose slot is used again inside the range)
+  // phases of p_full[slot] a range of TTp tiles adds (completed once per tile of the slot)
 #define VG_PAIR_ADVANCE_BASES \
-    _Pragma("unroll") for (int s_ = 0; s_ < kQSlots; ++s_) { \
+    _Pragma("unroll") for (int s_ = 0; s_ < kQSlots; ++s_) \
       pf_base[s_] += static_cast<uint32_t>((TTp - s_ + kQSlots - 1) / kQSlots); \
-      of_base[s_] += static_cast<uint32_t>(max(0, (TTp - kQSlots - s_ + kQSlots - 1) / kQSlots)); \
-    } \
     seq_base += static_cast<uint32_t>(Kp)
 
   if (warp >= 8) {
@@ -326,8 +333,10 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     for (int k = 0; k < Kp; ++k) {
       const int t = CS * k + c;
       const int slot = t % kQSlots;
+      VG_MARK(13, 100 + t);
       mbar_wait(&bar->pub_full[slot], (pub_mask >> slot) & 1);
       pub_mask ^= 1u << slot;
+      VG_MARK(13, 200 + t);
       if (lane == 0 && CS > 1) {
         const uint32_t q = seq_base + static_cast<uint32_t>(k);
         if (q >= static_cast<uint32_t>(kRing))
@@ -338,11 +347,12 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
         fence_proxy_async_all();
         st_release_gpu(my_ready, q + 1);
       }
+      VG_MARK(13, 300 + t);
       __syncwarp();
     }
   } else if (warp == 15) {
     // ===================== fetcher: the other pairs' P tiles of MY row tile, ring -> shared-memory slot ==========
-    // In tile order.  A slot is free once this pair's PV of the tile that used it before has completed (own_free,
+    // In tile order.  A slot is free once this pair's PV of the tile that used it before has completed (rem_free,
     // committed to both CTAs of the pair); the tile is there once its writer's ready count says so; the writer gets
     // the acknowledgement (fetched) when the load has landed.
     if (lane == 0 && CS > 1) {
@@ -350,10 +360,16 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
         const int d = t % CS;
         if (d == c) continue;
         const int slot = t % kQSlots;
-        if (t >= kQSlots) mbar_wait(&bar->own_free[slot], (of_base[slot] + static_cast<uint32_t>(t / kQSlots) - 1u) & 1u);
+        VG_MARK(15, 100 + t);
+        if (t >= kQSlots) {       // this pair finished PV(t - kQSlots): rem_free completes once per tile this warp fills
+          mbar_wait(&bar->rem_free[slot], (rf_mask >> slot) & 1);
+          rf_mask ^= 1u << slot;
+        }
         const int wblk = blk_of_pair0 + 2 * d + hh;   // the writer: pair d of this group, same row tile
         const uint32_t q = seq_base + static_cast<uint32_t>(t / CS);
+        VG_MARK(15, 200 + t);
         spin_until_ge(flag_ready + wblk, q + 1);
+        VG_MARK(15, 300 + t);
         fence_proxy_async_all();
         mbar_arrive_expect_tx(&bar->p_full[slot], pbytes);
         bulk_load_1d(smem + kQSmemP + slot * kQPBytes,
@@ -363,6 +379,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
         // next tile may be an own one, parked without this warp's help)
         mbar_wait(&bar->p_full[slot], (pf_base[slot] + static_cast<uint32_t>(t / kQSlots)) & 1u);
         red_release_gpu_add(flag_fetched + wblk, 1u);
+        VG_MARK(15, 400 + t);
       }
     }
     __syncwarp();
@@ -430,8 +447,11 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
       const int slot = t % kQSlots;
       {
         const long long t0 = VG_CLK();
+        VG_MARK(10, 100 + t);
         mbar_wait(&bar->p_full[slot], (pf_mask >> slot) & 1);   // my P(I0, t)
+        VG_MARK(10, 200 + t);
         mbar_wait(&bar->p_pair[slot], (pf_mask >> slot) & 1);   // the peer's P(I1, t)
+        VG_MARK(10, 300 + t);
         tm2 += VG_CLK() - t0;
       }
       pf_mask ^= 1u << slot;
@@ -461,8 +481,11 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
         }
       }
       // both CTAs of the pair are done with the slot once this PV has completed: whoever fills it with tile
-      // t + kQSlots (the epilogue for an own tile, the fetcher for another pair's) waits for this
-      if (t + kQSlots < TTp && elect_one()) umma_commit_2cta_mc(&bar->own_free[slot], pair_mask);
+      // t + kQSlots waits for this — the epilogue for an own tile (own_free), the fetcher for another pair's
+      // (rem_free).  Two barriers, so that each waiter sees EVERY phase of its barrier (a parity wait cannot tell
+      // phases two apart)
+      if (t + kQSlots < TTp && elect_one())
+        umma_commit_2cta_mc((t + kQSlots) % CS == c ? &bar->own_free[slot] : &bar->rem_free[slot], pair_mask);
       __syncwarp();
     }
     if (elect_one()) umma_commit_2cta_mc(&bar->o_full, pair_mask);
@@ -536,8 +559,11 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
       long long tq = VG_CLK();
       const int t = CS * k + c;                          // tile index within the range (slot protocol)
       const int slot = t % kQSlots;
-      if (t >= kQSlots)    // this pair finished PV(t - kQSlots): phase index = completions before the range + t / slots - 1
-        mbar_wait(&bar->own_free[slot], (of_base[slot] + static_cast<uint32_t>(t / kQSlots) - 1u) & 1u);
+      VG_MARK(warp, 100 + t);
+      if (t >= kQSlots) {
+        mbar_wait(&bar->own_free[slot], (of_mask >> slot) & 1);    // this pair finished PV(t - kQSlots)
+        of_mask ^= 1u << slot;
+      }
       tm2 += VG_CLK() - tq; tq = VG_CLK();
       uint8_t* p_slot = smem + kQSmemP + slot * kQPBytes;
       uint8_t* p_row = p_slot + g * kChunkBytes + row * 128;
@@ -550,6 +576,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
         mbar_arrive(&bar->p_full[slot]);     // own PV warp / forwarder
         mbar_arrive(&bar->pub_full[slot]);   // publisher warp
       }
+      VG_MARK(warp, 200 + t);
       tm3 += VG_CLK() - tq;
     };
     {
@@ -592,6 +619,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     // tiles: written to global memory, one arrival per CTA on the (group, hh) counter, then all CS parts are read back.
     // Two buffers alternate with the range parity: a CTA can only be one range ahead of the slowest reader.
     const long long tq_tail = VG_CLK();
+    VG_MARK(warp, 900);
     asm volatile("bar.sync 1, 256;" ::: "memory");     // both column halves of the row sums are in nj_smem
     float* rs_mine = rs_global + (static_cast<size_t>(part & 1u) * kXchgSms + blockIdx.x) * kTile;
     if (warp < 4) {
@@ -617,9 +645,11 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
         write_grad_rows(p, tmem_o, static_cast<uint32_t>(q * 32) << 16, g, row, ti, row_is_x, slice, slice_chunks,
                         rtot, partial, r0 == 0);
     }
+    VG_MARK(warp, 950);
     VG_PAIR_ADVANCE_BASES;
     tc_fence_before();
     cluster_sync_all();      // pair-wide: O, the norm buffers and the P slots may be reused by the next range
+    VG_MARK(warp, 999);
     tm_tail += VG_CLK() - tq_tail;
     }
   }

@@ -55,13 +55,18 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 #ifndef VG_SPIN_LIMIT
 #define VG_SPIN_LIMIT (1u << 28)
 #endif
+// (debug build, -DVG_SPIN_REPORT: report and carry on, so that the kernel ends and the messages reach the host)
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
     if (++spins > VG_SPIN_LIMIT) {
       printf("vgan_b200: mbarrier timeout block %d thread %d bar %u parity %u\n", blockIdx.x,
              threadIdx.x, smem_u32(bar), parity);
+#ifdef VG_SPIN_REPORT
+      return;
+#else
       __trap();
+#endif
     }
   }
 }
@@ -216,10 +221,14 @@ __device__ __forceinline__ void spin_until_ge(const uint32_t* p, uint32_t target
   uint32_t spins = 0;
   while (static_cast<int32_t>(ld_acquire_gpu(p) - target) < 0) {
     __nanosleep(32);
-    if (++spins > (1u << 26)) {
+    if (++spins > (VG_SPIN_LIMIT >> 2)) {
       printf("vgan_b200: flag timeout block %d thread %d target %u have %u\n", blockIdx.x, threadIdx.x, target,
              ld_acquire_gpu(p));
+#ifdef VG_SPIN_REPORT
+      return;
+#else
       __trap();
+#endif
     }
   }
 }
