@@ -165,3 +165,33 @@ def test_graph_replay_wide_data_uses_cluster_kernels(monkeypatch, capsys):
     eager = _fit(VGAN_no_kl, None, X, monkeypatch, **kw)
     a, b = np.array(graphed.train_history["generator_loss"]), np.array(eager.train_history["generator_loss"])
     np.testing.assert_allclose(a, b, rtol=1e-4, atol=1e-6)
+
+
+def test_no_kl_fit_within_reference_band(monkeypatch, capsys):
+    """vgan_b200.VGAN_no_kl.fit against the band spanned by the REFERENCE's own loop (tests/golden/fit_no_kl.npz, made by
+    oracle/make_fit_fixtures.py from /root/reference/src/vgan.py:546-637 on CPU for five seeds).  Bit equality is
+    impossible (the reference draws batches from its DataLoader's RNG and noise from the CPU generator, this build from
+    device generators), and the reference itself is strongly seed dependent — the epoch loss is dominated by the
+    penalty, 10 x the fraction of features no sampled mask selects, in steps of 0.24 — so what is held is: every epoch
+    loss inside the reference band (+- one penalty step), the seed-averaged loss level and the seed-averaged number of
+    selected features close to the reference's, and the same frozen bandwidth per seed (it depends on the first batch
+    only through which rows it holds: a few per cent)."""
+    import os
+    from vgan_b200 import VGAN_no_kl
+    from oracle.make_fit_fixtures import BATCH, EPOCHS, LR, SEEDS, fit_data
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "fit_no_kl.npz"))
+    X = fit_data()
+    losses, nsel, bws = [], [], []
+    for seed in SEEDS:
+        m = _fit(VGAN_no_kl, None, X, monkeypatch, batch_size=BATCH, epochs=EPOCHS, lr=LR, seed=int(seed))
+        losses.append(np.array(m.train_history["generator_loss"]))
+        nsel.append(float(m.generate_subspaces(500).float().sum(1).mean()))
+        bws.append(float(m.bandwidth))
+    L = np.stack(losses)
+    lo, hi = g["loss"].min(0), g["loss"].max(0)
+    step = 0.25
+    assert (L >= lo[None, :] - step).all() and (L <= hi[None, :] + step).all(), (L.min(), L.max(), lo.min(), hi.max())
+    assert abs(L.mean() - g["loss"].mean()) <= 0.8, (L.mean(), g["loss"].mean())
+    ref_nsel = float(g["freq"].sum(1).mean())
+    assert abs(np.mean(nsel) - ref_nsel) <= 3.0, (nsel, ref_nsel)
+    assert np.abs(np.array(bws) / g["bandwidth"].mean() - 1.0).max() <= 0.1, (bws, g["bandwidth"])

@@ -241,8 +241,6 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
   uint32_t kg = 0;                     // Gram tiles of this CTA so far: S / norm buffer kg & 1, parity (kg >> 1) & 1
   uint32_t pf_mask = 0, pub_mask = 0, of_mask = 0, rf_mask = 0;   // per-slot phase parities of p_full / pub_full /
                                        // own_free / rem_free, toggled by roles that wait for EVERY phase of the barrier
-  uint32_t pf_base[kQSlotsMax] = {0, 0, 0, 0};   // completed phases of p_full before this range (the fetcher waits for
-                                       // the phases it armed itself: by index)
   uint32_t seq_base = 0;               // tiles every CTA of the group has published before this range
   uint32_t part = 0;                   // ranges done: parity of o_full, group barrier count, row-sum buffer
   long long tm0 = 0, tm1 = 0, tm2 = 0, tm3 = 0;      // debug timers (meaning depends on the role)
@@ -250,11 +248,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
   unsigned long long gt_begin;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt_begin));
   long long tm_tail = 0;
-  // phases of p_full[slot] a range of TTp tiles adds (completed once per tile of the slot)
-#define VG_PAIR_ADVANCE_BASES \
-    _Pragma("unroll") for (int s_ = 0; s_ < kQSlots; ++s_) \
-      pf_base[s_] += static_cast<uint32_t>((TTp - s_ + kQSlots - 1) / kQSlots); \
-    seq_base += static_cast<uint32_t>(Kp)
+#define VG_PAIR_ADVANCE_BASES seq_base += static_cast<uint32_t>(Kp)
 
   if (warp >= 8) {
     // ===================== service warps (TMA, MMA issue, P exchange): few registers =====================
@@ -353,8 +347,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
   } else if (warp == 15) {
     // ===================== fetcher: the other pairs' P tiles of MY row tile, ring -> shared-memory slot ==========
     // In tile order.  A slot is free once this pair's PV of the tile that used it before has completed (rem_free,
-    // committed to both CTAs of the pair); the tile is there once its writer's ready count says so; the writer gets
-    // the acknowledgement (fetched) when the load has landed.
+    // committed to both CTAs of the pair); the tile is there once its writer's ready count says so.
     if (lane == 0 && CS > 1) {
       for (int t = 0; t < TTp; ++t) {
         const int d = t % CS;
@@ -375,10 +368,8 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
         bulk_load_1d(smem + kQSmemP + slot * kQPBytes,
                      p.xchg + static_cast<size_t>(wblk) * kXchgBytesPerSm + (q % kRing) * kQPBytes, pbytes,
                      &bar->p_full[slot]);
-        // acknowledged as soon as the bytes are here (waiting later could fall two phases behind the barrier: the slot's
-        // next tile may be an own one, parked without this warp's help)
-        mbar_wait(&bar->p_full[slot], (pf_base[slot] + static_cast<uint32_t>(t / kQSlots)) & 1u);
-        red_release_gpu_add(flag_fetched + wblk, 1u);
+        // not waited for here (the next loads go out at once): the warp that consumes p_full in tile order — the PV
+        // warp on the leader, the forwarder on the peer — acknowledges the tile to its writer (fetched)
         VG_MARK(15, 400 + t);
       }
     }
@@ -391,7 +382,10 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
       const int slot = t % kQSlots;
       mbar_wait(&bar->p_full[slot], (pf_mask >> slot) & 1);
       pf_mask ^= 1u << slot;
-      if (lane == 0) mbar_remote_arrive(pp0 + slot * 8);
+      if (lane == 0) {
+        mbar_remote_arrive(pp0 + slot * 8);
+        if (t % CS != c) red_relaxed_gpu_add(flag_fetched + blk_of_pair0 + 2 * (t % CS) + hh, 1u);   // landed: ring slot reusable
+      }
       __syncwarp();
     }
   } else if (warp == 9) {
@@ -450,6 +444,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
         VG_MARK(10, 100 + t);
         mbar_wait(&bar->p_full[slot], (pf_mask >> slot) & 1);   // my P(I0, t)
         VG_MARK(10, 200 + t);
+        if (lane == 0 && t % CS != c) red_relaxed_gpu_add(flag_fetched + blk_of_pair0 + 2 * (t % CS) + hh, 1u);
         mbar_wait(&bar->p_pair[slot], (pf_mask >> slot) & 1);   // the peer's P(I1, t)
         VG_MARK(10, 300 + t);
         tm2 += VG_CLK() - t0;

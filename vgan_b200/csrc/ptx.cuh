@@ -212,6 +212,9 @@ __device__ __forceinline__ void st_release_gpu(uint32_t* p, uint32_t v) {
 __device__ __forceinline__ void red_release_gpu_add(uint32_t* p, uint32_t v) {
   asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
+__device__ __forceinline__ void red_relaxed_gpu_add(uint32_t* p, uint32_t v) {
+  asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
 // orders generic-proxy accesses (flags) against async-proxy ones (bulk copies) on global and shared memory
 __device__ __forceinline__ void fence_proxy_async_all() {
   asm volatile("fence.proxy.async;" ::: "memory");
@@ -220,7 +223,7 @@ __device__ __forceinline__ void fence_proxy_async_all() {
 __device__ __forceinline__ void spin_until_ge(const uint32_t* p, uint32_t target) {
   uint32_t spins = 0;
   while (static_cast<int32_t>(ld_acquire_gpu(p) - target) < 0) {
-    __nanosleep(32);
+    __nanosleep(20);
     if (++spins > (VG_SPIN_LIMIT >> 2)) {
       printf("vgan_b200: flag timeout block %d thread %d target %u have %u\n", blockIdx.x, threadIdx.x, target,
              ld_acquire_gpu(p));
