@@ -48,7 +48,7 @@
 #define VG_MARK(w, v) do { if (p.dbg && (threadIdx.x & 31) == 0) { \
   reinterpret_cast<volatile float*>(p.dbg)[static_cast<int64_t>(blockIdx.x) * p.dbg_stride + 16 + (w)] = static_cast<float>(v); } } while (0)
 #else
-#define VG_MARK(w, v) do { } while (0)
+#define VG_MARK(w, v) do { (void)(v); } while (0)
 #endif
 
 namespace vg {
@@ -62,9 +62,6 @@ constexpr int kGStagesMax = 4;                     // barrier slots of the Gram 
 // stream, not against its own Gram.  Ranges are padded to an even number of rounds with zero-coefficient tiles.
 #ifndef VG_G2_STAGES
 #define VG_G2_STAGES 3
-#endif
-#ifndef VG_G2_SLOTS
-#define VG_G2_SLOTS 3
 #endif
 constexpr int kG2Stages = VG_G2_STAGES;
 constexpr int kG2StageBytes = 2 * kChunkBytes;                // 32 KiB
@@ -85,12 +82,42 @@ constexpr int kQSlotsMax = 4;
 //   + kRsBytes                        row-sum exchange: [2 parities][256 CTAs][128 rows] floats
 constexpr int kRing = kXchgBytesPerSm / (2 * kChunkBytes);     // 4 tiles of 32 KiB
 
+// ORDER in which a pair consumes (PV) the P tiles of a range of Kp rounds: its OWN tile of round k first, then the
+// other pairs' tiles of round k - 1.  A tile written by another pair has a whole round (>= 8192 tensor cycles) to
+// travel store -> flag -> fetch, so the exchange latency is off every critical path: the own slot is free again as
+// soon as the own PV has run (the epilogue never waits for another pair), and the remote tiles wait in the writers'
+// rings in L2 until one of the two remote slots is free.  (Consuming tiles in index order made every pair wait for
+// the slowest exchange once per tile: 16 200 cycles per round instead of 10 800 with the 8-CTA clusters.)
+// Slots: 0 = own tiles, 1 / 2 = remote tiles alternating.  Sequence position sq in [0, Kp * CS).
+struct SeqItem { int t, slot, own, k, r; };     // tile, slot, own?, round of the tile, running index among remote tiles
+__device__ __forceinline__ SeqItem seq_item(int sq, int CS, int c, int Kp) {
+  SeqItem it;
+  int i = 0;
+  if (sq == 0) { it.own = 1; it.k = 0; }
+  else {
+    const int m = sq - 1, blk = 1 + m / CS, pos = m % CS;
+    if (blk < Kp && pos == 0) { it.own = 1; it.k = blk; }
+    else { it.own = 0; it.k = blk - 1; i = blk < Kp ? pos - 1 : pos; }
+  }
+  if (it.own) { it.t = CS * it.k + c; it.slot = 0; it.r = 0; }
+  else {
+    const int d = i < c ? i : i + 1;
+    it.t = CS * it.k + d;
+    it.r = it.k * (CS - 1) + i;
+    it.slot = 1 + (it.r & 1);
+  }
+  return it;
+}
+__device__ __forceinline__ int seq_tile(int sq, int CS, int c, int Kp) { return seq_item(sq, CS, c, Kp).t; }
+__device__ __forceinline__ int seq_slot(int sq, int CS, int c, int Kp) { return seq_item(sq, CS, c, Kp).slot; }
+
 struct __align__(8) PairBarriers {
   uint64_t g_full[kGStagesMax], g_empty[kGStagesMax];
   uint64_t v_full[kVStages], v_empty[kVStages];
   uint64_t s_full[2], s_empty[2];
   uint64_t nj_full[2], nj_empty[2];
-  uint64_t p_full[kQSlotsMax], p_pair[kQSlotsMax], pub_full[kQSlotsMax], own_free[kQSlotsMax], rem_free[kQSlotsMax];
+  uint64_t p_full[kQSlotsMax], p_pair[kQSlotsMax], rem_free[kQSlotsMax];
+  uint64_t pub_full, pub_done, own_free;
   uint64_t o_full;
   uint32_t tmem_base;
   float red[8][4];
@@ -99,7 +126,7 @@ struct __align__(8) PairBarriers {
 struct PairCfg {
   static constexpr int GS = kG2Stages;              // Gram ring stages
   static constexpr int GSB = kG2StageBytes;         // bytes per stage
-  static constexpr int QS = VG_G2_SLOTS;            // P slots, 32 KiB each
+  static constexpr int QS = 3;                      // P slots, 32 KiB each: one for own tiles, two for remote ones
   static constexpr int SmemG = 0;
   static constexpr int SmemV = SmemG + GS * GSB;
   static constexpr int SmemP = SmemV + kVStages * kVStageBytes;
@@ -213,10 +240,11 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     for (int s = 0; s < kQSlots; ++s) {
       mbar_init(&bar->p_full[s], 1);
       mbar_init(&bar->p_pair[s], 1);
-      mbar_init(&bar->pub_full[s], 1);
-      mbar_init(&bar->own_free[s], 1);
       mbar_init(&bar->rem_free[s], 1);
     }
+    mbar_init(&bar->pub_full, 1);
+    mbar_init(&bar->pub_done, 1);
+    mbar_init(&bar->own_free, 1);
     mbar_init(&bar->o_full, 1);
     fence_barrier_init();
   }
@@ -239,8 +267,9 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
   // ---- pipeline state that persists across the work ranges of this CTA (each warp uses its role's part)
   uint32_t rs = 0, rph = 0;            // ring stage / phase: G ring (warps 8, 11, 9), V ring (warps 12, 10)
   uint32_t kg = 0;                     // Gram tiles of this CTA so far: S / norm buffer kg & 1, parity (kg >> 1) & 1
-  uint32_t pf_mask = 0, pub_mask = 0, of_mask = 0, rf_mask = 0;   // per-slot phase parities of p_full / pub_full /
-                                       // own_free / rem_free, toggled by roles that wait for EVERY phase of the barrier
+  uint32_t pf_mask = 0, rf_mask = 0;   // per-slot phase parities of p_full / rem_free (toggled by roles that wait for
+                                       // EVERY phase of the barrier)
+  uint32_t pub_ph = 0, pd_ph = 0, of_ph = 0;   // phase parities of pub_full / pub_done / own_free
   uint32_t seq_base = 0;               // tiles every CTA of the group has published before this range
   uint32_t part = 0;                   // ranges done: parity of o_full, group barrier count, row-sum buffer
   long long tm0 = 0, tm1 = 0, tm2 = 0, tm3 = 0;      // debug timers (meaning depends on the role)
@@ -285,7 +314,8 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
   } else if (warp == 12) {
     // ===================== V producer: half tiles of Z_J[:, this CTA's half of the slice] =====================
     if (my_chunks > 0) {
-      for (int t = 0; t < TTp; ++t) {
+      for (int sq = 0; sq < TTp; ++sq) {
+        const int t = seq_tile(sq, CS, c, Kp);
         const int jt = min(tile0 + t, T - 1);
         for (int h = 0; h < 2; ++h) {
           mbar_wait(&bar->v_empty[rs], rph ^ 1);
@@ -326,20 +356,21 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     uint8_t* ring = p.xchg + static_cast<size_t>(blockIdx.x) * kXchgBytesPerSm;
     for (int k = 0; k < Kp; ++k) {
       const int t = CS * k + c;
-      const int slot = t % kQSlots;
       VG_MARK(13, 100 + t);
-      mbar_wait(&bar->pub_full[slot], (pub_mask >> slot) & 1);
-      pub_mask ^= 1u << slot;
+      mbar_wait(&bar->pub_full, pub_ph);
+      pub_ph ^= 1u;
       VG_MARK(13, 200 + t);
-      if (lane == 0 && CS > 1) {
-        const uint32_t q = seq_base + static_cast<uint32_t>(k);
-        if (q >= static_cast<uint32_t>(kRing))
-          spin_until_ge(my_fetched, (q - kRing + 1) * static_cast<uint32_t>(CS - 1));
-        const uint32_t src = smem_u32(smem + kQSmemP + slot * kQPBytes);
-        bulk_store_global(ring + (q % kRing) * kQPBytes, src, pbytes);
-        bulk_commit_wait_all();                      // the tile is in global memory
-        fence_proxy_async_all();
-        st_release_gpu(my_ready, q + 1);
+      if (lane == 0) {
+        if (CS > 1) {
+          const uint32_t q = seq_base + static_cast<uint32_t>(k);
+          if (q >= static_cast<uint32_t>(kRing))
+            spin_until_ge(my_fetched, (q - kRing + 1) * static_cast<uint32_t>(CS - 1));
+          bulk_store_global(ring + (q % kRing) * kQPBytes, smem_u32(smem + kQSmemP), pbytes);   // own tiles: slot 0
+          bulk_commit_wait_all();                    // the tile is in global memory
+          fence_proxy_async_all();
+          st_release_gpu(my_ready, q + 1);
+        }
+        mbar_arrive(&bar->pub_done);                 // slot 0 is no longer read by this warp
       }
       VG_MARK(13, 300 + t);
       __syncwarp();
@@ -349,28 +380,32 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     // In tile order.  A slot is free once this pair's PV of the tile that used it before has completed (rem_free,
     // committed to both CTAs of the pair); the tile is there once its writer's ready count says so.
     if (lane == 0 && CS > 1) {
-      for (int t = 0; t < TTp; ++t) {
-        const int d = t % CS;
-        if (d == c) continue;
-        const int slot = t % kQSlots;
-        VG_MARK(15, 100 + t);
-        if (t >= kQSlots) {       // this pair finished PV(t - kQSlots): rem_free completes once per tile this warp fills
-          mbar_wait(&bar->rem_free[slot], (rf_mask >> slot) & 1);
-          rf_mask ^= 1u << slot;
+      int r = 0;                                      // remote tiles of this range so far
+      for (int k = 0; k < Kp; ++k) {
+        for (int d = 0; d < CS; ++d) {
+          if (d == c) continue;
+          const int t = CS * k + d;
+          const int slot = 1 + (r & 1);
+          VG_MARK(15, 100 + t);
+          if (r >= 2) {       // this pair finished the PV of the tile that was in the slot
+            mbar_wait(&bar->rem_free[slot], (rf_mask >> slot) & 1);
+            rf_mask ^= 1u << slot;
+          }
+          const int wblk = blk_of_pair0 + 2 * d + hh;   // the writer: pair d of this group, same row tile
+          const uint32_t q = seq_base + static_cast<uint32_t>(k);
+          VG_MARK(15, 200 + t);
+          spin_until_ge(flag_ready + wblk, q + 1);
+          VG_MARK(15, 300 + t);
+          fence_proxy_async_all();
+          mbar_arrive_expect_tx(&bar->p_full[slot], pbytes);
+          bulk_load_1d(smem + kQSmemP + slot * kQPBytes,
+                       p.xchg + static_cast<size_t>(wblk) * kXchgBytesPerSm + (q % kRing) * kQPBytes, pbytes,
+                       &bar->p_full[slot]);
+          // not waited for here (the next load goes out at once): the warp that consumes p_full in order — the PV warp
+          // on the leader, the forwarder on the peer — acknowledges the tile to its writer (fetched)
+          VG_MARK(15, 400 + t);
+          ++r;
         }
-        const int wblk = blk_of_pair0 + 2 * d + hh;   // the writer: pair d of this group, same row tile
-        const uint32_t q = seq_base + static_cast<uint32_t>(t / CS);
-        VG_MARK(15, 200 + t);
-        spin_until_ge(flag_ready + wblk, q + 1);
-        VG_MARK(15, 300 + t);
-        fence_proxy_async_all();
-        mbar_arrive_expect_tx(&bar->p_full[slot], pbytes);
-        bulk_load_1d(smem + kQSmemP + slot * kQPBytes,
-                     p.xchg + static_cast<size_t>(wblk) * kXchgBytesPerSm + (q % kRing) * kQPBytes, pbytes,
-                     &bar->p_full[slot]);
-        // not waited for here (the next loads go out at once): the warp that consumes p_full in tile order — the PV
-        // warp on the leader, the forwarder on the peer — acknowledges the tile to its writer (fetched)
-        VG_MARK(15, 400 + t);
       }
     }
     __syncwarp();
@@ -378,8 +413,9 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     // ===================== peer CTA: forward "my P tile t is in place" to the leader's PV warp =========
     // (own tiles are parked by the epilogue, the other pairs' tiles land by the fetcher's bulk loads)
     const uint32_t pp0 = mapa_u32(smem_u32(&bar->p_pair[0]), 0u);
-    for (int t = 0; t < TTp; ++t) {
-      const int slot = t % kQSlots;
+    for (int sq = 0; sq < TTp; ++sq) {
+      const int t = seq_tile(sq, CS, c, Kp);
+      const int slot = seq_slot(sq, CS, c, Kp);
       mbar_wait(&bar->p_full[slot], (pf_mask >> slot) & 1);
       pf_mask ^= 1u << slot;
       if (lane == 0) {
@@ -437,14 +473,16 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     const uint32_t idesc_pv = make_idesc_bf16(2 * kTile, slice_chunks * kChunk, 0, 1);
     const uint32_t v_lo0 = (smem_u32(smem + kQSmemV) & 0x3FFFFu) >> 4;
     const uint32_t p_lo0 = (smem_u32(smem + kQSmemP) & 0x3FFFFu) >> 4;
-    for (int t = 0; t < TTp; ++t) {
-      const int slot = t % kQSlots;
+    const int n_rem = Kp * (CS - 1);
+    for (int sq = 0; sq < TTp; ++sq) {
+      const SeqItem it = seq_item(sq, CS, c, Kp);
+      const int t = it.t, slot = it.slot;
       {
         const long long t0 = VG_CLK();
         VG_MARK(10, 100 + t);
         mbar_wait(&bar->p_full[slot], (pf_mask >> slot) & 1);   // my P(I0, t)
         VG_MARK(10, 200 + t);
-        if (lane == 0 && t % CS != c) red_relaxed_gpu_add(flag_fetched + blk_of_pair0 + 2 * (t % CS) + hh, 1u);
+        if (lane == 0 && !it.own) red_relaxed_gpu_add(flag_fetched + blk_of_pair0 + 2 * (t % CS) + hh, 1u);
         mbar_wait(&bar->p_pair[slot], (pf_mask >> slot) & 1);   // the peer's P(I1, t)
         VG_MARK(10, 300 + t);
         tm2 += VG_CLK() - t0;
@@ -467,7 +505,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
             for (int j = 0; j < 4; ++j) {
               const uint64_t adesc = (static_cast<uint64_t>(desc_hi) << 32) | (pa_lo + j * 2);
               const uint64_t bdesc = (static_cast<uint64_t>(desc_hi) << 32) | (v_lo + j * (2048 >> 4)) | lbo_v;
-              umma_bf16_ss_2cta(tmem_o, adesc, bdesc, idesc_pv, (t | h | j) != 0);
+              umma_bf16_ss_2cta(tmem_o, adesc, bdesc, idesc_pv, (sq | h | j) != 0);
             }
             umma_commit_2cta_mc(&bar->v_empty[rs], pair_mask);
           }
@@ -475,12 +513,13 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
           if (++rs == kVStages) { rs = 0; rph ^= 1; }
         }
       }
-      // both CTAs of the pair are done with the slot once this PV has completed: whoever fills it with tile
-      // t + kQSlots waits for this — the epilogue for an own tile (own_free), the fetcher for another pair's
-      // (rem_free).  Two barriers, so that each waiter sees EVERY phase of its barrier (a parity wait cannot tell
-      // phases two apart)
-      if (t + kQSlots < TTp && elect_one())
-        umma_commit_2cta_mc((t + kQSlots) % CS == c ? &bar->own_free[slot] : &bar->rem_free[slot], pair_mask);
+      // both CTAs of the pair are done with the slot once this PV has completed: the epilogue waits for the own slot
+      // (own_free: once per own tile that has a successor in the range), the fetcher for a remote slot (rem_free).
+      // Every waiter sees EVERY phase of its barrier (a parity wait cannot tell phases two apart).
+      if (elect_one()) {
+        if (it.own) { if (it.k + 1 < Kp) umma_commit_2cta_mc(&bar->own_free, pair_mask); }
+        else if (it.r + 2 < n_rem) umma_commit_2cta_mc(&bar->rem_free[slot], pair_mask);
+      }
       __syncwarp();
     }
     if (elect_one()) umma_commit_2cta_mc(&bar->o_full, pair_mask);
@@ -552,12 +591,14 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     };
     auto park = [&](int k, const uint4 (&pk)[8]) {
       long long tq = VG_CLK();
-      const int t = CS * k + c;                          // tile index within the range (slot protocol)
-      const int slot = t % kQSlots;
+      const int t = CS * k + c;                          // tile index within the range
+      constexpr int slot = 0;                            // own tiles live in slot 0
       VG_MARK(warp, 100 + t);
-      if (t >= kQSlots) {
-        mbar_wait(&bar->own_free[slot], (of_mask >> slot) & 1);    // this pair finished PV(t - kQSlots)
-        of_mask ^= 1u << slot;
+      if (k >= 1) {
+        mbar_wait(&bar->own_free, of_ph);                // this pair's PV of the previous own tile has completed
+        of_ph ^= 1u;
+        mbar_wait(&bar->pub_done, pd_ph);                // and the publisher has stored it
+        pd_ph ^= 1u;
       }
       tm2 += VG_CLK() - tq; tq = VG_CLK();
       uint8_t* p_slot = smem + kQSmemP + slot * kQPBytes;
@@ -569,7 +610,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
       asm volatile("bar.sync 1, 256;" ::: "memory");
       if (threadIdx.x == 0) {
         mbar_arrive(&bar->p_full[slot]);     // own PV warp / forwarder
-        mbar_arrive(&bar->pub_full[slot]);   // publisher warp
+        mbar_arrive(&bar->pub_full);         // publisher warp
       }
       VG_MARK(warp, 200 + t);
       tm3 += VG_CLK() - tq;
@@ -589,6 +630,8 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
         park(k + 1, pk1);
       }
     }
+    mbar_wait(&bar->pub_done, pd_ph);                    // the last own tile of the range has been stored (every
+    pd_ph ^= 1u;                                         // phase of pub_done is waited for, in order)
     // ---- partial sums of this CTA's tiles
     acc_x = warp_sum(acc_x);
     acc_y = warp_sum(acc_y);
