@@ -88,7 +88,9 @@ constexpr int kRing = kXchgBytesPerSm / (2 * kChunkBytes);     // 4 tiles of 32 
 // soon as the own PV has run (the epilogue never waits for another pair), and the remote tiles wait in the writers'
 // rings in L2 until one of the two remote slots is free.  (Consuming tiles in index order made every pair wait for
 // the slowest exchange once per tile: 16 200 cycles per round instead of 10 800 with the 8-CTA clusters.)
-// Slots: 0 = own tiles, 1 / 2 = remote tiles alternating.  Sequence position sq in [0, Kp * CS).
+// Slots go round-robin over the sequence (slot = sq % 3): the tile of position sq + 3 can be brought in as soon as
+// the PV of position sq is done, i.e. three PV times before its own turn — a fetch from L2 fits in that.
+// Sequence position sq in [0, Kp * CS).
 struct SeqItem { int t, slot, own, k, r; };     // tile, slot, own?, round of the tile, running index among remote tiles
 __device__ __forceinline__ SeqItem seq_item(int sq, int CS, int c, int Kp) {
   SeqItem it;
@@ -99,25 +101,27 @@ __device__ __forceinline__ SeqItem seq_item(int sq, int CS, int c, int Kp) {
     if (blk < Kp && pos == 0) { it.own = 1; it.k = blk; }
     else { it.own = 0; it.k = blk - 1; i = blk < Kp ? pos - 1 : pos; }
   }
-  if (it.own) { it.t = CS * it.k + c; it.slot = 0; it.r = 0; }
+  if (it.own) { it.t = CS * it.k + c; it.r = 0; }
   else {
     const int d = i < c ? i : i + 1;
     it.t = CS * it.k + d;
     it.r = it.k * (CS - 1) + i;
-    it.slot = 1 + (it.r & 1);
   }
+  it.slot = sq % 3;
   return it;
 }
 __device__ __forceinline__ int seq_tile(int sq, int CS, int c, int Kp) { return seq_item(sq, CS, c, Kp).t; }
 __device__ __forceinline__ int seq_slot(int sq, int CS, int c, int Kp) { return seq_item(sq, CS, c, Kp).slot; }
+__device__ __forceinline__ int seq_of_own(int k, int CS) { return k == 0 ? 0 : (k - 1) * CS + 1; }   // position of own(k)
 
 struct __align__(8) PairBarriers {
   uint64_t g_full[kGStagesMax], g_empty[kGStagesMax];
   uint64_t v_full[kVStages], v_empty[kVStages];
   uint64_t s_full[2], s_empty[2];
   uint64_t nj_full[2], nj_empty[2];
-  uint64_t p_full[kQSlotsMax], p_pair[kQSlotsMax], rem_free[kQSlotsMax];
-  uint64_t pub_full, pub_done, own_free;
+  uint64_t p_full[kQSlotsMax], p_pair[kQSlotsMax], own_free[kQSlotsMax], rem_free[kQSlotsMax];
+  uint64_t pub_full;
+  uint32_t pub_count;          // own tiles this CTA's publisher has finished reading out of shared memory (monotonic)
   uint64_t o_full;
   uint32_t tmem_base;
   float red[8][4];
@@ -240,11 +244,11 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     for (int s = 0; s < kQSlots; ++s) {
       mbar_init(&bar->p_full[s], 1);
       mbar_init(&bar->p_pair[s], 1);
+      mbar_init(&bar->own_free[s], 1);
       mbar_init(&bar->rem_free[s], 1);
     }
     mbar_init(&bar->pub_full, 1);
-    mbar_init(&bar->pub_done, 1);
-    mbar_init(&bar->own_free, 1);
+    bar->pub_count = 0;
     mbar_init(&bar->o_full, 1);
     fence_barrier_init();
   }
@@ -267,9 +271,19 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
   // ---- pipeline state that persists across the work ranges of this CTA (each warp uses its role's part)
   uint32_t rs = 0, rph = 0;            // ring stage / phase: G ring (warps 8, 11, 9), V ring (warps 12, 10)
   uint32_t kg = 0;                     // Gram tiles of this CTA so far: S / norm buffer kg & 1, parity (kg >> 1) & 1
-  uint32_t pf_mask = 0, rf_mask = 0;   // per-slot phase parities of p_full / rem_free (toggled by roles that wait for
-                                       // EVERY phase of the barrier)
-  uint32_t pub_ph = 0, pd_ph = 0, of_ph = 0;   // phase parities of pub_full / pub_done / own_free
+  uint32_t pf_mask = 0, rf_mask = 0, of_mask = 0;   // per-slot phase parities of p_full / rem_free / own_free (toggled by
+                                       // roles that wait for EVERY phase of the barrier)
+  uint32_t pub_ph = 0;                 // phase parity of pub_full
+  // a slot that held an OWN tile is also read by the publisher (bulk store to the ring): whoever refills it waits until
+  // the publisher's count has passed that tile (a monotonic counter in shared memory: no phase to lose track of)
+  auto wait_published = [&](uint32_t count) {
+    const volatile uint32_t* pc = &bar->pub_count;
+    uint32_t spins = 0;
+    while (static_cast<int32_t>(*pc - count) < 0) {
+      __nanosleep(20);
+      if (++spins > (VG_SPIN_LIMIT >> 2)) { printf("vgan_b200: publisher timeout block %d\n", blockIdx.x); __trap(); }
+    }
+  };
   uint32_t seq_base = 0;               // tiles every CTA of the group has published before this range
   uint32_t part = 0;                   // ranges done: parity of o_full, group barrier count, row-sum buffer
   long long tm0 = 0, tm1 = 0, tm2 = 0, tm3 = 0;      // debug timers (meaning depends on the role)
@@ -365,12 +379,13 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
           const uint32_t q = seq_base + static_cast<uint32_t>(k);
           if (q >= static_cast<uint32_t>(kRing))
             spin_until_ge(my_fetched, (q - kRing + 1) * static_cast<uint32_t>(CS - 1));
-          bulk_store_global(ring + (q % kRing) * kQPBytes, smem_u32(smem + kQSmemP), pbytes);   // own tiles: slot 0
+          const int slot = seq_of_own(k, CS) % kQSlots;
+          bulk_store_global(ring + (q % kRing) * kQPBytes, smem_u32(smem + kQSmemP + slot * kQPBytes), pbytes);
           bulk_commit_wait_all();                    // the tile is in global memory
           fence_proxy_async_all();
           st_release_gpu(my_ready, q + 1);
         }
-        mbar_arrive(&bar->pub_done);                 // slot 0 is no longer read by this warp
+        *reinterpret_cast<volatile uint32_t*>(&bar->pub_count) = seq_base + static_cast<uint32_t>(k) + 1u;   // slot no longer read
       }
       VG_MARK(13, 300 + t);
       __syncwarp();
@@ -380,32 +395,30 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     // In tile order.  A slot is free once this pair's PV of the tile that used it before has completed (rem_free,
     // committed to both CTAs of the pair); the tile is there once its writer's ready count says so.
     if (lane == 0 && CS > 1) {
-      int r = 0;                                      // remote tiles of this range so far
-      for (int k = 0; k < Kp; ++k) {
-        for (int d = 0; d < CS; ++d) {
-          if (d == c) continue;
-          const int t = CS * k + d;
-          const int slot = 1 + (r & 1);
-          VG_MARK(15, 100 + t);
-          if (r >= 2) {       // this pair finished the PV of the tile that was in the slot
-            mbar_wait(&bar->rem_free[slot], (rf_mask >> slot) & 1);
-            rf_mask ^= 1u << slot;
-          }
-          const int wblk = blk_of_pair0 + 2 * d + hh;   // the writer: pair d of this group, same row tile
-          const uint32_t q = seq_base + static_cast<uint32_t>(k);
-          VG_MARK(15, 200 + t);
-          spin_until_ge(flag_ready + wblk, q + 1);
-          VG_MARK(15, 300 + t);
-          fence_proxy_async_all();
-          mbar_arrive_expect_tx(&bar->p_full[slot], pbytes);
-          bulk_load_1d(smem + kQSmemP + slot * kQPBytes,
-                       p.xchg + static_cast<size_t>(wblk) * kXchgBytesPerSm + (q % kRing) * kQPBytes, pbytes,
-                       &bar->p_full[slot]);
-          // not waited for here (the next load goes out at once): the warp that consumes p_full in order — the PV warp
-          // on the leader, the forwarder on the peer — acknowledges the tile to its writer (fetched)
-          VG_MARK(15, 400 + t);
-          ++r;
+      for (int sq = 0; sq < TTp; ++sq) {
+        const SeqItem it = seq_item(sq, CS, c, Kp);
+        if (it.own) continue;
+        const int t = it.t, slot = it.slot, d = t % CS, k = it.k;
+        VG_MARK(15, 100 + t);
+        if (sq >= kQSlots) {       // this pair finished the PV of the tile that was in the slot
+          mbar_wait(&bar->rem_free[slot], (rf_mask >> slot) & 1);
+          rf_mask ^= 1u << slot;
+          const SeqItem prev = seq_item(sq - kQSlots, CS, c, Kp);
+          if (prev.own) wait_published(seq_base + static_cast<uint32_t>(prev.k) + 1u);
         }
+        const int wblk = blk_of_pair0 + 2 * d + hh;   // the writer: pair d of this group, same row tile
+        const uint32_t q = seq_base + static_cast<uint32_t>(k);
+        VG_MARK(15, 200 + t);
+        spin_until_ge(flag_ready + wblk, q + 1);
+        VG_MARK(15, 300 + t);
+        fence_proxy_async_all();
+        mbar_arrive_expect_tx(&bar->p_full[slot], pbytes);
+        bulk_load_1d(smem + kQSmemP + slot * kQPBytes,
+                     p.xchg + static_cast<size_t>(wblk) * kXchgBytesPerSm + (q % kRing) * kQPBytes, pbytes,
+                     &bar->p_full[slot]);
+        // not waited for here (the next load goes out at once): the warp that consumes p_full in order — the PV warp
+        // on the leader, the forwarder on the peer — acknowledges the tile to its writer (fetched)
+        VG_MARK(15, 400 + t);
       }
     }
     __syncwarp();
@@ -473,7 +486,6 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     const uint32_t idesc_pv = make_idesc_bf16(2 * kTile, slice_chunks * kChunk, 0, 1);
     const uint32_t v_lo0 = (smem_u32(smem + kQSmemV) & 0x3FFFFu) >> 4;
     const uint32_t p_lo0 = (smem_u32(smem + kQSmemP) & 0x3FFFFu) >> 4;
-    const int n_rem = Kp * (CS - 1);
     for (int sq = 0; sq < TTp; ++sq) {
       const SeqItem it = seq_item(sq, CS, c, Kp);
       const int t = it.t, slot = it.slot;
@@ -513,12 +525,13 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
           if (++rs == kVStages) { rs = 0; rph ^= 1; }
         }
       }
-      // both CTAs of the pair are done with the slot once this PV has completed: the epilogue waits for the own slot
-      // (own_free: once per own tile that has a successor in the range), the fetcher for a remote slot (rem_free).
-      // Every waiter sees EVERY phase of its barrier (a parity wait cannot tell phases two apart).
-      if (elect_one()) {
-        if (it.own) { if (it.k + 1 < Kp) umma_commit_2cta_mc(&bar->own_free, pair_mask); }
-        else if (it.r + 2 < n_rem) umma_commit_2cta_mc(&bar->rem_free[slot], pair_mask);
+      // both CTAs of the pair are done with the slot once this PV has completed: whoever fills it with the tile of
+      // position sq + 3 waits for that — the epilogue for an own tile (own_free), the fetcher for another pair's
+      // (rem_free).  Two barriers per slot, so that every waiter sees EVERY phase of its barrier (a parity wait cannot
+      // tell phases two apart).
+      if (sq + kQSlots < TTp && elect_one()) {
+        const SeqItem nxt = seq_item(sq + kQSlots, CS, c, Kp);
+        umma_commit_2cta_mc(nxt.own ? &bar->own_free[slot] : &bar->rem_free[slot], pair_mask);
       }
       __syncwarp();
     }
@@ -592,13 +605,14 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     auto park = [&](int k, const uint4 (&pk)[8]) {
       long long tq = VG_CLK();
       const int t = CS * k + c;                          // tile index within the range
-      constexpr int slot = 0;                            // own tiles live in slot 0
+      const int sq = seq_of_own(k, CS);                  // position in the consumption order -> slot
+      const int slot = sq % kQSlots;
       VG_MARK(warp, 100 + t);
-      if (k >= 1) {
-        mbar_wait(&bar->own_free, of_ph);                // this pair's PV of the previous own tile has completed
-        of_ph ^= 1u;
-        mbar_wait(&bar->pub_done, pd_ph);                // and the publisher has stored it
-        pd_ph ^= 1u;
+      if (sq >= kQSlots) {
+        mbar_wait(&bar->own_free[slot], (of_mask >> slot) & 1);    // this pair's PV of position sq - 3 has completed
+        of_mask ^= 1u << slot;
+        const SeqItem prev = seq_item(sq - kQSlots, CS, c, Kp);
+        if (prev.own) wait_published(seq_base + static_cast<uint32_t>(prev.k) + 1u);
       }
       tm2 += VG_CLK() - tq; tq = VG_CLK();
       uint8_t* p_slot = smem + kQSmemP + slot * kQPBytes;
@@ -630,8 +644,6 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
         park(k + 1, pk1);
       }
     }
-    mbar_wait(&bar->pub_done, pd_ph);                    // the last own tile of the range has been stored (every
-    pd_ph ^= 1u;                                         // phase of pub_done is waited for, in order)
     // ---- partial sums of this CTA's tiles
     acc_x = warp_sum(acc_x);
     acc_y = warp_sum(acc_y);
