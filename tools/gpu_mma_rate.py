@@ -2,7 +2,8 @@
 import os, sys, torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from vgan_b200 import _lib
-L = _lib.lib()
+L = _lib.lib_debug()      # probes live in the debug build only
+CTX = _lib.ctx(0, L)
 rows = 32768
 Z = torch.randn(rows, 1024, device="cuda").bfloat16()
 grid = 148
@@ -12,7 +13,7 @@ iters = 4000
 for n in (128, 256):
     for mn in (0, 1):
         for tw in (0, 1, 2, 4, 8):
-            _lib.check(L.vgan_b200_umma_rate_probe(n, iters, mn, Z.data_ptr(), rows, tw, grid, out.data_ptr(), st), "rate")
+            _lib.check(L.vgan_b200_umma_rate_probe(CTX, n, iters, mn, Z.data_ptr(), rows, tw, grid, out.data_ptr(), st), "rate")
             torch.cuda.synchronize()
             o = out.view(grid, 2).double()
             cyc = o[:, 0].mean().item(); boxes = o[:, 1].mean().item()

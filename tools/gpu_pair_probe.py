@@ -1,14 +1,15 @@
 import os, sys, torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from vgan_b200 import _lib
-L = _lib.lib()
+L = _lib.lib_debug()      # probes live in the debug build only
+CTX = _lib.ctx(0, L)
 torch.manual_seed(0)
 A0 = torch.randn(128, 128, device="cuda").bfloat16().contiguous()
 A1 = torch.randn(128, 128, device="cuda").bfloat16().contiguous()
 B = torch.randn(128, 128, device="cuda").bfloat16().contiguous()
 V = torch.randn(128, 256, device="cuda").bfloat16().contiguous()
 S = torch.zeros(2, 128, 128, device="cuda"); O = torch.zeros(2, 128, 256, device="cuda")
-_lib.check(L.vgan_b200_pair_probe(A0.data_ptr(), A1.data_ptr(), B.data_ptr(), V.data_ptr(), S.data_ptr(), O.data_ptr(),
+_lib.check(L.vgan_b200_pair_probe(CTX, A0.data_ptr(), A1.data_ptr(), B.data_ptr(), V.data_ptr(), S.data_ptr(), O.data_ptr(),
                                   torch.cuda.current_stream().cuda_stream), "pair_probe")
 torch.cuda.synchronize()
 for h, A in enumerate((A0, A1)):

@@ -2,7 +2,8 @@
 import os, sys, torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from vgan_b200 import _lib
-L = _lib.lib()
+L = _lib.lib_debug()      # probes live in the debug build only
+CTX = _lib.ctx(0, L)
 rows, cols = 131072, 1024
 Z = torch.randn(rows, cols, device="cuda").bfloat16()
 st = torch.cuda.current_stream().cuda_stream
@@ -17,9 +18,9 @@ for mode in (2, 6):
                 if stages * loads * box > 200 * 1024 or stages % nprod: continue
                 a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 args = (Z.data_ptr(), rows, cols, stages, loads, box_rows, iters, mode, grid, nprod, out.data_ptr(), st)
-                _lib.check(L.vgan_b200_tma_rate_probe(*args), "tma")
+                _lib.check(L.vgan_b200_tma_rate_probe(CTX, *args), "tma")
                 a.record()
-                _lib.check(L.vgan_b200_tma_rate_probe(*args), "tma")
+                _lib.check(L.vgan_b200_tma_rate_probe(CTX, *args), "tma")
                 b.record(); torch.cuda.synchronize()
                 ms = a.elapsed_time(b)
                 byts = iters * loads * box
