@@ -278,10 +278,7 @@ static int run_tc(vgan_b200_ctx* ctx, const vgan_b200_layout_t& L, void* ws, con
 #ifdef VGAN_B200_DEBUG
     xx_mode = ctx->xx_mode;             // 1: serial, 2: S_xx kernel dispatched first (measurement)
 #endif
-    // the S_xx kernel runs BESIDE the gradient kernel only when that leaves it SMs (cluster limit set, or fewer units
-    // than the device holds pairs); otherwise behind it on the same stream
-    const int pair_ctas = pair_grid_ctas(ctx, p, ladder);
-    const bool overlap = p.n_xx_units > 0 && xx_mode != 1 && pair_ctas > 0 && ctx->n_sms - pair_ctas >= kXxMinFreeSms;
+    const bool overlap = p.n_xx_units > 0 && xx_mode != 1;
     if (overlap)
       if (int e = ensure_aux(ctx)) return e;
     cudaStream_t main_st = st;

@@ -32,14 +32,11 @@ constexpr int kParFloats = 64;
 // misc words of the accumulator block (layout.off_misc): float penalty, float loss, uint32 "CTAs started"
 constexpr int kMiscPenalty = 0, kMiscLoss = 4, kMiscStarted = 8, kMiscBytes = 64;
 constexpr int kXxMinFreeSms = 8;         // fewer SMs left free by the gradient clusters: S_xx runs over all SMs at low priority instead
-// Exchange scratch of the pair kernel (global memory that lives in L2: rewritten in place all the time), indexed by
-// blockIdx of the persistent grid: a ring of P tiles per CTA, three flag words per CTA, the row-sum exchange buffers
-constexpr int kXchgSms = 256;                          // CTAs of the persistent grid the scratch is laid out for
-constexpr int kXchgBytesPerSm = 4 * 2 * kChunkBytes;   // ring of 4 P tiles of 32 KiB per CTA
-constexpr size_t kRingBytes = static_cast<size_t>(kXchgSms) * kXchgBytesPerSm;
-constexpr size_t kPairFlagBytes = 3 * kXchgSms * 4;    // ready / fetched / group-barrier counters (zeroed per launch)
-constexpr size_t kPairRsBytes = 2 * static_cast<size_t>(kXchgSms) * kTile * 4;   // row-sum exchange, two parities
-constexpr size_t kXchgTotalBytes = kRingBytes + kPairFlagBytes + kPairRsBytes;
+// P-tile exchange scratch (pair kernel): 3 slots of one bf16 [128,128] tile per SM, indexed by %smid so that a
+// region is only ever rewritten by the CTA resident on that SM (stays in L2, never streams to HBM)
+constexpr int kXchgSms = 256;
+constexpr int kXchgBytesPerSm = 4 * 2 * kChunkBytes;   // up to 4 P tiles of 32 KiB per SM
+constexpr size_t kXchgTotalBytes = static_cast<size_t>(kXchgSms) * kXchgBytesPerSm;
 
 struct TcParams {
   int tiles_x, tiles_y;       // 128-row tiles in the X / Y regions of the stacked operand
@@ -153,6 +150,5 @@ int launch_xx(vgan_b200_ctx* ctx, const TcParams& p, const CUtensorMap& map, con
               cudaStream_t st, int max_ctas = 0);
 int launch_tc_pair(vgan_b200_ctx* ctx, const TcParams& p, const CUtensorMap& map, const CUtensorMap& mapB64,
                    const CUtensorMap& mapV64, int ladder, cudaStream_t st, int* resident_ctas = nullptr);
-int pair_grid_ctas(vgan_b200_ctx* ctx, const TcParams& p, int ladder);   // CTAs launch_tc_pair will launch (<0: error)
 
 }  // namespace vg

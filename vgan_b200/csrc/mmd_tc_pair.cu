@@ -43,14 +43,6 @@
 #define VG_CLK() 0ll
 #endif
 
-// progress markers (debug build, p.dbg in host-mapped memory): role `w` of this CTA has reached `v`
-#ifdef VGAN_B200_DEBUG
-#define VG_MARK(w, v) do { if (p.dbg && (threadIdx.x & 31) == 0) { \
-  reinterpret_cast<volatile float*>(p.dbg)[static_cast<int64_t>(blockIdx.x) * p.dbg_stride + 16 + (w)] = static_cast<float>(v); } } while (0)
-#else
-#define VG_MARK(w, v) do { (void)(v); } while (0)
-#endif
-
 namespace vg {
 
 constexpr int kGStagesMax = 4;                     // barrier slots of the Gram operand ring
@@ -62,6 +54,9 @@ constexpr int kGStagesMax = 4;                     // barrier slots of the Gram 
 // stream, not against its own Gram.  Ranges are padded to an even number of rounds with zero-coefficient tiles.
 #ifndef VG_G2_STAGES
 #define VG_G2_STAGES 3
+#endif
+#ifndef VG_G2_SLOTS
+#define VG_G2_SLOTS 3
 #endif
 constexpr int kG2Stages = VG_G2_STAGES;
 constexpr int kG2StageBytes = 2 * kChunkBytes;                // 32 KiB
@@ -75,53 +70,13 @@ constexpr int kQThreads = 512;   // warps: 0-7 epilogue (192 registers), 8-15 se
 // 12 710 — the Gram warp then waits 6 600 cycles per round for operands, and the slot wait does not shrink because
 // the in-order PV stream of every pair stalls on whichever pair is late.
 constexpr int kQSlotsMax = 4;
-// P exchange between the pairs of a group goes through global memory (L2): every CTA owns a ring of kRing tiles
-// (indexed by blockIdx: kXchgBytesPerSm per CTA) plus three flag words, all inside TcParams::xchg:
-//   [0, kXchgSms * kXchgBytesPerSm)  tile rings
-//   + kFlagBytes                      ready[256], fetched[256], group barrier counters[256]  (zeroed per launch)
-//   + kRsBytes                        row-sum exchange: [2 parities][256 CTAs][128 rows] floats
-constexpr int kRing = kXchgBytesPerSm / (2 * kChunkBytes);     // 4 tiles of 32 KiB
-
-// ORDER in which a pair consumes (PV) the P tiles of a range of Kp rounds: its OWN tile of round k first, then the
-// other pairs' tiles of round k - 1.  A tile written by another pair has a whole round (>= 8192 tensor cycles) to
-// travel store -> flag -> fetch, so the exchange latency is off every critical path: the own slot is free again as
-// soon as the own PV has run (the epilogue never waits for another pair), and the remote tiles wait in the writers'
-// rings in L2 until one of the two remote slots is free.  (Consuming tiles in index order made every pair wait for
-// the slowest exchange once per tile: 16 200 cycles per round instead of 10 800 with the 8-CTA clusters.)
-// Slots go round-robin over the sequence (slot = sq % 3): the tile of position sq + 3 can be brought in as soon as
-// the PV of position sq is done, i.e. three PV times before its own turn — a fetch from L2 fits in that.
-// Sequence position sq in [0, Kp * CS).
-struct SeqItem { int t, slot, own, k, r; };     // tile, slot, own?, round of the tile, running index among remote tiles
-__device__ __forceinline__ SeqItem seq_item(int sq, int CS, int c, int Kp) {
-  SeqItem it;
-  int i = 0;
-  if (sq == 0) { it.own = 1; it.k = 0; }
-  else {
-    const int m = sq - 1, blk = 1 + m / CS, pos = m % CS;
-    if (blk < Kp && pos == 0) { it.own = 1; it.k = blk; }
-    else { it.own = 0; it.k = blk - 1; i = blk < Kp ? pos - 1 : pos; }
-  }
-  if (it.own) { it.t = CS * it.k + c; it.r = 0; }
-  else {
-    const int d = i < c ? i : i + 1;
-    it.t = CS * it.k + d;
-    it.r = it.k * (CS - 1) + i;
-  }
-  it.slot = sq % 3;
-  return it;
-}
-__device__ __forceinline__ int seq_tile(int sq, int CS, int c, int Kp) { return seq_item(sq, CS, c, Kp).t; }
-__device__ __forceinline__ int seq_slot(int sq, int CS, int c, int Kp) { return seq_item(sq, CS, c, Kp).slot; }
-__device__ __forceinline__ int seq_of_own(int k, int CS) { return k == 0 ? 0 : (k - 1) * CS + 1; }   // position of own(k)
 
 struct __align__(8) PairBarriers {
   uint64_t g_full[kGStagesMax], g_empty[kGStagesMax];
   uint64_t v_full[kVStages], v_empty[kVStages];
   uint64_t s_full[2], s_empty[2];
   uint64_t nj_full[2], nj_empty[2];
-  uint64_t p_full[kQSlotsMax], p_pair[kQSlotsMax], own_free[kQSlotsMax], rem_free[kQSlotsMax];
-  uint64_t pub_full;
-  uint32_t pub_count;          // own tiles this CTA's publisher has finished reading out of shared memory (monotonic)
+  uint64_t p_full[kQSlotsMax], slot_free[kQSlotsMax], p_pair[kQSlotsMax], pub_full[kQSlotsMax], own_free[kQSlotsMax];
   uint64_t o_full;
   uint32_t tmem_base;
   float red[8][4];
@@ -130,7 +85,7 @@ struct __align__(8) PairBarriers {
 struct PairCfg {
   static constexpr int GS = kG2Stages;              // Gram ring stages
   static constexpr int GSB = kG2StageBytes;         // bytes per stage
-  static constexpr int QS = 3;                      // P slots, 32 KiB each: one for own tiles, two for remote ones
+  static constexpr int QS = VG_G2_SLOTS;            // P slots, 32 KiB each
   static constexpr int SmemG = 0;
   static constexpr int SmemV = SmemG + GS * GSB;
   static constexpr int SmemP = SmemV + kVStages * kVStageBytes;
@@ -139,7 +94,7 @@ struct PairCfg {
   static constexpr int SmemTotal = SmemBar + static_cast<int>(sizeof(PairBarriers));
   static_assert(SmemTotal <= 232448, "shared memory budget");
   static_assert(SmemV % 1024 == 0 && SmemP % 1024 == 0, "operand tiles need 1024-byte alignment");
-  static_assert(kRing >= 2 && kRing * kQPBytes <= kXchgBytesPerSm, "exchange ring per CTA");
+  static_assert(QS * kQPBytes <= kXchgBytesPerSm, "exchange scratch per SM");
 };
 
 #define VG_PAIR_DECODE_RANGE \
@@ -182,31 +137,21 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  // The hardware cluster is the CTA pair only (so that all 148 SMs can host one: 8-CTA clusters fit 120).  CS
-  // consecutive pairs form a GROUP = 2 row tiles x CS feature slices; the pairs of a group exchange their P tiles and
-  // row sums through global memory (L2) with release/acquire flags.  The persistent grid is resident as a whole
-  // (launch_tc_pair sizes it by cudaOccupancyMaxActiveClusters), so the flag waits always make progress.
-  const int CS = p.cs;                                 // feature slices (pairs) per group
-  const int hh = static_cast<int>(cluster_ctarank());  // 0: leader (row tile I0), 1: peer (row tile I1)
-  const int pair_id = static_cast<int>(blockIdx.x) >> 1;
-  const int c = pair_id % CS;                          // pair index = slice within the group
-  const int vc = pair_id / CS;                         // group index
-  const int n_clusters = (static_cast<int>(gridDim.x) >> 1) / CS;    // groups
-  if (p.started && threadIdx.x == 0) atomicAdd(p.started, 1u);      // resident now (see abi.cu: S_xx launch gate)
-  if (vc >= n_clusters) return;                        // pairs beyond the last whole group have no work
+  const int CS = p.cs;                                 // feature slices per cluster; cluster size = 2 CS
+  const int rank = static_cast<int>(cluster_ctarank());
+  const int c = rank >> 1;                             // pair index = slice within the group
+  const int hh = rank & 1;                             // 0: leader (row tile I0), 1: peer (row tile I1)
+  const int csz = 2 * CS;
   const int ngx = p.gx_end - p.gx_begin;
   const int ngrad = ngx + (p.gy_end - p.gy_begin);
-  constexpr uint16_t pair_mask = 3;
-  uint32_t* const flag_ready = reinterpret_cast<uint32_t*>(p.xchg + kRingBytes);
-  uint32_t* const flag_fetched = flag_ready + kXchgSms;
-  uint32_t* const flag_bar = flag_fetched + kXchgSms;
-  float* const rs_global = reinterpret_cast<float*>(flag_bar + kXchgSms);
-  const int blk_of_pair0 = (vc * CS) << 1;             // blockIdx of the leader of pair 0 of this group
+  const uint16_t pair_mask = static_cast<uint16_t>(3u << (2 * c));
   const int T = p.tiles_x + p.tiles_y;                 // column tiles
   const int K = (T + CS - 1) / CS;                     // rounds of CS column tiles per unit (the tail is padded)
   // ---- stream-K partition: units x K rounds, equal contiguous ranges per cluster
   const int n_units = ((ngrad + 1) / 2) * p.ngroups;   // (row-tile pair, slice group)
   const long long W = static_cast<long long>(n_units) * K;
+  const int n_clusters = static_cast<int>(gridDim.x) / csz;
+  const int vc = static_cast<int>(blockIdx.x) / csz;
   const long long w_begin = W * vc / n_clusters, w_end = W * (vc + 1) / n_clusters;
   // Order of the ranges of this cluster: its FULL units first, every one swept from column round 0, so that all
   // clusters walk the column operand in step (one HBM fetch per Z_J tile serves them all through L2: Z is
@@ -243,12 +188,11 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     }
     for (int s = 0; s < kQSlots; ++s) {
       mbar_init(&bar->p_full[s], 1);
+      mbar_init(&bar->slot_free[s], CS);
       mbar_init(&bar->p_pair[s], 1);
+      mbar_init(&bar->pub_full[s], 1);
       mbar_init(&bar->own_free[s], 1);
-      mbar_init(&bar->rem_free[s], 1);
     }
-    mbar_init(&bar->pub_full, 1);
-    bar->pub_count = 0;
     mbar_init(&bar->o_full, 1);
     fence_barrier_init();
   }
@@ -271,27 +215,16 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
   // ---- pipeline state that persists across the work ranges of this CTA (each warp uses its role's part)
   uint32_t rs = 0, rph = 0;            // ring stage / phase: G ring (warps 8, 11, 9), V ring (warps 12, 10)
   uint32_t kg = 0;                     // Gram tiles of this CTA so far: S / norm buffer kg & 1, parity (kg >> 1) & 1
-  uint32_t pf_mask = 0, rf_mask = 0, of_mask = 0;   // per-slot phase parities of p_full / rem_free / own_free (toggled by
-                                       // roles that wait for EVERY phase of the barrier)
-  uint32_t pub_ph = 0;                 // phase parity of pub_full
-  // a slot that held an OWN tile is also read by the publisher (bulk store to the ring): whoever refills it waits until
-  // the publisher's count has passed that tile (a monotonic counter in shared memory: no phase to lose track of)
-  auto wait_published = [&](uint32_t count) {
-    const volatile uint32_t* pc = &bar->pub_count;
-    uint32_t spins = 0;
-    while (static_cast<int32_t>(*pc - count) < 0) {
-      __nanosleep(20);
-      if (++spins > (VG_SPIN_LIMIT >> 2)) { printf("vgan_b200: publisher timeout block %d\n", blockIdx.x); __trap(); }
-    }
-  };
-  uint32_t seq_base = 0;               // tiles every CTA of the group has published before this range
-  uint32_t part = 0;                   // ranges done: parity of o_full, group barrier count, row-sum buffer
+  uint32_t pf_mask = 0, sf_mask = 0, pub_mask = 0, of_mask = 0;   // per-slot phase parities of p_full / slot_free / pub_full / own_free
+  uint32_t part = 0;                   // parity of o_full
   long long tm0 = 0, tm1 = 0, tm2 = 0, tm3 = 0;      // debug timers (meaning depends on the role)
   const long long t_begin = VG_CLK();
   unsigned long long gt_begin;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt_begin));
+  // resident now: the host makes the S_xx launch wait until every persistent CTA has counted itself in
+  if (p.started && threadIdx.x == 0) atomicAdd(p.started, 1u);
   long long tm_tail = 0;
-#define VG_PAIR_ADVANCE_BASES seq_base += static_cast<uint32_t>(Kp)
+  float* rsx = reinterpret_cast<float*>(smem + kQSmemP);       // [CS][128] row-sum exchange, reuses P slot 0
 
   if (warp >= 8) {
     // ===================== service warps (TMA, MMA issue, P exchange): few registers =====================
@@ -328,8 +261,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
   } else if (warp == 12) {
     // ===================== V producer: half tiles of Z_J[:, this CTA's half of the slice] =====================
     if (my_chunks > 0) {
-      for (int sq = 0; sq < TTp; ++sq) {
-        const int t = seq_tile(sq, CS, c, Kp);
+      for (int t = 0; t < TTp; ++t) {
         const int jt = min(tile0 + t, T - 1);
         for (int h = 0; h < 2; ++h) {
           mbar_wait(&bar->v_empty[rs], rph ^ 1);
@@ -361,79 +293,61 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
       }
     }
   } else if (warp == 13) {
-    // ===================== publisher: this CTA's P tiles -> its ring in global memory (L2), then the ready flag =====
-    // (kept off the epilogue warps).  pub_full[slot] counts only this CTA's own tiles.  Tile number q of this CTA goes
-    // to ring slot q % kRing once every other pair of the group has fetched tile q - kRing (fetched counts one per
-    // reader and tile); the shared-memory copy stays where it is for this pair's own PV.
-    uint32_t* my_ready = flag_ready + blockIdx.x;
-    const uint32_t* my_fetched = flag_fetched + blockIdx.x;
-    uint8_t* ring = p.xchg + static_cast<size_t>(blockIdx.x) * kXchgBytesPerSm;
+    // ===================== publisher: sends this CTA's P tiles to the other slices of its row tile =======
+    // (kept off the epilogue warps).  pub_full[slot] counts only this CTA's own tiles (waiting on p_full would
+    // alias: it advances through the peers' tiles in between, and a parity wait cannot tell phases two apart)
+    uint16_t peers = 0;                                   // the other slices of MY row tile
+    for (int d = 0; d < CS; ++d)
+      if (d != c) peers |= static_cast<uint16_t>(1u << (2 * d + hh));
+    const uint32_t smid = sm_id();
+    if (smid >= static_cast<uint32_t>(kXchgSms)) __trap();
+    uint8_t* xbase = p.xchg + static_cast<size_t>(smid) * kXchgBytesPerSm;
     for (int k = 0; k < Kp; ++k) {
       const int t = CS * k + c;
-      VG_MARK(13, 100 + t);
-      mbar_wait(&bar->pub_full, pub_ph);
-      pub_ph ^= 1u;
-      VG_MARK(13, 200 + t);
-      if (lane == 0) {
-        if (CS > 1) {
-          const uint32_t q = seq_base + static_cast<uint32_t>(k);
-          if (q >= static_cast<uint32_t>(kRing))
-            spin_until_ge(my_fetched, (q - kRing + 1) * static_cast<uint32_t>(CS - 1));
-          const int slot = seq_of_own(k, CS) % kQSlots;
-          bulk_store_global(ring + (q % kRing) * kQPBytes, smem_u32(smem + kQSmemP + slot * kQPBytes), pbytes);
-          bulk_commit_wait_all();                    // the tile is in global memory
-          fence_proxy_async_all();
-          st_release_gpu(my_ready, q + 1);
+      const int slot = t % kQSlots;
+      mbar_wait(&bar->pub_full[slot], (pub_mask >> slot) & 1);
+      pub_mask ^= 1u << slot;
+      if (lane == 0 && peers) {
+        const uint32_t src = smem_u32(smem + kQSmemP + slot * kQPBytes);
+        if (dbg_flags & 8) {
+          // DSMEM route: one bulk copy per peer (~12 B/clk per SM: 3 x 32 KiB take ~8000 cycles)
+          if (t >= kQSlots) mbar_wait(&bar->slot_free[slot], (sf_mask >> slot) & 1);
+          for (int d = 0; d < CS; ++d)
+            if (d != c) {
+              const uint32_t peer = static_cast<uint32_t>(2 * d + hh);
+              bulk_copy_to_peer(mapa_u32(src, peer), src, pbytes, mapa_u32(smem_u32(&bar->p_full[slot]), peer));
+            }
+        } else {
+          // L2 route: bulk store to this SM's scratch slot, then ONE multicast bulk load into the same slot of
+          // every peer.  The scratch slot is free for the same reason the shared-memory slot is (slot_free).
+          // The store to L2 does not wait for the receivers: the tile was parked as soon as THIS pair's PV(t - slots)
+          // had finished (own_free).  Only the multicast load into the peers' slots waits until every pair is done
+          // with the slot's previous tile, so store + commit are off the slot loop's critical path.
+          uint8_t* g = xbase + slot * kQPBytes;
+          bulk_store_global(g, src, pbytes);
+          bulk_commit_wait_all();
+          if (t >= kQSlots) mbar_wait(&bar->slot_free[slot], (sf_mask >> slot) & 1);   // every CTA finished PV(t - kQSlots)
+          bulk_load_multicast(src, g, pbytes, smem_u32(&bar->p_full[slot]), peers);
         }
-        *reinterpret_cast<volatile uint32_t*>(&bar->pub_count) = seq_base + static_cast<uint32_t>(k) + 1u;   // slot no longer read
       }
-      VG_MARK(13, 300 + t);
+      if (t >= kQSlots) sf_mask ^= 1u << slot;
       __syncwarp();
     }
-  } else if (warp == 15) {
-    // ===================== fetcher: the other pairs' P tiles of MY row tile, ring -> shared-memory slot ==========
-    // In tile order.  A slot is free once this pair's PV of the tile that used it before has completed (rem_free,
-    // committed to both CTAs of the pair); the tile is there once its writer's ready count says so.
-    if (lane == 0 && CS > 1) {
-      for (int sq = 0; sq < TTp; ++sq) {
-        const SeqItem it = seq_item(sq, CS, c, Kp);
-        if (it.own) continue;
-        const int t = it.t, slot = it.slot, d = t % CS, k = it.k;
-        VG_MARK(15, 100 + t);
-        if (sq >= kQSlots) {       // this pair finished the PV of the tile that was in the slot
-          mbar_wait(&bar->rem_free[slot], (rf_mask >> slot) & 1);
-          rf_mask ^= 1u << slot;
-          const SeqItem prev = seq_item(sq - kQSlots, CS, c, Kp);
-          if (prev.own) wait_published(seq_base + static_cast<uint32_t>(prev.k) + 1u);
-        }
-        const int wblk = blk_of_pair0 + 2 * d + hh;   // the writer: pair d of this group, same row tile
-        const uint32_t q = seq_base + static_cast<uint32_t>(k);
-        VG_MARK(15, 200 + t);
-        spin_until_ge(flag_ready + wblk, q + 1);
-        VG_MARK(15, 300 + t);
-        fence_proxy_async_all();
-        mbar_arrive_expect_tx(&bar->p_full[slot], pbytes);
-        bulk_load_1d(smem + kQSmemP + slot * kQPBytes,
-                     p.xchg + static_cast<size_t>(wblk) * kXchgBytesPerSm + (q % kRing) * kQPBytes, pbytes,
-                     &bar->p_full[slot]);
-        // not waited for here (the next load goes out at once): the warp that consumes p_full in order — the PV warp
-        // on the leader, the forwarder on the peer — acknowledges the tile to its writer (fetched)
-        VG_MARK(15, 400 + t);
-      }
-    }
-    __syncwarp();
   } else if (warp == 9 && hh == 1) {
     // ===================== peer CTA: forward "my P tile t is in place" to the leader's PV warp =========
-    // (own tiles are parked by the epilogue, the other pairs' tiles land by the fetcher's bulk loads)
-    const uint32_t pp0 = mapa_u32(smem_u32(&bar->p_pair[0]), 0u);
-    for (int sq = 0; sq < TTp; ++sq) {
-      const int t = seq_tile(sq, CS, c, Kp);
-      const int slot = seq_slot(sq, CS, c, Kp);
+    // P tiles written by another slice land by bulk copy: the RECEIVER arms its own barrier (no remote
+    // arrive): the first kQSlots tiles of the range here, tile t + kQSlots right after the wait for tile t
+    if (lane == 0)
+      for (int t = 0; t < kQSlots && t < TTp; ++t)
+        if (t % CS != c) mbar_arrive_expect_tx(&bar->p_full[t % kQSlots], pbytes);
+    const uint32_t pp0 = mapa_u32(smem_u32(&bar->p_pair[0]), static_cast<uint32_t>(rank - 1));
+    for (int t = 0; t < TTp; ++t) {
+      const int slot = t % kQSlots;
       mbar_wait(&bar->p_full[slot], (pf_mask >> slot) & 1);
       pf_mask ^= 1u << slot;
       if (lane == 0) {
+        if (t + kQSlots < TTp && (t + kQSlots) % CS != c) mbar_arrive_expect_tx(&bar->p_full[slot], pbytes);
         mbar_remote_arrive(pp0 + slot * 8);
-        if (t % CS != c) red_relaxed_gpu_add(flag_fetched + blk_of_pair0 + 2 * (t % CS) + hh, 1u);   // landed: ring slot reusable
       }
       __syncwarp();
     }
@@ -486,17 +400,17 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     const uint32_t idesc_pv = make_idesc_bf16(2 * kTile, slice_chunks * kChunk, 0, 1);
     const uint32_t v_lo0 = (smem_u32(smem + kQSmemV) & 0x3FFFFu) >> 4;
     const uint32_t p_lo0 = (smem_u32(smem + kQSmemP) & 0x3FFFFu) >> 4;
-    for (int sq = 0; sq < TTp; ++sq) {
-      const SeqItem it = seq_item(sq, CS, c, Kp);
-      const int t = it.t, slot = it.slot;
+    if (lane == 0)                                       // arm the first remote tiles of the range (see warp 9, peer)
+      for (int t = 0; t < kQSlots && t < TTp; ++t)
+        if (t % CS != c) mbar_arrive_expect_tx(&bar->p_full[t % kQSlots], pbytes);
+    for (int t = 0; t < TTp; ++t) {
+      const int slot = t % kQSlots;
       {
         const long long t0 = VG_CLK();
-        VG_MARK(10, 100 + t);
         mbar_wait(&bar->p_full[slot], (pf_mask >> slot) & 1);   // my P(I0, t)
-        VG_MARK(10, 200 + t);
-        if (lane == 0 && !it.own) red_relaxed_gpu_add(flag_fetched + blk_of_pair0 + 2 * (t % CS) + hh, 1u);
+        if (lane == 0 && t + kQSlots < TTp && (t + kQSlots) % CS != c)
+          mbar_arrive_expect_tx(&bar->p_full[slot], pbytes);    // arm the slot for its next (remote) tile
         mbar_wait(&bar->p_pair[slot], (pf_mask >> slot) & 1);   // the peer's P(I1, t)
-        VG_MARK(10, 300 + t);
         tm2 += VG_CLK() - t0;
       }
       pf_mask ^= 1u << slot;
@@ -517,7 +431,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
             for (int j = 0; j < 4; ++j) {
               const uint64_t adesc = (static_cast<uint64_t>(desc_hi) << 32) | (pa_lo + j * 2);
               const uint64_t bdesc = (static_cast<uint64_t>(desc_hi) << 32) | (v_lo + j * (2048 >> 4)) | lbo_v;
-              umma_bf16_ss_2cta(tmem_o, adesc, bdesc, idesc_pv, (sq | h | j) != 0);
+              umma_bf16_ss_2cta(tmem_o, adesc, bdesc, idesc_pv, (t | h | j) != 0);
             }
             umma_commit_2cta_mc(&bar->v_empty[rs], pair_mask);
           }
@@ -525,22 +439,21 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
           if (++rs == kVStages) { rs = 0; rph ^= 1; }
         }
       }
-      // both CTAs of the pair are done with the slot once this PV has completed: whoever fills it with the tile of
-      // position sq + 3 waits for that — the epilogue for an own tile (own_free), the fetcher for another pair's
-      // (rem_free).  Two barriers per slot, so that every waiter sees EVERY phase of its barrier (a parity wait cannot
-      // tell phases two apart).
-      if (sq + kQSlots < TTp && elect_one()) {
-        const SeqItem nxt = seq_item(sq + kQSlots, CS, c, Kp);
-        umma_commit_2cta_mc(nxt.own ? &bar->own_free[slot] : &bar->rem_free[slot], pair_mask);
+      // both CTAs of the pair are done with slot: tell the two writers (rows I0 and I1) of tile t + kQSlots
+      if (t + kQSlots < TTp && elect_one()) {
+        umma_commit_2cta_mc(&bar->slot_free[slot], static_cast<uint16_t>(3u << (2 * ((t + kQSlots) % CS))));
+        // the next tile of this slot is written by this pair: its epilogues may park it once OUR PV(t) is done
+        if ((t + kQSlots) % CS == c) umma_commit_2cta_mc(&bar->own_free[slot], pair_mask);
       }
       __syncwarp();
     }
     if (elect_one()) umma_commit_2cta_mc(&bar->o_full, pair_mask);
     __syncwarp();
   }
-    VG_PAIR_ADVANCE_BASES;
     tc_fence_before();
-    cluster_sync_all();      // the pair-wide barrier at the end of the range (see the epilogue warps below)
+    cluster_sync_all();      // #1, #2, #3 of the epilogue warps below
+    cluster_sync_all();
+    cluster_sync_all();
     }
   } else {
     // ===================== epilogue warps: this CTA's own column tiles (register-hungry) =====================
@@ -580,7 +493,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
       tmem_ld_wait();
       tc_fence_before();
       mbar_arrive(&bar->s_empty[b]);
-      if (hh == 1) mbar_remote_arrive(mapa_u32(smem_u32(&bar->s_empty[b]), 0u));
+      if (hh == 1) mbar_remote_arrive(mapa_u32(smem_u32(&bar->s_empty[b]), static_cast<uint32_t>(rank - 1)));
     };
     auto compute = [&](int k, uint32_t b, const uint32_t (&va)[32], const uint32_t (&vb)[32], uint4 (&pk)[8]) {
       const long long tq = VG_CLK();
@@ -604,15 +517,11 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     };
     auto park = [&](int k, const uint4 (&pk)[8]) {
       long long tq = VG_CLK();
-      const int t = CS * k + c;                          // tile index within the range
-      const int sq = seq_of_own(k, CS);                  // position in the consumption order -> slot
-      const int slot = sq % kQSlots;
-      VG_MARK(warp, 100 + t);
-      if (sq >= kQSlots) {
-        mbar_wait(&bar->own_free[slot], (of_mask >> slot) & 1);    // this pair's PV of position sq - 3 has completed
+      const int t = CS * k + c;                          // tile index within the range (slot protocol)
+      const int slot = t % kQSlots;
+      if (t >= kQSlots) {
+        mbar_wait(&bar->own_free[slot], (of_mask >> slot) & 1);    // this pair finished PV(t - kQSlots)
         of_mask ^= 1u << slot;
-        const SeqItem prev = seq_item(sq - kQSlots, CS, c, Kp);
-        if (prev.own) wait_published(seq_base + static_cast<uint32_t>(prev.k) + 1u);
       }
       tm2 += VG_CLK() - tq; tq = VG_CLK();
       uint8_t* p_slot = smem + kQSmemP + slot * kQPBytes;
@@ -624,9 +533,8 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
       asm volatile("bar.sync 1, 256;" ::: "memory");
       if (threadIdx.x == 0) {
         mbar_arrive(&bar->p_full[slot]);     // own PV warp / forwarder
-        mbar_arrive(&bar->pub_full);         // publisher warp
+        mbar_arrive(&bar->pub_full[slot]);   // publisher warp
       }
-      VG_MARK(warp, 200 + t);
       tm3 += VG_CLK() - tq;
     };
     {
@@ -664,42 +572,29 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     tc_fence_after();
     }
 
-    // ===================== group-wide row sums of P, then the gradient rows of this range =====================
-    // Every CTA of the group that works on MY row tile (one per pair, same hh) holds the row sums of its own column
-    // tiles: written to global memory, one arrival per CTA on the (group, hh) counter, then all CS parts are read back.
-    // Two buffers alternate with the range parity: a CTA can only be one range ahead of the slowest reader.
+    // ===================== cluster-wide row sums of P, then the gradient rows of this range =====================
     const long long tq_tail = VG_CLK();
-    VG_MARK(warp, 900);
-    asm volatile("bar.sync 1, 256;" ::: "memory");     // both column halves of the row sums are in nj_smem
-    float* rs_mine = rs_global + (static_cast<size_t>(part & 1u) * kXchgSms + blockIdx.x) * kTile;
+    tc_fence_before();
+    cluster_sync_all();      // #1: no CTA of the cluster reads a P slot any more
     if (warp < 4) {
       const int row = warp * 32 + lane;
-      __stcg(rs_mine + row, nj_smem[row] + nj_smem[kTile + row]);
-      __threadfence();
+      const float tot = nj_smem[row] + nj_smem[kTile + row];     // both column halves of this CTA's tiles
+      const uint32_t a = smem_u32(rsx + c * kTile + row);
+      for (int d = 0; d < CS; ++d) st_cluster_f32(mapa_u32(a, static_cast<uint32_t>(2 * d + hh)), tot);
     }
-    asm volatile("bar.sync 1, 256;" ::: "memory");
-    if (threadIdx.x == 0) {
-      uint32_t* cnt = flag_bar + 2 * vc + hh;
-      red_release_gpu_add(cnt, 1u);
-      spin_until_ge(cnt, static_cast<uint32_t>(CS) * (part + 1u));
-    }
-    asm volatile("bar.sync 1, 256;" ::: "memory");
-    {
+    cluster_sync_all();      // #2: all partial row sums have arrived
+    if (warp < 8) {
       const int q = warp & 3, g = warp >> 2;
       const int row = q * 32 + lane;
       float rtot = 0.f;
-      for (int d = 0; d < CS; ++d)
-        rtot += __ldcg(rs_global + (static_cast<size_t>(part & 1u) * kXchgSms + blk_of_pair0 + 2 * d + hh) * kTile + row);
+      for (int d = 0; d < CS; ++d) rtot += rsx[d * kTile + row];
       tc_fence_after();
       if (!dup)
         write_grad_rows(p, tmem_o, static_cast<uint32_t>(q * 32) << 16, g, row, ti, row_is_x, slice, slice_chunks,
                         rtot, partial, r0 == 0);
     }
-    VG_MARK(warp, 950);
-    VG_PAIR_ADVANCE_BASES;
     tc_fence_before();
-    cluster_sync_all();      // pair-wide: O, the norm buffers and the P slots may be reused by the next range
-    VG_MARK(warp, 999);
+    cluster_sync_all();      // #3: O, the norm buffers and P slot 0 may be reused by the next range
     tm_tail += VG_CLK() - tq_tail;
     }
   }
@@ -730,65 +625,39 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
   if (warp == 11) tmem_dealloc_2cta(tmem, 512);
 }
 
-// Persistent grid of the gradient kernel: as many CTA pairs as the device holds at once (74 on a B200: every SM),
-// rounded down to whole groups of p.cs pairs, never more groups than (row-tile pair, slice group) units.
-int pair_grid_ctas(vgan_b200_ctx* ctx, const TcParams& p, int ladder) {
-  const int ngrad = (p.gx_end - p.gx_begin) + (p.gy_end - p.gy_begin);
-  if (ngrad <= 0) return 0;
-  auto kern = ladder ? mmd2_tc_pair_kernel<true> : mmd2_tc_pair_kernel<false>;
-  int& npairs = ctx->resident_clusters[2];
-  if (npairs == 0) {
-    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, PairCfg::SmemTotal) != cudaSuccess) return -1;
-    cudaLaunchConfig_t cfg{};
-    cfg.blockDim = dim3(kQThreads);
-    cfg.dynamicSmemBytes = PairCfg::SmemTotal;
-    cfg.gridDim = dim3(2 * 128);
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = 2;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    if (cudaOccupancyMaxActiveClusters(&npairs, kern, &cfg) != cudaSuccess) return -1;
-    if (npairs < 1) npairs = 1;
-  }
-  const int n_units = ((ngrad + 1) / 2) * p.ngroups;
-  int groups = npairs / p.cs;
-  if (groups > kXchgSms / (2 * p.cs)) groups = kXchgSms / (2 * p.cs);            // flags / rings are indexed by blockIdx
-  if (p.max_clusters > 0 && p.max_clusters < groups) groups = p.max_clusters;    // vgan_b200_set_cluster_limit
-  if (groups > n_units) groups = n_units;
-  if (groups < 1) return -2;          // the device cannot hold one whole group at once: the flag protocol needs that
-  return groups * p.cs * 2;
-}
-
 int launch_tc_pair(vgan_b200_ctx* ctx, const TcParams& p, const CUtensorMap& map, const CUtensorMap& map64,
                    const CUtensorMap& mapV64, int ladder, cudaStream_t st, int* resident_ctas) {
   if (resident_ctas) *resident_ctas = 0;
-  const int grid = pair_grid_ctas(ctx, p, ladder);
-  if (grid == 0) return VGAN_B200_OK;
-  if (grid < 0) {
-    set_error(grid == -2 ? "mmd2_fwd_bwd: the device cannot keep one group of %d CTA pairs resident" :
-                           "mmd2_fwd_bwd: occupancy query of the gradient kernel failed", p.cs);
-    return VGAN_B200_ERR_CUDA;
-  }
+  const int ngrad = (p.gx_end - p.gx_begin) + (p.gy_end - p.gy_begin);
+  if (ngrad <= 0) return VGAN_B200_OK;
   auto kern = ladder ? mmd2_tc_pair_kernel<true> : mmd2_tc_pair_kernel<false>;
-  VG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, PairCfg::SmemTotal));
-  // ready / fetched / barrier counters start every launch at zero
-  VG_CUDA_CHECK(cudaMemsetAsync(p.xchg + kRingBytes, 0, kPairFlagBytes, st));
+  const int smem_bytes = PairCfg::SmemTotal;
+  VG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+  const int n_units = ((ngrad + 1) / 2) * p.ngroups;
   cudaLaunchConfig_t cfg{};
   cfg.blockDim = dim3(kQThreads);
-  cfg.dynamicSmemBytes = PairCfg::SmemTotal;
+  cfg.dynamicSmemBytes = smem_bytes;
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.x = static_cast<unsigned>(2 * p.cs);
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  cfg.gridDim = dim3(static_cast<unsigned>(grid));
-  if (resident_ctas) *resident_ctas = grid;
+  // persistent grid: as many clusters as can be resident at once (cached per cluster size in the context; the same
+  // for both instantiations: same block size and shared memory)
+  int& ncl = ctx->resident_clusters[2 * p.cs];
+  if (ncl == 0) {
+    cfg.gridDim = dim3(static_cast<unsigned>(2 * p.cs * 64));
+    VG_CUDA_CHECK(cudaOccupancyMaxActiveClusters(&ncl, kern, &cfg));
+    if (ncl < 1) ncl = 1;
+  }
+  int cap = ncl;
+  if (p.max_clusters > 0 && p.max_clusters < cap) cap = p.max_clusters;   // vgan_b200_set_cluster_limit
+  const int n_clusters = cap < n_units ? cap : n_units;
+  cfg.gridDim = dim3(static_cast<unsigned>(n_clusters * 2 * p.cs));
+  if (resident_ctas) *resident_ctas = (n_clusters < ncl ? n_clusters : ncl) * 2 * p.cs;
   VG_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, map, map64, mapV64, p));
   count_launch();
   return VGAN_B200_OK;
