@@ -333,7 +333,10 @@ static int run_tc(vgan_b200_ctx* ctx, const vgan_b200_layout_t& L, void* ws, con
     return VGAN_B200_OK;
   };
   if (!split) return run_pass(p, true);
-  // BF16X3: O = P_hi V_hi + P_hi V_lo + P_lo V_hi, one pass each into zeroed outputs; pass 1 also produces the kernel
+  // BF16X3, D_p <= 256: ONE pass — the K = 3 D_p Gram once per column tile, both bf16(P) and P - bf16(P) parked, the
+  // three gradient parts issued back to back (mmd_tc.cu, TcCfg<true>)
+  if (!multi_slice) return launch_tc(p, map, mapB, mapV, ladder, st, 1);
+  // BF16X3, D_p > 256: O = P_hi V_hi + P_hi V_lo + P_lo V_hi, one pass each into zeroed outputs; pass 1 also produces the kernel
   // sums, the rowsum(P) z_i term and the common-mode remainder; the S_xx units run once beside it
   if (p.pv) {
     if (ye > row_begin)

@@ -145,7 +145,7 @@ int get_tmap_bf16_2d(vgan_b200_ctx* ctx, CUtensorMap* map, const void* base, uin
 // map = row operand (A), mapB = column operand of the Gram, mapV = value operand of the gradient GEMM; the three are
 // the same array on the plain bf16 path and differ with split operands (BF16X3, see prologue.cu)
 int launch_tc(const TcParams& p, const CUtensorMap& map, const CUtensorMap& mapB, const CUtensorMap& mapV, int ladder,
-              cudaStream_t st);
+              cudaStream_t st, int split = 0);   // split: BF16X3 in one pass (D_p <= 256)
 int launch_xx(vgan_b200_ctx* ctx, const TcParams& p, const CUtensorMap& map, const CUtensorMap& map256, int ladder,
               cudaStream_t st, int max_ctas = 0);
 int launch_tc_pair(vgan_b200_ctx* ctx, const TcParams& p, const CUtensorMap& map, const CUtensorMap& mapB64,

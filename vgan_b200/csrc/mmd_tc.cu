@@ -24,7 +24,7 @@
 
 namespace vg {
 
-constexpr int kStages = 5;
+constexpr int kStagesMax = 5;
 constexpr int kStageBytes = 2 * kChunkBytes;   // Gram: Z_I chunk + Z_J chunk;  PV: two V chunks (128 features)
 constexpr int kPBytes = 2 * kChunkBytes;                     // 128 x 128 bf16
 constexpr int kNumEpiWarps = 16;
@@ -34,7 +34,7 @@ constexpr int kWarpTma = kNumEpiWarps, kWarpMma = kNumEpiWarps + 1, kWarpNorms =
               kWarpAlloc = kNumEpiWarps + 3;
 
 struct __align__(8) TcBarriers {
-  uint64_t ring_full[kStages], ring_empty[kStages];
+  uint64_t ring_full[kStagesMax], ring_empty[kStagesMax];
   uint64_t s_full[2], s_empty[2];
   uint64_t nj_full[2];
   uint64_t p_full[2], p_empty[2];
@@ -43,12 +43,23 @@ struct __align__(8) TcBarriers {
   float red[kNumEpiWarps][2];
 };
 
-constexpr int kSmemRing = 0;
-constexpr int kSmemP = kSmemRing + kStages * kStageBytes;
-constexpr int kSmemNj = kSmemP + 2 * kPBytes;
-constexpr int kSmemBar = kSmemNj + 2 * kTile * 4;
-constexpr int kSmemTotal = kSmemBar + static_cast<int>(sizeof(TcBarriers));
-static_assert(kSmemTotal <= 232448, "shared memory budget");
+// SPLIT (fp32-class results from split bf16 operands z = hi + lo, BF16X3) in ONE pass: the K = 3 D_p Gram
+// [hi|hi|lo] x [hi|lo|hi] is computed once per column tile, the epilogue parks BOTH bf16(P) and the remainder
+// P - bf16(P), and the gradient GEMM issues its three parts O += P_hi V_hi + P_hi V_lo + P_lo V_hi back to back
+// (three passes of the plain kernel recomputed the Gram and the whole epilogue three times: 3x the time where the
+// epilogue is the bound, i.e. at every width this kernel serves).  Four P buffers instead of two, three ring stages
+// instead of five.
+template <bool SPLIT> struct TcCfg {
+  static constexpr int Stages = SPLIT ? 3 : 5;
+  static constexpr int PBufs = SPLIT ? 4 : 2;        // [hi 0, hi 1] (+ [lo 0, lo 1])
+  static constexpr int PvParts = SPLIT ? 3 : 1;
+  static constexpr int SmemRing = 0;
+  static constexpr int SmemP = SmemRing + Stages * kStageBytes;
+  static constexpr int SmemNj = SmemP + PBufs * kPBytes;
+  static constexpr int SmemBar = SmemNj + 2 * kTile * 4;
+  static constexpr int SmemTotal = SmemBar + static_cast<int>(sizeof(TcBarriers));
+  static_assert(SmemTotal <= 232448, "shared memory budget");
+};
 
 struct Unit {
   int ti;        // stacked row tile
@@ -87,12 +98,15 @@ __device__ __forceinline__ Unit decode_unit(const TcParams& p) {
   return u;
 }
 
-template <bool LADDER>
+template <bool LADDER, bool SPLIT>
 __global__ void __launch_bounds__(kThreads, 1)
 mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__ CUtensorMap zmapB,
                const __grid_constant__ CUtensorMap zmapV, const TcParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];   // SWIZZLE_128B tiles need 1024-byte alignment
   if ((smem_u32(smem) & 1023u) != 0) __trap();
+  using Cfg = TcCfg<SPLIT>;
+  constexpr int kStages = Cfg::Stages, kSmemRing = Cfg::SmemRing, kSmemP = Cfg::SmemP, kSmemNj = Cfg::SmemNj,
+                kSmemBar = Cfg::SmemBar, kPvParts = Cfg::PvParts;
   TcBarriers* bar = reinterpret_cast<TcBarriers*>(smem + kSmemBar);
   float* nj_smem = reinterpret_cast<float*>(smem + kSmemNj);
 
@@ -155,15 +169,19 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__
         }
         if (u.pv && n >= 1) {
           const int jt = u.j_begin + n - 1;
-          for (int h = 0; h < pv_stages; ++h) {
-            const int nch = min(2, slice_chunks - 2 * h);
-            mbar_wait(&bar->ring_empty[s], ph ^ 1);
-            uint8_t* dst = smem + kSmemRing + s * kStageBytes;
-            mbar_arrive_expect_tx(&bar->ring_full[s], nch * kChunkBytes);
-            for (int c = 0; c < nch; ++c)
-              tma_load_2d(dst + c * kChunkBytes, &zmapV, &bar->ring_full[s],
-                          (p.v_chunk0 + u.slice * p.slice_chunks + 2 * h + c) * kChunk, jt * kTile);
-            if (++s == kStages) { s = 0; ph ^= 1; }
+          for (int part = 0; part < kPvParts; ++part) {
+            // V operand of this part: the hi block (chunk 0) or the lo block (chunk 2 kchunks) of the row-operand array
+            const int vbase = SPLIT ? (part == 1 ? 2 * p.kchunks : 0) : p.v_chunk0;
+            for (int h = 0; h < pv_stages; ++h) {
+              const int nch = min(2, slice_chunks - 2 * h);
+              mbar_wait(&bar->ring_empty[s], ph ^ 1);
+              uint8_t* dst = smem + kSmemRing + s * kStageBytes;
+              mbar_arrive_expect_tx(&bar->ring_full[s], nch * kChunkBytes);
+              for (int c = 0; c < nch; ++c)
+                tma_load_2d(dst + c * kChunkBytes, &zmapV, &bar->ring_full[s],
+                            (vbase + u.slice * p.slice_chunks + 2 * h + c) * kChunk, jt * kTile);
+              if (++s == kStages) { s = 0; ph ^= 1; }
+            }
           }
         }
       }
@@ -224,25 +242,28 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__
         const int m = n - 1, pb = m & 1;
         mbar_wait(&bar->p_full[pb], (m >> 1) & 1);
         tc_fence_after();
-        const uint32_t p_lo = p_lo0 + pb * (kPBytes >> 4);
-        for (int h = 0; h < pv_stages; ++h) {
-          const int nch = min(2, slice_chunks - 2 * h);
-          const uint32_t idesc_pv = make_idesc_bf16(kTile, nch * kChunk, 0, 1);
-          mbar_wait(&bar->ring_full[s], ph);
-          tc_fence_after();
-          const uint32_t v_lo = ring_lo + s * (kStageBytes >> 4);
-          if (elect_one()) {
+        for (int part = 0; part < kPvParts; ++part) {
+          // A operand: bf16(P) (parts 0, 1) or the remainder tile (part 2: buffers 2, 3)
+          const uint32_t p_lo = p_lo0 + (pb + (part == 2 ? 2 : 0)) * (kPBytes >> 4);
+          for (int h = 0; h < pv_stages; ++h) {
+            const int nch = min(2, slice_chunks - 2 * h);
+            const uint32_t idesc_pv = make_idesc_bf16(kTile, nch * kChunk, 0, 1);
+            mbar_wait(&bar->ring_full[s], ph);
+            tc_fence_after();
+            const uint32_t v_lo = ring_lo + s * (kStageBytes >> 4);
+            if (elect_one()) {
 #pragma unroll
-            for (int kk = 0; kk < kTile / 16; ++kk) {
-              const uint64_t adesc = (static_cast<uint64_t>(desc_hi) << 32) |
-                                     (p_lo + (kk >> 2) * (kChunkBytes >> 4) + (kk & 3) * 2);
-              const uint64_t bdesc = (static_cast<uint64_t>(desc_hi) << 32) | (v_lo + kk * (2048 >> 4)) | lbo_v;
-              umma_bf16_ss(tmem_o + h * 2 * kChunk, adesc, bdesc, idesc_pv, (m | kk) != 0);
+              for (int kk = 0; kk < kTile / 16; ++kk) {
+                const uint64_t adesc = (static_cast<uint64_t>(desc_hi) << 32) |
+                                       (p_lo + (kk >> 2) * (kChunkBytes >> 4) + (kk & 3) * 2);
+                const uint64_t bdesc = (static_cast<uint64_t>(desc_hi) << 32) | (v_lo + kk * (2048 >> 4)) | lbo_v;
+                umma_bf16_ss(tmem_o + h * 2 * kChunk, adesc, bdesc, idesc_pv, (m | part | kk) != 0);
+              }
+              umma_commit(&bar->ring_empty[s]);
             }
-            umma_commit(&bar->ring_empty[s]);
+            __syncwarp();
+            if (++s == kStages) { s = 0; ph ^= 1; }
           }
-          __syncwarp();
-          if (++s == kStages) { s = 0; ph ^= 1; }
         }
         if (elect_one()) umma_commit(&bar->p_empty[pb]);
         __syncwarp();
@@ -286,14 +307,19 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__
       uint8_t* p_row = smem + kSmemP + b * kPBytes + (g >> 1) * kChunkBytes + row * 128;
       const float* njp = nj_smem + b * kTile + g * 32;
       float ksum = 0.f;
-      uint4 pk[4];
+      uint4 pk[4], pk_lo[4];
       epi_half_tile<LADDER>(tmem + lane_addr + b * kTile + g * 32, njp, ni, m2c0, cf, ratio, p.n_scales, ksum, rsum, pk,
-                            p.p_lo != 0, col_is_x ? cw0_x : cw0_y);
+                            p.p_lo != 0, col_is_x ? cw0_x : cw0_y, SPLIT ? pk_lo : nullptr);
       if (u.pv) {
         mbar_wait(&bar->p_empty[b], ((n >> 1) & 1) ^ 1);   // PV(n-2) done with P[b]
 #pragma unroll
         for (int i = 0; i < 4; ++i)                          // 128B-swizzled K-major A operand
           *reinterpret_cast<uint4*>(p_row + ((((g & 1) * 4 + i) ^ (row & 7)) << 4)) = pk[i];
+        if constexpr (SPLIT) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i)                        // the remainder tile, two buffers further on
+            *reinterpret_cast<uint4*>(p_row + 2 * kPBytes + ((((g & 1) * 4 + i) ^ (row & 7)) << 4)) = pk_lo[i];
+        }
       }
       tc_fence_before();
       mbar_arrive(&bar->s_empty[b]);
@@ -348,13 +374,20 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__
 }
 
 int launch_tc(const TcParams& p, const CUtensorMap& map, const CUtensorMap& mapB, const CUtensorMap& mapV, int ladder,
-              cudaStream_t st) {
+              cudaStream_t st, int split) {
   const int ngrad = (p.gx_end - p.gx_begin) + (p.gy_end - p.gy_begin);
   const int grid = ngrad * p.nslices + p.n_xx_units;
   if (grid <= 0) return VGAN_B200_OK;
-  auto kern = ladder ? mmd2_tc_kernel<true> : mmd2_tc_kernel<false>;
-  VG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
-  kern<<<grid, kThreads, kSmemTotal, st>>>(map, mapB, mapV, p); count_launch();
+  if (split) {
+    auto kern = ladder ? mmd2_tc_kernel<true, true> : mmd2_tc_kernel<false, true>;
+    VG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg<true>::SmemTotal));
+    kern<<<grid, kThreads, TcCfg<true>::SmemTotal, st>>>(map, mapB, mapV, p);
+  } else {
+    auto kern = ladder ? mmd2_tc_kernel<true, false> : mmd2_tc_kernel<false, false>;
+    VG_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg<false>::SmemTotal));
+    kern<<<grid, kThreads, TcCfg<false>::SmemTotal, st>>>(map, mapB, mapV, p);
+  }
+  count_launch();
   VG_CUDA_CHECK(cudaGetLastError());
   return VGAN_B200_OK;
 }

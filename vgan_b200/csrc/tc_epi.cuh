@@ -11,7 +11,8 @@ __device__ __forceinline__ void epi_compute_32(const uint32_t (&v)[32], const fl
                                                     float m2c0, const float (&cf)[VGAN_B200_MAX_SCALES],
                                                     const float (&ratio)[VGAN_B200_MAX_SCALES], int n_scales,
                                                     float& ksum, float& rsum, uint4 (&pk)[4], bool plo = false,
-                                                    float cw0 = 0.f) {
+                                                    float cw0 = 0.f, uint4* pk_lo = nullptr) {
+  // pk_lo != nullptr (single-pass split operands): pk = bf16(P') and pk_lo = bf16(P' - bf16(P')), both tiles at once
   // cw0 = c_j w0: the common-mode level of this (row block, column block) pair.  P' = c_j (w - w0) is what gets rounded
   // to bf16 and multiplied; the closed-form remainder is added back in write_grad_rows.  It rides in the last FMA of
   // the weight sum, so it costs no instruction.
@@ -26,7 +27,7 @@ __device__ __forceinline__ void epi_compute_32(const uint32_t (&v)[32], const fl
       const float4 nja = *reinterpret_cast<const float4*>(njp + c * 8);
       const float4 njb = *reinterpret_cast<const float4*>(njp + c * 8 + 4);
       const uint64_t nj2[4] = {f2_pack(nja.x, nja.y), f2_pack(nja.z, nja.w), f2_pack(njb.x, njb.y), f2_pack(njb.z, njb.w)};
-      uint32_t pw[4];
+      uint32_t pw[4], pl[4];
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
         const uint64_t s2 = f2_pack(__uint_as_float(v[c * 8 + 2 * q]), __uint_as_float(v[c * 8 + 2 * q + 1]));
@@ -44,10 +45,12 @@ __device__ __forceinline__ void epi_compute_32(const uint32_t (&v)[32], const fl
         float w0, w1;
         f2_unpack(w2, w0, w1);
         pw[q] = pack_bf16x2(w0, w1);
-        if (plo)      // split-operand pass 3: the remainder of P after its bf16 rounding
-          pw[q] = pack_bf16x2(w0 - __uint_as_float(pw[q] << 16), w1 - __uint_as_float(pw[q] & 0xffff0000u));
+        const uint32_t rem = pack_bf16x2(w0 - __uint_as_float(pw[q] << 16), w1 - __uint_as_float(pw[q] & 0xffff0000u));
+        if (plo) pw[q] = rem;      // split-operand pass 3: the remainder of P after its bf16 rounding
+        pl[q] = rem;
       }
       pk[c].x = pw[0]; pk[c].y = pw[1]; pk[c].z = pw[2]; pk[c].w = pw[3];
+      if (pk_lo) { pk_lo[c].x = pl[0]; pk_lo[c].y = pl[1]; pk_lo[c].z = pl[2]; pk_lo[c].w = pl[3]; }
     }
     float a, b;
     f2_unpack(ks2, a, b);
@@ -75,14 +78,15 @@ __device__ __forceinline__ void epi_compute_32(const uint32_t (&v)[32], const fl
       w[e] = ww;
       rsum += w[e];
     }
-    uint32_t pw[4];
+    uint32_t pw[4], pl[4];
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       pw[q] = pack_bf16x2(w[2 * q], w[2 * q + 1]);
-      if (plo)
-        pw[q] = pack_bf16x2(w[2 * q] - __uint_as_float(pw[q] << 16), w[2 * q + 1] - __uint_as_float(pw[q] & 0xffff0000u));
+      pl[q] = pack_bf16x2(w[2 * q] - __uint_as_float(pw[q] << 16), w[2 * q + 1] - __uint_as_float(pw[q] & 0xffff0000u));
+      if (plo) pw[q] = pl[q];
     }
     pk[c].x = pw[0]; pk[c].y = pw[1]; pk[c].z = pw[2]; pk[c].w = pw[3];
+    if (pk_lo) { pk_lo[c].x = pl[0]; pk_lo[c].y = pl[1]; pk_lo[c].z = pl[2]; pk_lo[c].w = pl[3]; }
   }
   }
 }
@@ -96,11 +100,11 @@ __device__ __forceinline__ void epi_half_tile(uint32_t taddr, const float* __res
                                               float m2c0, const float (&cf)[VGAN_B200_MAX_SCALES],
                                               const float (&ratio)[VGAN_B200_MAX_SCALES], int n_scales,
                                               float& ksum, float& rsum, uint4 (&pk)[4], bool plo = false,
-                                              float cw0 = 0.f) {
+                                              float cw0 = 0.f, uint4* pk_lo = nullptr) {
   uint32_t v[32];
   tmem_ld_32x32(taddr, v);
   tmem_ld_wait();
-  epi_compute_32<LADDER>(v, njp, ni, m2c0, cf, ratio, n_scales, ksum, rsum, pk, plo, cw0);
+  epi_compute_32<LADDER>(v, njp, ni, m2c0, cf, ratio, n_scales, ksum, rsum, pk, plo, cw0, pk_lo);
 }
 
 // Column sums over the 32 lanes of a warp of 32 per-lane values: lane l returns sum over lanes of v[l].
