@@ -225,6 +225,22 @@ VGAN_B200_API int vgan_b200_subspace_dist(vgan_b200_ctx* ctx, const void* U, int
                                           float threshold, void* scratch, uint8_t* unique_out, long long* counts_out,
                                           int* n_unique, void* stream);
 
+/* vgan_b200_subspace_dist without a scratch argument and without any allocation: no cudaMalloc / cudaFree / allocating
+ * library call happens inside, so it can be used where those are forbidden (under CUDA graph capture, in tight
+ * serving loops, in harnesses that ban them).  NO COUNTERPART IN THE REFERENCE.
+ * The scratch is a static device array of VGAN_B200_SUBSPACE_STATIC_SCRATCH_BYTES (1 MiB) that every GPU
+ * which loads the library holds until the process exits; shapes with
+ * vgan_b200_subspace_scratch_bytes(n, D) > VGAN_B200_SUBSPACE_STATIC_SCRATCH_BYTES are rejected with
+ * VGAN_B200_ERR_ARG (the reference's 500 sampled subspaces fit up to D = 16,704 features; n = 4096 up to D = 1,984).
+ * Inputs and outputs are the caller's, as in vgan_b200_subspace_dist, and the results are identical.  All calls on a
+ * device share the one array, which keeps the previous call's contents (nothing in it needs to start at zero): calls
+ * that overlap on the GPU - different streams, contexts or host threads - RACE on it and must be serialised by the
+ * caller. */
+#define VGAN_B200_SUBSPACE_STATIC_SCRATCH_BYTES (1u << 20)
+VGAN_B200_API int vgan_b200_subspace_dist_static(vgan_b200_ctx* ctx, const void* U, int in_is_bool, int64_t n,
+                                                 int64_t D, float threshold, uint8_t* unique_out,
+                                                 long long* counts_out, int* n_unique, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

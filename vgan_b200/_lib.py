@@ -18,6 +18,7 @@ CSRC = os.path.join(HERE, "csrc")
 
 PREC_BF16, PREC_FP32, CENTER, NEED_DX, LADDER, BF16X3 = 0, 1, 2, 4, 8, 64
 MAX_SCALES = 8
+SUBSPACE_STATIC_SCRATCH_BYTES = 1 << 20      # VGAN_B200_SUBSPACE_STATIC_SCRATCH_BYTES
 
 EXPORTS = [
     "vgan_b200_abi_version", "vgan_b200_last_error", "vgan_b200_create", "vgan_b200_destroy",
@@ -25,7 +26,7 @@ EXPORTS = [
     "vgan_b200_pack", "vgan_b200_mmd2_fwd_bwd", "vgan_b200_finalize", "vgan_b200_mmd2_eval",
     "vgan_b200_upper_softmax", "vgan_b200_upper_softmax_bwd", "vgan_b200_mmd2_matrix",
     "vgan_b200_permutation_scratch_bytes", "vgan_b200_permutation_stats",
-    "vgan_b200_subspace_scratch_bytes", "vgan_b200_subspace_dist",
+    "vgan_b200_subspace_scratch_bytes", "vgan_b200_subspace_dist", "vgan_b200_subspace_dist_static",
 ]
 DEBUG_EXPORTS = ["vgan_b200_debug_tile_sums", "vgan_b200_debug_timeline", "vgan_b200_debug_variant",
                  "vgan_b200_umma_probe", "vgan_b200_pair_probe", "vgan_b200_tma_rate_probe",
@@ -115,6 +116,7 @@ def _declare(L: C.CDLL) -> None:
     L.vgan_b200_permutation_scratch_bytes.argtypes = [i64, C.POINTER(C.c_size_t)]
     L.vgan_b200_permutation_stats.argtypes = [p, p, i64, i64, p, i64, p, p, p]
     L.vgan_b200_subspace_dist.argtypes = [p, p, i, i64, i64, f, p, p, p, p, p]
+    L.vgan_b200_subspace_dist_static.argtypes = [p, p, i, i64, i64, f, p, p, p, p]
     for name in EXPORTS:
         if name != "vgan_b200_last_error":
             getattr(L, name).restype = i

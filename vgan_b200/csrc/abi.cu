@@ -86,6 +86,7 @@ int run_upper_softmax(const float*, int64_t, int64_t, float*, float*, float*, cu
 int run_upper_softmax_bwd(const float*, const float*, const float*, const float*, int64_t, int64_t, float*, cudaStream_t);
 int launch_matrix(const float*, int64_t, int64_t, const float*, int, float, float*, cudaStream_t);
 int run_subspace_dist(const void*, int, int64_t, int64_t, float, void*, uint8_t*, long long*, int*, cudaStream_t);
+int run_subspace_dist_static(const void*, int, int64_t, int64_t, float, uint8_t*, long long*, int*, cudaStream_t);
 size_t perm_scratch_bytes(int64_t n);
 int run_permutation_stats(const float*, int64_t, int64_t, const uint8_t*, int64_t, void*, double*, cudaStream_t);
 int launch_simt_from_abi(const vgan_b200_layout_t& L, void* ws, int64_t row_begin, int64_t row_end, int xx_part,
@@ -590,6 +591,18 @@ int vgan_b200_subspace_dist(vgan_b200_ctx* ctx, const void* U, int in_is_bool, i
   }
   return run_subspace_dist(U, in_is_bool, n, D, threshold, scratch, unique_out, counts_out, n_unique,
                            static_cast<cudaStream_t>(stream));
+}
+
+int vgan_b200_subspace_dist_static(vgan_b200_ctx* ctx, const void* U, int in_is_bool, int64_t n, int64_t D,
+                                   float threshold, uint8_t* unique_out, long long* counts_out, int* n_unique,
+                                   void* stream) {
+  VG_ENTER(ctx);   // makes the context's device current: the static array's address is asked for on that device
+  if (!U || !unique_out || !counts_out || !n_unique || n < 1 || D < 1 || n > 65536) {
+    set_error("subspace_dist_static: null pointer or bad size (1 <= n <= 65536)");
+    return VGAN_B200_ERR_ARG;
+  }
+  return run_subspace_dist_static(U, in_is_bool, n, D, threshold, unique_out, counts_out, n_unique,
+                                  static_cast<cudaStream_t>(stream));
 }
 
 }  // extern "C"
