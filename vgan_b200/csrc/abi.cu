@@ -223,6 +223,7 @@ static int run_tc(vgan_b200_ctx* ctx, const vgan_b200_layout_t& L, void* ws, con
   p.xx_part = xx_part; p.xx_nparts = xx_nparts;
   p.n_scales = L.n_scales;
   p.max_clusters = ctx->cluster_limit;
+  p.v_parts = 1;
   p.Nx = Nx; p.Ny = Ny; p.D = D; p.Dp = L.Dp;
   p.row_begin = row_begin; p.row_end = row_end;
   p.zq = reinterpret_cast<const __nv_bfloat16*>(base + L.off_zq);
@@ -267,7 +268,7 @@ static int run_tc(vgan_b200_ctx* ctx, const vgan_b200_layout_t& L, void* ws, con
 
   // one pass of the tcgen05 kernels over this shard (BF16X3 runs three: see below)
   auto run_pass = [&](TcParams& p, bool zero_outputs) -> int {
-    if (!multi_slice) return launch_tc(p, map, mapB, mapV, ladder, st);
+    if (!multi_slice) return launch_tc(p, map, mapB, mapV, ladder, st, 0, ctx->n_sms);
     // D_p > 256: the slice CTAs of two row tiles run as one thread-block cluster (mmd_tc_pair.cu) and share every
     // P tile; the S_xx-only units (no gradient GEMM) run as their own sums-only kernel (mmd_xx.cu) on a low-priority
     // side stream, the cluster kernel on a high-priority one.  8-CTA clusters occupy 120 of the 148 SMs; the S_xx
@@ -336,9 +337,11 @@ static int run_tc(vgan_b200_ctx* ctx, const vgan_b200_layout_t& L, void* ws, con
   if (!split) return run_pass(p, true);
   // BF16X3, D_p <= 256: ONE pass — the K = 3 D_p Gram once per column tile, both bf16(P) and P - bf16(P) parked, the
   // three gradient parts issued back to back (mmd_tc.cu, TcCfg<true>)
-  if (!multi_slice) return launch_tc(p, map, mapB, mapV, ladder, st, 1);
-  // BF16X3, D_p > 256: O = P_hi V_hi + P_hi V_lo + P_lo V_hi, one pass each into zeroed outputs; pass 1 also produces the kernel
-  // sums, the rowsum(P) z_i term and the common-mode remainder; the S_xx units run once beside it
+  if (!multi_slice) return launch_tc(p, map, mapB, mapV, ladder, st, 1, ctx->n_sms);
+  // BF16X3, D_p > 256: O = P_hi (V_hi + V_lo) + P_lo V_hi in TWO passes into zeroed outputs.  Pass 1 multiplies every
+  // parked P tile with both V blocks (one Gram and one epilogue for two of the three parts) and also produces the
+  // kernel sums, the rowsum(P) z_i term and the common-mode remainder, with the S_xx units beside it; pass 2 parks
+  // the remainder P - bf16(P) against V_hi.  (Three passes until round 2: 214 ms at the bench shape.)
   if (p.pv) {
     if (ye > row_begin)
       VG_CUDA_CHECK(cudaMemsetAsync(dY, 0, static_cast<size_t>(ye - row_begin) * D * sizeof(float), st));
@@ -346,14 +349,12 @@ static int run_tc(vgan_b200_ctx* ctx, const vgan_b200_layout_t& L, void* ws, con
       VG_CUDA_CHECK(cudaMemsetAsync(dX, 0, static_cast<size_t>(xe - row_begin) * D * sizeof(float), st));
   }
   p.pass_flags = kPassAccumulate;
-  p.v_chunk0 = 0; p.p_lo = 0;
+  p.v_chunk0 = 0; p.v_chunk1 = 2 * p.kchunks; p.v_parts = p.pv ? 2 : 1; p.p_lo = 0;
   if (int e = run_pass(p, false)) return e;
   if (!p.pv) return VGAN_B200_OK;
   p.n_xx_units = 0;
   p.pass_flags = kPassAccumulate | kPassNoSums | kPassNoRowsum;
-  p.v_chunk0 = 2 * p.kchunks; p.p_lo = 0;
-  if (int e = run_pass(p, false)) return e;
-  p.v_chunk0 = 0; p.p_lo = 1;
+  p.v_chunk0 = 0; p.v_parts = 1; p.p_lo = 1;
   return run_pass(p, false);
 }
 

@@ -43,6 +43,7 @@ struct TcParams {
   int kchunks;                // Dp / 64 (feature chunks: slices, O columns, V operand)
   int gchunks;                // K chunks of the Gram GEMM: kchunks, or 3 * kchunks with split operands (BF16X3)
   int v_chunk0;               // chunk offset of the V operand inside its array (split: hi block 0, lo block 2 * kchunks)
+  int v_parts, v_chunk1;      // pair kernel: 2 = every P tile multiplies a second V block (at v_chunk1) as well
   int p_lo;                   // 1: the P operand is the bf16 remainder P - bf16(P) (third pass of BF16X3)
   int pass_flags;             // kPassNoSums | kPassNoRowsum | kPassAccumulate (passes 2, 3 of BF16X3)
   int nslices, slice_chunks;  // output feature slices per row tile, chunks per (full) slice
@@ -51,6 +52,7 @@ struct TcParams {
   int gy_begin, gy_end;       // Y row tiles of this shard
   int xx_part, xx_nparts;     // S_xx-only units: X tiles t with t % nparts == part
   int n_xx_units;
+  int col_split, xx_chunk;    // mmd_tc.cu (set by its launcher): column ranges per gradient unit, tiles per S_xx chunk
   int pv;                     // 1: run the gradient GEMM and write dX/dY
   int n_scales;
   int max_clusters;           // pair kernel: cap on the persistent clusters (0 = none)
@@ -145,7 +147,7 @@ int get_tmap_bf16_2d(vgan_b200_ctx* ctx, CUtensorMap* map, const void* base, uin
 // map = row operand (A), mapB = column operand of the Gram, mapV = value operand of the gradient GEMM; the three are
 // the same array on the plain bf16 path and differ with split operands (BF16X3, see prologue.cu)
 int launch_tc(const TcParams& p, const CUtensorMap& map, const CUtensorMap& mapB, const CUtensorMap& mapV, int ladder,
-              cudaStream_t st, int split = 0);   // split: BF16X3 in one pass (D_p <= 256)
+              cudaStream_t st, int split, int n_sms);   // split: BF16X3 in one pass (D_p <= 256)
 int launch_xx(vgan_b200_ctx* ctx, const TcParams& p, const CUtensorMap& map, const CUtensorMap& map256, int ladder,
               cudaStream_t st, int max_ctas = 0);
 int launch_tc_pair(vgan_b200_ctx* ctx, const TcParams& p, const CUtensorMap& map, const CUtensorMap& mapB64,

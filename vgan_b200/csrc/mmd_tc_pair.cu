@@ -263,7 +263,9 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     if (my_chunks > 0) {
       for (int t = 0; t < TTp; ++t) {
         const int jt = min(tile0 + t, T - 1);
-        for (int h = 0; h < 2; ++h) {
+        for (int vh = 0; vh < 2 * p.v_parts; ++vh) {     // split operands, first pass: V_hi then V_lo against the same P tile
+          const int h = vh & 1;
+          const int vbase = vh < 2 ? p.v_chunk0 : p.v_chunk1;
           mbar_wait(&bar->v_empty[rs], rph ^ 1);
           uint8_t* dst = smem + kQSmemV + rs * kVStageBytes;
           if (dbg_flags & 4) {            // measurement only: no V loads
@@ -272,7 +274,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
             if (lane == 0 && hh == 0) mbar_arrive_expect_tx(&bar->v_full[rs], slice_chunks * (kChunkBytes / 2));
             if (lane < my_chunks)
               tma_load_2d_2cta(dst + lane * (kChunkBytes / 2), &vmap64, &bar->v_full[rs],
-                               (p.v_chunk0 + slice * p.slice_chunks + hh * my_chunks + lane) * kChunk,
+                               (vbase + slice * p.slice_chunks + hh * my_chunks + lane) * kChunk,
                                jt * kTile + 64 * h);
           }
           __syncwarp();
@@ -417,7 +419,8 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
       tc_fence_after();
       const uint32_t p_lo = p_lo0 + slot * (kQPBytes >> 4);
       if (my_chunks > 0) {
-        for (int h = 0; h < 2; ++h) {
+        for (int vh = 0; vh < 2 * p.v_parts; ++vh) {
+          const int h = vh & 1;
           {
             const long long t0 = VG_CLK();
             mbar_wait(&bar->v_full[rs], rph);
@@ -431,7 +434,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
             for (int j = 0; j < 4; ++j) {
               const uint64_t adesc = (static_cast<uint64_t>(desc_hi) << 32) | (pa_lo + j * 2);
               const uint64_t bdesc = (static_cast<uint64_t>(desc_hi) << 32) | (v_lo + j * (2048 >> 4)) | lbo_v;
-              umma_bf16_ss_2cta(tmem_o, adesc, bdesc, idesc_pv, (t | h | j) != 0);
+              umma_bf16_ss_2cta(tmem_o, adesc, bdesc, idesc_pv, (t | vh | j) != 0);
             }
             umma_commit_2cta_mc(&bar->v_empty[rs], pair_mask);
           }

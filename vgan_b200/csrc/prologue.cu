@@ -53,97 +53,157 @@ __device__ __forceinline__ float block_sum_256(float v, float* red) {
   return t;   // valid in thread 0
 }
 
-// ---- generic statistics: rows q of the range's stack [X rows rb..xe ; Y rows rb..ye)
-__global__ void __launch_bounds__(256) colstats_kernel(PackArgs a, int rows_per_block) {
+// 2-D thread map of the statistics kernels (round 2: one thread per column walking 32-64 rows serially left 20 of 256
+// threads busy at D = 20 and cost 30 us for 40 KB): column c = tid % cp of the pass (cp = power of two <= 256 that
+// covers the column items), row lane tid / cp; a thread strides the block's rows by the 256 / cp row lanes and the
+// lanes meet through shared memory before the block's atomics.
+__host__ __device__ inline int pow2_cols(int64_t cols) {
+  int p = 1;
+  while (p < cols && p < 256) p <<= 1;
+  return p;
+}
+
+// ---- generic statistics: rows q of the range's stack [X rows rb..xe ; Y rows rb..ye), and the column maxima of the
+// U rows that belong to the block's X rows (cpu = pow2_cols(D_u))
+__global__ void __launch_bounds__(256) colstats_kernel(PackArgs a, int rows_per_block, int cp, int cpu) {
+  __shared__ float part[2][256];
+  __shared__ unsigned long long kpart[256];
+  __shared__ float red[8];
   const int64_t xe = min(a.re, a.Nx), ye = min(a.re, a.Ny);
   const int64_t nX = max(xe - a.rb, static_cast<int64_t>(0)), nY = max(ye - a.rb, static_cast<int64_t>(0));
   const int64_t q0 = static_cast<int64_t>(blockIdx.x) * rows_per_block;
   const int64_t q1 = min(q0 + rows_per_block, nX + nY);
-  float sqx = 0.f, sqy = 0.f;
-  for (int64_t f = threadIdx.x; f < a.D; f += blockDim.x) {
-    float cx = 0.f, cy = 0.f;
-    for (int64_t q = q0; q < q1; ++q) {
-      if (q < nX) {
-        const float v = a.X[(a.rb + q) * a.D + f];
-        cx += v;
-        sqx = fmaf(v, v, sqx);
-      } else {
-        const int64_t y = a.rb + (q - nX);
-        const float v = a.Y ? a.Y[y * a.D + f] : a.U[y * a.D + f] * a.X[y * a.D + f];
-        cy += v;
-        sqy = fmaf(v, v, sqy);
+  const int64_t qx1 = min(q1, nX), qy0 = max(q0, nX);       // X rows [q0, qx1), Y rows [qy0, q1) of the stack
+  const int tid = threadIdx.x;
+  {
+    const int c = tid & (cp - 1), rl = tid / cp, rl_n = 256 / cp;
+    float sqx = 0.f, sqy = 0.f;
+    for (int64_t f0 = 0; f0 < a.D; f0 += cp) {
+      const int64_t f = f0 + c;
+      float cx = 0.f, cy = 0.f;
+      if (f < a.D) {
+#pragma unroll 4
+        for (int64_t q = q0 + rl; q < qx1; q += rl_n) {
+          const float v = a.X[(a.rb + q) * a.D + f];
+          cx += v;
+          sqx = fmaf(v, v, sqx);
+        }
+#pragma unroll 4
+        for (int64_t q = qy0 + rl; q < q1; q += rl_n) {
+          const int64_t y = a.rb + (q - nX);
+          const float v = a.Y ? a.Y[y * a.D + f] : a.U[y * a.D + f] * a.X[y * a.D + f];
+          cy += v;
+          sqy = fmaf(v, v, sqy);
+        }
+      }
+      if (rl_n > 1) {            // (block-uniform; the column loop then runs once)
+        part[0][tid] = cx;
+        part[1][tid] = cy;
+        __syncthreads();
+        if (rl == 0)
+          for (int k = c + cp; k < 256; k += cp) { cx += part[0][k]; cy += part[1][k]; }
+      }
+      if (rl == 0 && f < a.D) {
+        if (q0 < nX) atomicAdd(&a.stats[2 + f], static_cast<double>(cx));
+        if (q1 > nX) atomicAdd(&a.stats[2 + a.Dp + f], static_cast<double>(cy));
       }
     }
-    if (q0 < nX) atomicAdd(&a.stats[2 + f], static_cast<double>(cx));
-    if (q1 > nX) atomicAdd(&a.stats[2 + a.Dp + f], static_cast<double>(cy));
-  }
-  __shared__ float red[8];
-  const float tx = block_sum_256(sqx, red);
-  const float ty = block_sum_256(sqy, red);
-  if (threadIdx.x == 0) {
-    if (tx != 0.f) atomicAdd(&a.stats[0], static_cast<double>(tx));
-    if (ty != 0.f) atomicAdd(&a.stats[1], static_cast<double>(ty));
-  }
-}
-
-__global__ void __launch_bounds__(256)
-colmax_kernel(const float* __restrict__ U, int64_t r_begin, int64_t r_end, int64_t D, int rows_per_block,
-              unsigned long long* __restrict__ cmax) {
-  const int64_t r0 = r_begin + static_cast<int64_t>(blockIdx.x) * rows_per_block;
-  const int64_t r1 = min(r0 + rows_per_block, r_end);
-  for (int64_t d = threadIdx.x; d < D; d += blockDim.x) {
-    unsigned long long best = 0ull;
-    for (int64_t r = r0; r < r1; ++r) {
-      const unsigned long long key = max_key(U[r * D + d], r);
-      best = key > best ? key : best;
+    const float tx = block_sum_256(sqx, red);
+    const float ty = block_sum_256(sqy, red);
+    if (tid == 0) {
+      if (tx != 0.f) atomicAdd(&a.stats[0], static_cast<double>(tx));
+      if (ty != 0.f) atomicAdd(&a.stats[1], static_cast<double>(ty));
     }
-    atomicMax(&cmax[d], best);
+  }
+  if (a.cmax && q0 < qx1) {
+    const int c = tid & (cpu - 1), rl = tid / cpu, rl_n = 256 / cpu;
+    for (int64_t d0 = 0; d0 < a.D_u; d0 += cpu) {
+      const int64_t d = d0 + c;
+      unsigned long long best = 0ull;
+      if (d < a.D_u) {
+#pragma unroll 4
+        for (int64_t q = q0 + rl; q < qx1; q += rl_n) {
+          const unsigned long long key = max_key(a.U[(a.rb + q) * a.D_u + d], a.rb + q);
+          best = key > best ? key : best;
+        }
+      }
+      if (rl_n > 1) {
+        kpart[tid] = best;
+        __syncthreads();
+        if (rl == 0)
+          for (int k = c + cpu; k < 256; k += cpu) best = kpart[k] > best ? kpart[k] : best;
+      }
+      if (rl == 0 && d < a.D_u) atomicMax(&a.cmax[d], best);
+    }
   }
 }
 
 // ---- masked fast path (Y = U*X, Nx == Ny, D % 4 == 0, 16-byte aligned inputs): X and U are read ONCE per pass
-// for both halves of the stack, with 16-byte loads; the column maxima of U ride along.
-__global__ void __launch_bounds__(256) colstats_masked_kernel(PackArgs a, int rows_per_block) {
+// for both halves of the stack, with 16-byte loads; the column maxima of U ride along.  cp = pow2_cols(D / 4).
+__global__ void __launch_bounds__(256) colstats_masked_kernel(PackArgs a, int rows_per_block, int cp) {
+  __shared__ float4 pcx[256], pcy[256];
+  __shared__ unsigned long long pkey[4][256];
+  __shared__ float red[8];
+  const int tid = threadIdx.x;
+  const int c = tid & (cp - 1), rl = tid / cp, rl_n = 256 / cp;
   const int64_t r0 = a.rb + static_cast<int64_t>(blockIdx.x) * rows_per_block;
   const int64_t r1 = min(r0 + rows_per_block, min(a.re, a.Nx));
   const int64_t D4 = a.D >> 2;
   float sqx = 0.f, sqy = 0.f;
-  for (int64_t f4 = threadIdx.x; f4 < D4; f4 += blockDim.x) {
+  for (int64_t f0 = 0; f0 < D4; f0 += cp) {
+    const int64_t f4 = f0 + c;
     float4 cx = make_float4(0.f, 0.f, 0.f, 0.f), cy = cx;
     unsigned long long m0 = 0ull, m1 = 0ull, m2 = 0ull, m3 = 0ull;
-    const float4* xp = reinterpret_cast<const float4*>(a.X) + r0 * D4 + f4;
-    const float4* up = reinterpret_cast<const float4*>(a.U) + r0 * D4 + f4;
+    if (f4 < D4) {
+      const float4* xp = reinterpret_cast<const float4*>(a.X) + (r0 + rl) * D4 + f4;
+      const float4* up = reinterpret_cast<const float4*>(a.U) + (r0 + rl) * D4 + f4;
+      const int64_t step = static_cast<int64_t>(rl_n) * D4;
 #pragma unroll 4
-    for (int64_t r = r0; r < r1; ++r, xp += D4, up += D4) {
-      const float4 x = __ldg(xp), u = __ldg(up);
-      const float4 y = make_float4(u.x * x.x, u.y * x.y, u.z * x.z, u.w * x.w);
-      cx.x += x.x; cx.y += x.y; cx.z += x.z; cx.w += x.w;
-      cy.x += y.x; cy.y += y.y; cy.z += y.z; cy.w += y.w;
-      sqx = fmaf(x.x, x.x, fmaf(x.y, x.y, fmaf(x.z, x.z, fmaf(x.w, x.w, sqx))));
-      sqy = fmaf(y.x, y.x, fmaf(y.y, y.y, fmaf(y.z, y.z, fmaf(y.w, y.w, sqy))));
-      if (a.cmax) {
-        unsigned long long k;
-        k = max_key(u.x, r); m0 = k > m0 ? k : m0;
-        k = max_key(u.y, r); m1 = k > m1 ? k : m1;
-        k = max_key(u.z, r); m2 = k > m2 ? k : m2;
-        k = max_key(u.w, r); m3 = k > m3 ? k : m3;
+      for (int64_t r = r0 + rl; r < r1; r += rl_n, xp += step, up += step) {
+        const float4 x = __ldg(xp), u = __ldg(up);
+        const float4 y = make_float4(u.x * x.x, u.y * x.y, u.z * x.z, u.w * x.w);
+        cx.x += x.x; cx.y += x.y; cx.z += x.z; cx.w += x.w;
+        cy.x += y.x; cy.y += y.y; cy.z += y.z; cy.w += y.w;
+        sqx = fmaf(x.x, x.x, fmaf(x.y, x.y, fmaf(x.z, x.z, fmaf(x.w, x.w, sqx))));
+        sqy = fmaf(y.x, y.x, fmaf(y.y, y.y, fmaf(y.z, y.z, fmaf(y.w, y.w, sqy))));
+        if (a.cmax) {
+          unsigned long long k;
+          k = max_key(u.x, r); m0 = k > m0 ? k : m0;
+          k = max_key(u.y, r); m1 = k > m1 ? k : m1;
+          k = max_key(u.z, r); m2 = k > m2 ? k : m2;
+          k = max_key(u.w, r); m3 = k > m3 ? k : m3;
+        }
       }
     }
-    double* sx = a.stats + 2 + 4 * f4;
-    double* sy = a.stats + 2 + a.Dp + 4 * f4;
-    atomicAdd(sx + 0, static_cast<double>(cx.x)); atomicAdd(sx + 1, static_cast<double>(cx.y));
-    atomicAdd(sx + 2, static_cast<double>(cx.z)); atomicAdd(sx + 3, static_cast<double>(cx.w));
-    atomicAdd(sy + 0, static_cast<double>(cy.x)); atomicAdd(sy + 1, static_cast<double>(cy.y));
-    atomicAdd(sy + 2, static_cast<double>(cy.z)); atomicAdd(sy + 3, static_cast<double>(cy.w));
-    if (a.cmax) {
-      atomicMax(a.cmax + 4 * f4 + 0, m0); atomicMax(a.cmax + 4 * f4 + 1, m1);
-      atomicMax(a.cmax + 4 * f4 + 2, m2); atomicMax(a.cmax + 4 * f4 + 3, m3);
+    if (rl_n > 1) {              // (block-uniform; the column loop then runs once)
+      pcx[tid] = cx; pcy[tid] = cy;
+      pkey[0][tid] = m0; pkey[1][tid] = m1; pkey[2][tid] = m2; pkey[3][tid] = m3;
+      __syncthreads();
+      if (rl == 0)
+        for (int k = c + cp; k < 256; k += cp) {
+          const float4 x = pcx[k], y = pcy[k];
+          cx.x += x.x; cx.y += x.y; cx.z += x.z; cx.w += x.w;
+          cy.x += y.x; cy.y += y.y; cy.z += y.z; cy.w += y.w;
+          m0 = pkey[0][k] > m0 ? pkey[0][k] : m0; m1 = pkey[1][k] > m1 ? pkey[1][k] : m1;
+          m2 = pkey[2][k] > m2 ? pkey[2][k] : m2; m3 = pkey[3][k] > m3 ? pkey[3][k] : m3;
+        }
+    }
+    if (rl == 0 && f4 < D4) {
+      double* sx = a.stats + 2 + 4 * f4;
+      double* sy = a.stats + 2 + a.Dp + 4 * f4;
+      atomicAdd(sx + 0, static_cast<double>(cx.x)); atomicAdd(sx + 1, static_cast<double>(cx.y));
+      atomicAdd(sx + 2, static_cast<double>(cx.z)); atomicAdd(sx + 3, static_cast<double>(cx.w));
+      atomicAdd(sy + 0, static_cast<double>(cy.x)); atomicAdd(sy + 1, static_cast<double>(cy.y));
+      atomicAdd(sy + 2, static_cast<double>(cy.z)); atomicAdd(sy + 3, static_cast<double>(cy.w));
+      if (a.cmax) {
+        atomicMax(a.cmax + 4 * f4 + 0, m0); atomicMax(a.cmax + 4 * f4 + 1, m1);
+        atomicMax(a.cmax + 4 * f4 + 2, m2); atomicMax(a.cmax + 4 * f4 + 3, m3);
+      }
     }
   }
-  __shared__ float red[8];
   const float tx = block_sum_256(sqx, red);
   const float ty = block_sum_256(sqy, red);
-  if (threadIdx.x == 0) {
+  if (tid == 0) {
     atomicAdd(&a.stats[0], static_cast<double>(tx));
     atomicAdd(&a.stats[1], static_cast<double>(ty));
   }
@@ -192,6 +252,8 @@ __global__ void __launch_bounds__(256) scales_kernel(ScaleArgs a) {
   axy = block_sum_256d(axy, red);
   const double nx = static_cast<double>(a.Nx), ny = static_cast<double>(a.Ny), n = nx + ny;
   const double sqx = a.stats[0], sqy = a.stats[1];
+  __shared__ float sh_inv[VGAN_B200_MAX_SCALES];
+  __shared__ double sh_w[4][VGAN_B200_MAX_SCALES];
   if (threadIdx.x == 0) {
     float bw;
     if (!a.frozen) {
@@ -200,13 +262,32 @@ __global__ void __launch_bounds__(256) scales_kernel(ScaleArgs a) {
     } else {
       bw = *a.bandwidth;
     }
+    sh[4] = bw;
     // the reference multiplies the 0-dim bandwidth with the fp32 multiplier vector -> fp32
+    for (int m = 0; m < VGAN_B200_MAX_SCALES; ++m) sh_inv[m] = m < a.n_scales ? 1.0f / (bw * a.mults[m]) : 0.f;
+  }
+  if (threadIdx.x < kParFloats) a.par[threadIdx.x] = 0.f;
+  __syncthreads();
+  // common mode: w0_ab = w(mean squared distance between block a and block b); one (block pair, scale) per thread
+  if (threadIdx.x < 4 * VGAN_B200_MAX_SCALES) {
+    const int rc = threadIdx.x / VGAN_B200_MAX_SCALES, m = threadIdx.x % VGAN_B200_MAX_SCALES;
+    double w = 0.0;
+    if (a.common_mode && m < a.n_scales) {
+      const double mx = sqx / nx, my = sqy / ny;
+      const double d2 = rc == 0 ? 2.0 * (mx - axx / (nx * nx))
+                                : (rc == 3 ? 2.0 * (my - ayy / (ny * ny)) : mx + my - 2.0 * axy / (nx * ny));
+      w = exp(-fmax(d2, 0.0) * sh_inv[m]) * sh_inv[m];
+    }
+    sh_w[rc][m] = w;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const float bw = sh[4];
     float inv_s[VGAN_B200_MAX_SCALES];
-    for (int m = 0; m < VGAN_B200_MAX_SCALES; ++m) inv_s[m] = m < a.n_scales ? 1.0f / (bw * a.mults[m]) : 0.f;
+    for (int m = 0; m < VGAN_B200_MAX_SCALES; ++m) inv_s[m] = sh_inv[m];
     const int ref = a.n_scales - 1;
     const float c0 = kLog2e * inv_s[ref];
     float* par = a.par;
-    for (int t = 0; t < kParFloats; ++t) par[t] = 0.f;
     par[0] = c0;
     par[1] = -2.f * c0;
     const float cx = 1.f / static_cast<float>(a.Nx), cy = -1.f / static_cast<float>(a.Ny);
@@ -217,19 +298,13 @@ __global__ void __launch_bounds__(256) scales_kernel(ScaleArgs a) {
       par[kParInvS + m] = inv_s[m];
     }
     par[kParBw] = bw;
-    // common mode: w0_ab = w(mean squared distance between block a and block b)
-    float w0[2][2] = {{0.f, 0.f}, {0.f, 0.f}};
-    if (a.common_mode) {
-      const double mx = sqx / nx, my = sqy / ny;
-      const double dxy = mx + my - 2.0 * axy / (nx * ny);
-      const double d2[2][2] = {{2.0 * (mx - axx / (nx * nx)), dxy}, {dxy, 2.0 * (my - ayy / (ny * ny))}};
-      for (int r = 0; r < 2; ++r)
-        for (int c = 0; c < 2; ++c) {
-          double w = 0.0;
-          for (int m = 0; m < a.n_scales; ++m) w += exp(-fmax(d2[r][c], 0.0) * inv_s[m]) * inv_s[m];
-          w0[r][c] = static_cast<float>(w);
-        }
-    }
+    float w0[2][2];
+    for (int r = 0; r < 2; ++r)
+      for (int c = 0; c < 2; ++c) {
+        double w = 0.0;
+        for (int m = 0; m < a.n_scales; ++m) w += sh_w[2 * r + c][m];
+        w0[r][c] = static_cast<float>(w);
+      }
     const float npx = static_cast<float>(a.Nxp - a.Nx), npy = static_cast<float>(a.Nyp - a.Ny);
     for (int r = 0; r < 2; ++r) {
       par[kParCw0 + 2 * r + 0] = cx * w0[r][0];
@@ -418,16 +493,20 @@ int run_stats(const vgan_b200_layout_t& L, void* ws, const float* X, const float
   if (nY < 0) nY = 0;
   const int64_t rows = nX + nY;
   if (rows <= 0) return VGAN_B200_OK;       // an empty shard only takes part in the exchanges
+  // rows per block: 8 (masked: 16-byte loads) or 4 (generic) strides of the row lanes, doubled until at most 1024 blocks
+  // (every block ends in 2-12 double atomics per column)
   if (masked_fast(a)) {
-    const int rpb = nX >= 32768 ? 64 : 32;
-    colstats_masked_kernel<<<static_cast<unsigned>((nX + rpb - 1) / rpb), 256, 0, st>>>(a, rpb); count_launch();
+    const int cp = pow2_cols(L.D >> 2);
+    int64_t rpb = (256 / cp) * 8;
+    while ((nX + rpb - 1) / rpb > 1024) rpb *= 2;
+    colstats_masked_kernel<<<static_cast<unsigned>((nX + rpb - 1) / rpb), 256, 0, st>>>(a, static_cast<int>(rpb), cp);
+    count_launch();
   } else {
-    const int rpb = 64;
-    colstats_kernel<<<static_cast<unsigned>((rows + rpb - 1) / rpb), 256, 0, st>>>(a, rpb); count_launch();
-    if (a.cmax && nX > 0) {
-      colmax_kernel<<<static_cast<unsigned>((nX + rpb - 1) / rpb), 256, 0, st>>>(U, rb, rb + nX, L.D_u, rpb, a.cmax);
-      count_launch();
-    }
+    const int cp = pow2_cols(L.D), cpu = pow2_cols(L.D_u > 0 ? L.D_u : 1);
+    int64_t rpb = (256 / cp) * 4;
+    while ((rows + rpb - 1) / rpb > 1024) rpb *= 2;
+    colstats_kernel<<<static_cast<unsigned>((rows + rpb - 1) / rpb), 256, 0, st>>>(a, static_cast<int>(rpb), cp, cpu);
+    count_launch();
   }
   VG_CUDA_CHECK(cudaGetLastError());
   return VGAN_B200_OK;

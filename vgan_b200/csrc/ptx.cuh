@@ -53,7 +53,7 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 }
 // Bounded spin: a protocol bug traps (-> CUDA error on the host) instead of hanging the box.
 #ifndef VG_SPIN_LIMIT
-#define VG_SPIN_LIMIT (1u << 28)
+#define VG_SPIN_LIMIT (1u << 24)
 #endif
 // (debug build, -DVG_SPIN_REPORT: report and carry on, so that the kernel ends and the messages reach the host)
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {

@@ -5,23 +5,29 @@
 
 namespace vg {
 
+// What the epilogue parks for the gradient GEMM: bf16(P'), the remainder P' - bf16(P') (third pass of the three-pass
+// split-operand form), or both tiles at once (single-pass split operands, mmd_tc.cu)
+enum : int { kPHi = 0, kPLo = 1, kPBoth = 2 };
+
 // Kernel values of 32 columns already in registers (see epi_half_tile for the math).
-template <bool LADDER>
-__device__ __forceinline__ void epi_compute_32(const uint32_t (&v)[32], const float* __restrict__ njp, float ni,
-                                                    float m2c0, const float (&cf)[VGAN_B200_MAX_SCALES],
-                                                    const float (&ratio)[VGAN_B200_MAX_SCALES], int n_scales,
-                                                    float& ksum, float& rsum, uint4 (&pk)[4], bool plo = false,
-                                                    float cw0 = 0.f, uint4* pk_lo = nullptr) {
-  // pk_lo != nullptr (single-pass split operands): pk = bf16(P') and pk_lo = bf16(P' - bf16(P')), both tiles at once
+// Ladder form, nested so that t^16 is never formed (3 squarings, 16 packed ops per column pair instead of 17):
+//   k = t (1 + t (1 + t^2 (1 + t^4 (1 + t^8))))                    = t + t^2 + t^4 + t^8 + t^16
+//   w = t (c4 + t (c3 + t^2 (c2 + t^4 (c1 + t^8 c0)))) - c_j w0    = sum_m c_m t^(2^(4-m)) - c_j w0
+// (scale index 4 is the widest kernel, t itself; index 0 the narrowest, t^16)
+template <bool LADDER, int PMODE>
+__device__ __forceinline__ void epi_core_32(const uint32_t (&v)[32], const float* __restrict__ njp, float ni,
+                                            float m2c0, const float (&cf)[VGAN_B200_MAX_SCALES],
+                                            const float (&ratio)[VGAN_B200_MAX_SCALES], int n_scales,
+                                            float& ksum, float& rsum, uint4 (&pk)[4], float cw0, uint4* pk_lo) {
   // cw0 = c_j w0: the common-mode level of this (row block, column block) pair.  P' = c_j (w - w0) is what gets rounded
   // to bf16 and multiplied; the closed-form remainder is added back in write_grad_rows.  It rides in the last FMA of
   // the weight sum, so it costs no instruction.
   if constexpr (LADDER) {
-    // two columns per issue slot (packed f32x2): ~11.5 instead of ~19.5 instructions per pair
-    const uint64_t m2 = f2_pack(m2c0, m2c0), ni2 = f2_pack(ni, ni), mcw = f2_pack(-cw0, -cw0);
+    // two columns per issue slot (packed f32x2)
+    const uint64_t m2 = f2_pack(m2c0, m2c0), ni2 = f2_pack(ni, ni), mcw = f2_pack(-cw0, -cw0), one = f2_pack(1.f, 1.f);
     const uint64_t c0 = f2_pack(cf[0], cf[0]), c1 = f2_pack(cf[1], cf[1]), c2 = f2_pack(cf[2], cf[2]),
                    c3 = f2_pack(cf[3], cf[3]), c4 = f2_pack(cf[4], cf[4]);
-    uint64_t ks2 = f2_pack(0.f, 0.f), rs2 = f2_pack(0.f, 0.f);
+    uint64_t ks2 = f2_pack(ksum, 0.f), rs2 = f2_pack(rsum, 0.f);
 #pragma unroll
     for (int c = 0; c < 4; ++c) {
       const float4 nja = *reinterpret_cast<const float4*>(njp + c * 8);
@@ -35,28 +41,28 @@ __device__ __forceinline__ void epi_compute_32(const uint32_t (&v)[32], const fl
         f2_unpack(f2_fma(s2, m2, f2_add(ni2, nj2[q])), u0, u1);
         // no clamp at 0 here (the reference's cdist clamps): the norms are those of the values the tensor core
         // multiplies, so u of a coincident pair is 0 +- 1e-6 and t = 1 +- 1e-6 — far inside the 2e-3 / 1e-4 budgets,
-        // and two FMNMX per column pair (8 % of the epilogue's instructions) are saved; padding has u = +huge
+        // and two FMNMX per column pair are saved; padding has u = +huge
         const uint64_t t1 = f2_pack(ex2_approx(-u0), ex2_approx(-u1));
-        const uint64_t t2 = f2_mul(t1, t1), t4 = f2_mul(t2, t2), t8 = f2_mul(t4, t4), t16 = f2_mul(t8, t8);
-        ks2 = f2_add(ks2, f2_add(f2_add(t1, t2), f2_add(f2_add(t4, t8), t16)));
-        // scale index 4 is the widest kernel (t1), index 0 the narrowest (t16)
-        const uint64_t w2 = f2_fma(t16, c0, f2_fma(t8, c1, f2_fma(t4, c2, f2_fma(t2, c3, f2_fma(t1, c4, mcw)))));
+        const uint64_t t2 = f2_mul(t1, t1), t4 = f2_mul(t2, t2), t8 = f2_mul(t4, t4);
+        ks2 = f2_fma(t1, f2_fma(t1, f2_fma(t2, f2_fma(t4, f2_add(t8, one), one), one), one), ks2);
+        const uint64_t w2 = f2_fma(t1, f2_fma(t1, f2_fma(t2, f2_fma(t4, f2_fma(t8, c0, c1), c2), c3), c4), mcw);
         rs2 = f2_add(rs2, w2);
         float w0, w1;
         f2_unpack(w2, w0, w1);
         pw[q] = pack_bf16x2(w0, w1);
-        const uint32_t rem = pack_bf16x2(w0 - __uint_as_float(pw[q] << 16), w1 - __uint_as_float(pw[q] & 0xffff0000u));
-        if (plo) pw[q] = rem;      // split-operand pass 3: the remainder of P after its bf16 rounding
-        pl[q] = rem;
+        if constexpr (PMODE != kPHi) {
+          pl[q] = pack_bf16x2(w0 - __uint_as_float(pw[q] << 16), w1 - __uint_as_float(pw[q] & 0xffff0000u));
+          if constexpr (PMODE == kPLo) pw[q] = pl[q];      // split-operand pass 3: the remainder of P after its bf16 rounding
+        }
       }
       pk[c].x = pw[0]; pk[c].y = pw[1]; pk[c].z = pw[2]; pk[c].w = pw[3];
-      if (pk_lo) { pk_lo[c].x = pl[0]; pk_lo[c].y = pl[1]; pk_lo[c].z = pl[2]; pk_lo[c].w = pl[3]; }
+      if constexpr (PMODE == kPBoth) { pk_lo[c].x = pl[0]; pk_lo[c].y = pl[1]; pk_lo[c].z = pl[2]; pk_lo[c].w = pl[3]; }
     }
     float a, b;
     f2_unpack(ks2, a, b);
-    ksum += a + b;
+    ksum = a + b;
     f2_unpack(rs2, a, b);
-    rsum += a + b;
+    rsum = a + b;
   } else {
 #pragma unroll
   for (int c = 0; c < 4; ++c) {
@@ -83,11 +89,61 @@ __device__ __forceinline__ void epi_compute_32(const uint32_t (&v)[32], const fl
     for (int q = 0; q < 4; ++q) {
       pw[q] = pack_bf16x2(w[2 * q], w[2 * q + 1]);
       pl[q] = pack_bf16x2(w[2 * q] - __uint_as_float(pw[q] << 16), w[2 * q + 1] - __uint_as_float(pw[q] & 0xffff0000u));
-      if (plo) pw[q] = pl[q];
+      if constexpr (PMODE == kPLo) pw[q] = pl[q];
     }
     pk[c].x = pw[0]; pk[c].y = pw[1]; pk[c].z = pw[2]; pk[c].w = pw[3];
-    if (pk_lo) { pk_lo[c].x = pl[0]; pk_lo[c].y = pl[1]; pk_lo[c].z = pl[2]; pk_lo[c].w = pl[3]; }
+    if constexpr (PMODE == kPBoth) { pk_lo[c].x = pl[0]; pk_lo[c].y = pl[1]; pk_lo[c].z = pl[2]; pk_lo[c].w = pl[3]; }
   }
+  }
+}
+
+// The same with the parked tile chosen at run time (pair kernel: plo = third pass of the three-pass split form)
+template <bool LADDER>
+__device__ __forceinline__ void epi_compute_32(const uint32_t (&v)[32], const float* __restrict__ njp, float ni,
+                                               float m2c0, const float (&cf)[VGAN_B200_MAX_SCALES],
+                                               const float (&ratio)[VGAN_B200_MAX_SCALES], int n_scales,
+                                               float& ksum, float& rsum, uint4 (&pk)[4], bool plo = false,
+                                               float cw0 = 0.f) {
+  if (plo) epi_core_32<LADDER, kPLo>(v, njp, ni, m2c0, cf, ratio, n_scales, ksum, rsum, pk, cw0, nullptr);
+  else epi_core_32<LADDER, kPHi>(v, njp, ni, m2c0, cf, ratio, n_scales, ksum, rsum, pk, cw0, nullptr);
+}
+
+// Sum over 32 columns already in registers of k alone (units without a gradient GEMM): 10 packed ops per column pair
+template <bool LADDER>
+__device__ __forceinline__ void epi_k_32(const uint32_t (&v)[32], const float* __restrict__ njp, float ni, float m2c0,
+                                         const float (&ratio)[VGAN_B200_MAX_SCALES], int n_scales, float& ksum) {
+  if constexpr (LADDER) {
+    const uint64_t m2 = f2_pack(m2c0, m2c0), ni2 = f2_pack(ni, ni), one = f2_pack(1.f, 1.f);
+    uint64_t ks2 = f2_pack(ksum, 0.f);
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+      const float4 nj4 = *reinterpret_cast<const float4*>(njp + c * 4);
+      const uint64_t nj2[2] = {f2_pack(nj4.x, nj4.y), f2_pack(nj4.z, nj4.w)};
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        const uint64_t s2 = f2_pack(__uint_as_float(v[c * 4 + 2 * q]), __uint_as_float(v[c * 4 + 2 * q + 1]));
+        float u0, u1;
+        f2_unpack(f2_fma(s2, m2, f2_add(ni2, nj2[q])), u0, u1);
+        const uint64_t t1 = f2_pack(ex2_approx(-u0), ex2_approx(-u1));
+        const uint64_t t2 = f2_mul(t1, t1), t4 = f2_mul(t2, t2), t8 = f2_mul(t4, t4);
+        ks2 = f2_fma(t1, f2_fma(t1, f2_fma(t2, f2_fma(t4, f2_add(t8, one), one), one), one), ks2);
+      }
+    }
+    float a, b;
+    f2_unpack(ks2, a, b);
+    ksum = a + b;
+  } else {
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+      const float4 nj4 = *reinterpret_cast<const float4*>(njp + c * 4);
+      const float njv[4] = {nj4.x, nj4.y, nj4.z, nj4.w};
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        float uarg = fmaf(__uint_as_float(v[c * 4 + e]), m2c0, ni + njv[e]);
+        uarg = fmaxf(uarg, 0.f);
+        for (int m = 0; m < n_scales; ++m) ksum += ex2_approx(-uarg * ratio[m]);
+      }
+    }
   }
 }
 
@@ -95,16 +151,15 @@ __device__ __forceinline__ void epi_compute_32(const uint32_t (&v)[32], const fl
 //   u = c0*d2 = fma(S, -2c0, ni + nj),  t = 2^-u,  k = sum_m t^(2^q),  w = sum_m coef_m t^(2^q)
 // (ladder) or the general n_scales form, adds k to ksum and w to rsum, and returns the 32 values of
 // P = w as bf16 packed into 4 x uint4 (8 columns each, ascending).
-template <bool LADDER>
+template <bool LADDER, int PMODE>
 __device__ __forceinline__ void epi_half_tile(uint32_t taddr, const float* __restrict__ njp, float ni,
                                               float m2c0, const float (&cf)[VGAN_B200_MAX_SCALES],
                                               const float (&ratio)[VGAN_B200_MAX_SCALES], int n_scales,
-                                              float& ksum, float& rsum, uint4 (&pk)[4], bool plo = false,
-                                              float cw0 = 0.f, uint4* pk_lo = nullptr) {
+                                              float& ksum, float& rsum, uint4 (&pk)[4], float cw0, uint4* pk_lo) {
   uint32_t v[32];
   tmem_ld_32x32(taddr, v);
   tmem_ld_wait();
-  epi_compute_32<LADDER>(v, njp, ni, m2c0, cf, ratio, n_scales, ksum, rsum, pk, plo, cw0, pk_lo);
+  epi_core_32<LADDER, PMODE>(v, njp, ni, m2c0, cf, ratio, n_scales, ksum, rsum, pk, cw0, pk_lo);
 }
 
 // Column sums over the 32 lanes of a warp of 32 per-lane values: lane l returns sum over lanes of v[l].
@@ -154,7 +209,7 @@ __device__ __forceinline__ void write_grad_rows(const TcParams& p, uint32_t tmem
   const float* cmv = p.cm + (row_is_x ? 0 : p.Dp);
   accumulate = accumulate || (p.pass_flags & kPassAccumulate);
   const int f_slice = slice * p.slice_chunks * kChunk;
-  const bool vec_ok = !accumulate && (p.D & 3) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0 &&
+  const bool vec_ok = (p.D & 3) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0 &&
                       (!mul || (reinterpret_cast<uintptr_t>(mul) & 15) == 0);
   const bool want_colsum = p.colsum != nullptr && !row_is_x;       // warp-uniform
   for (int cc = 0; cc < slice_chunks; ++cc) {
@@ -214,8 +269,13 @@ __device__ __forceinline__ void write_grad_rows(const TcParams& p, uint32_t tmem
             gv[0] *= m0.x; gv[1] *= m0.y; gv[2] *= m0.z; gv[3] *= m0.w;
             gv[4] *= m1.x; gv[5] *= m1.y; gv[6] *= m1.z; gv[7] *= m1.w;
           }
-          *reinterpret_cast<float4*>(out + f0) = make_float4(gv[0], gv[1], gv[2], gv[3]);
-          *reinterpret_cast<float4*>(out + f0 + 4) = make_float4(gv[4], gv[5], gv[6], gv[7]);
+          if (accumulate) {     // unit shared between CTAs (column ranges / stream-K cut) or a BF16X3 pass: red.v4.f32
+            atomicAdd(reinterpret_cast<float4*>(out + f0), make_float4(gv[0], gv[1], gv[2], gv[3]));
+            atomicAdd(reinterpret_cast<float4*>(out + f0 + 4), make_float4(gv[4], gv[5], gv[6], gv[7]));
+          } else {
+            *reinterpret_cast<float4*>(out + f0) = make_float4(gv[0], gv[1], gv[2], gv[3]);
+            *reinterpret_cast<float4*>(out + f0 + 4) = make_float4(gv[4], gv[5], gv[6], gv[7]);
+          }
 #pragma unroll
           for (int e = 0; e < 8; ++e) cs[c * 8 + e] = gv[e];
         } else {
