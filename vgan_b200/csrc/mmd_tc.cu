@@ -17,8 +17,8 @@
 // (an X row tile against a chunk of its upper-triangle columns, kernel sums only: no weights, no P, no second GEMM).
 // The S_xx chunks are short (<= xx_chunk tiles) so that they pack the tail of the grid behind the long gradient units.
 //
-// Warp roles (640 threads): warps 0-15 epilogue (warp%4 = TMEM lane quadrant, warp/4 = column quarter of 32),
-// warp 16 = TMA producer (column operand and V slices), warp 17 = MMA issuer, warp 18 = column norms,
+// Warp roles (640 threads): warps 0-15 epilogue in two groups of 8 that alternate over the column tiles (warp%4 = TMEM
+// lane quadrant, (warp/4)%2 = column half of 64, warp/8 = group = parity of the tile), warp 16 = TMA producer (column operand and V slices), warp 17 = MMA issuer, warp 18 = column norms,
 // warp 19 = TMEM allocator.  This kernel serves D_p <= 256, where the epilogue (FP32 + MUFU issue) is the bound:
 // with 8 epilogue warps (2 per scheduler) the issue slots were 49 % busy (ncu, profiles/r1d_base_d64_summary.txt:
 // fixed-latency dependency stalls with nothing else to issue); 4 warps per scheduler hide them.  setmaxnreg moves
@@ -43,11 +43,7 @@ constexpr int kThreads = kNumEpiThreads + 128;
 constexpr int kWarpTma = kNumEpiWarps, kWarpMma = kNumEpiWarps + 1, kWarpNorms = kNumEpiWarps + 2,
               kWarpAlloc = kNumEpiWarps + 3;
 constexpr int kSmemLimit = 232448;
-#ifdef VG_TC_PINGPONG
 constexpr int kEpiGroupThreads = kNumEpiThreads / 2;   // two epilogue groups of 8 warps alternate over the column tiles
-#else
-constexpr int kEpiGroupThreads = kNumEpiThreads;
-#endif
 constexpr int kLag = 3;   // the Gram stream runs this many column tiles ahead of the gradient GEMM (see the MMA warp)
 
 struct __align__(8) TcBarriers {
@@ -145,10 +141,11 @@ __device__ __forceinline__ Unit decode_unit(const TcParams& p) {
   return u;
 }
 
-#ifdef VG_TC_PINGPONG
 // Epilogue of one unit, two groups of 8 warps: group n & 1 owns column tile n (S[n & 1], P[n & 1], the norms buffer
 // n & 1); a warp covers 32 rows x 64 columns in two steps of 32.  The groups only meet in the FP32 pipe: while one sits
-// in its barrier waits, tcgen05.ld latency and the fence behind its P stores, the other one computes.
+// in its barrier waits, tcgen05.ld latency and the fence behind its P stores, the other one computes (measured against
+// all 16 warps sharing every tile, same box: N = 16384, D = 128 506 -> 454 us, N = 65536, D = 64 7.65 -> 6.72 ms).
+// PV = false: kernel sums only (S_xx chunks, forward-only calls).
 template <bool LADDER, bool SPLIT, bool PV>
 __device__ __forceinline__ void epilogue_tiles(const TcParams& p, const Unit& u, TcBarriers* bar, uint8_t* p_smem,
                                                const float* nj_smem, uint32_t tmem, int warp, int lane, float& acc_x,
@@ -232,84 +229,6 @@ __device__ __forceinline__ void epilogue_tiles(const TcParams& p, const Unit& u,
     }
   }
 }
-#else
-// Epilogue of one unit.  PV = false: kernel sums only (S_xx chunks, forward-only calls).
-template <bool LADDER, bool SPLIT, bool PV>
-__device__ __forceinline__ void epilogue_tiles(const TcParams& p, const Unit& u, TcBarriers* bar, uint8_t* p_smem,
-                                               const float* nj_smem, uint32_t tmem, int warp, int lane, float& acc_x,
-                                               float& acc_y, float& rsum) {
-  const int q = warp & 3, g = warp >> 2;                 // lane quadrant, column quarter
-  const int row = q * 32 + lane;
-  const uint32_t lane_addr = static_cast<uint32_t>(q * 32) << 16;
-  const float m2c0 = p.par[1];
-  const float ni = p.nrms[static_cast<int64_t>(u.ti) * kTile + row];
-  float coef_x[VGAN_B200_MAX_SCALES], coef_y[VGAN_B200_MAX_SCALES], ratio[VGAN_B200_MAX_SCALES];
-#pragma unroll
-  for (int m = 0; m < VGAN_B200_MAX_SCALES; ++m) {
-    ratio[m] = p.par[2 + m];
-    coef_x[m] = PV ? p.par[kParCoefX + m] : 0.f;
-    coef_y[m] = PV ? p.par[kParCoefY + m] : 0.f;
-  }
-  // common-mode level c_j w0 of (this row block, X columns) / (this row block, Y columns)
-  const float cw0_x = PV ? p.par[kParCw0 + (u.row_is_x ? 0 : 2)] : 0.f;
-  const float cw0_y = PV ? p.par[kParCw0 + (u.row_is_x ? 0 : 2) + 1] : 0.f;
-  const int n_tiles = u.j_end - u.j_begin;
-  for (int n = 0; n < n_tiles; ++n) {
-    const int jt = u.j_begin + n;
-    const int b = n & 1;
-    const bool col_is_x = jt < p.tiles_x;
-    mbar_wait(&bar->nj_full[b], (n >> 1) & 1);
-    mbar_wait(&bar->s_full[b], (n >> 1) & 1);
-    tc_fence_after();
-    const float* njp = nj_smem + b * kTile + g * 32;
-    float ksum = 0.f;
-    if constexpr (PV) {
-      float cf[VGAN_B200_MAX_SCALES];
-#pragma unroll
-      for (int m = 0; m < VGAN_B200_MAX_SCALES; ++m) cf[m] = col_is_x ? coef_x[m] : coef_y[m];
-      uint8_t* p_row = p_smem + b * kPBytes + (g >> 1) * kChunkBytes + row * 128;
-      uint4 pk[4], pk_lo[4];
-      {
-        uint32_t v[32];
-        tmem_ld_32x32(tmem + lane_addr + b * kTile + g * 32, v);
-        tmem_ld_wait();
-        tc_fence_before();
-        mbar_arrive(&bar->s_empty[b]);     // S[b] is in registers: the Gram two tiles on may overwrite it during the math
-        epi_core_32<LADDER, SPLIT ? kPBoth : kPHi>(v, njp, ni, m2c0, cf, ratio, p.n_scales, ksum, rsum, pk,
-                                                   col_is_x ? cw0_x : cw0_y, pk_lo);
-      }
-      mbar_arrive(&bar->nj_empty[b]);      // the column norms of this tile are no longer read
-      mbar_wait(&bar->p_empty[b], ((n >> 1) & 1) ^ 1);   // PV(n-2) done with P[b]
-#pragma unroll
-      for (int i = 0; i < 4; ++i)                          // 128B-swizzled K-major A operand
-        *reinterpret_cast<uint4*>(p_row + ((((g & 1) * 4 + i) ^ (row & 7)) << 4)) = pk[i];
-      if constexpr (SPLIT) {
-#pragma unroll
-        for (int i = 0; i < 4; ++i)                        // the remainder tile, two buffers further on
-          *reinterpret_cast<uint4*>(p_row + 2 * kPBytes + ((((g & 1) * 4 + i) ^ (row & 7)) << 4)) = pk_lo[i];
-      }
-      fence_proxy_async_smem();
-      mbar_arrive(&bar->p_full[b]);
-      if (col_is_x) acc_x += ksum; else acc_y += ksum;
-    } else {
-      uint32_t v[32];
-      tmem_ld_32x32(tmem + lane_addr + b * kTile + g * 32, v);
-      tmem_ld_wait();
-      tc_fence_before();
-      mbar_arrive(&bar->s_empty[b]);
-      epi_k_32<LADDER>(v, njp, ni, m2c0, ratio, p.n_scales, ksum);
-      mbar_arrive(&bar->nj_empty[b]);
-      const float fac = (u.sym && jt != u.ti) ? 2.f : 1.f;
-      if (col_is_x) acc_x = fmaf(ksum, fac, acc_x); else acc_y += ksum;
-    }
-#ifdef VGAN_B200_DEBUG
-    if (p.dbg) atomicAdd(&p.dbg[static_cast<int64_t>(blockIdx.x) * p.dbg_stride + n], ksum);
-#endif
-  }
-}
-
-#endif  // VG_TC_PINGPONG
-
 template <bool LADDER, bool SPLIT>
 __global__ void __launch_bounds__(kThreads, 1)
 mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__ CUtensorMap zmapB,

@@ -54,21 +54,40 @@ __device__ __forceinline__ float block_sum_256(float v, float* red) {
 }
 
 // 2-D thread map of the statistics kernels (round 2: one thread per column walking 32-64 rows serially left 20 of 256
-// threads busy at D = 20 and cost 30 us for 40 KB): column c = tid % cp of the pass (cp = power of two <= 256 that
-// covers the column items), row lane tid / cp; a thread strides the block's rows by the 256 / cp row lanes and the
-// lanes meet through shared memory before the block's atomics.
+// threads busy at D = 20 and cost 30 us for 40 KB).  1024 threads: column c = tid % cp of the pass (cp = power of two
+// <= 64 that covers the column items), row lane tid / cp (>= 16 of them); a thread strides the block's rows by the row
+// lanes and the lanes meet through shared memory before the block's atomics.  Few, fat blocks: every block ends in
+// atomics on the SAME addresses, which serialise at ~60 ns each (1024 blocks: 65 us at N = 65536, D = 256), so the
+// grid is at most 64-128 blocks and the bytes in flight come from the 1024 threads.
+constexpr int kStatThreads = 1024;
 __host__ __device__ inline int pow2_cols(int64_t cols) {
   int p = 1;
-  while (p < cols && p < 256) p <<= 1;
+  while (p < cols && p < 64) p <<= 1;
   return p;
+}
+// rows per block of a statistics kernel: at most max_blocks blocks, at least 4 strides of the row lanes, a multiple of
+// the row lanes
+static int64_t stat_rows_per_block(int64_t rows, int rl_n, int max_blocks) {
+  int64_t rpb = (rows + max_blocks - 1) / max_blocks;
+  if (rpb < 4 * rl_n) rpb = 4 * rl_n;
+  return (rpb + rl_n - 1) / rl_n * rl_n;
+}
+__device__ __forceinline__ float block_sum_1024(float v, float* red) {     // red[32]; result valid in thread 0
+  v = warp_sum(v);
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  float t = 0.f;
+  if (threadIdx.x < 32) t = warp_sum(red[threadIdx.x]);
+  return t;
 }
 
 // ---- generic statistics: rows q of the range's stack [X rows rb..xe ; Y rows rb..ye), and the column maxima of the
 // U rows that belong to the block's X rows (cpu = pow2_cols(D_u))
-__global__ void __launch_bounds__(256) colstats_kernel(PackArgs a, int rows_per_block, int cp, int cpu) {
-  __shared__ float part[2][256];
-  __shared__ unsigned long long kpart[256];
-  __shared__ float red[8];
+__global__ void __launch_bounds__(kStatThreads) colstats_kernel(PackArgs a, int rows_per_block, int cp, int cpu) {
+  __shared__ float part[2][kStatThreads];
+  __shared__ unsigned long long kpart[kStatThreads];
+  __shared__ float red[32];
   const int64_t xe = min(a.re, a.Nx), ye = min(a.re, a.Ny);
   const int64_t nX = max(xe - a.rb, static_cast<int64_t>(0)), nY = max(ye - a.rb, static_cast<int64_t>(0));
   const int64_t q0 = static_cast<int64_t>(blockIdx.x) * rows_per_block;
@@ -76,7 +95,7 @@ __global__ void __launch_bounds__(256) colstats_kernel(PackArgs a, int rows_per_
   const int64_t qx1 = min(q1, nX), qy0 = max(q0, nX);       // X rows [q0, qx1), Y rows [qy0, q1) of the stack
   const int tid = threadIdx.x;
   {
-    const int c = tid & (cp - 1), rl = tid / cp, rl_n = 256 / cp;
+    const int c = tid & (cp - 1), rl = tid / cp, rl_n = kStatThreads / cp;
     float sqx = 0.f, sqy = 0.f;
     for (int64_t f0 = 0; f0 < a.D; f0 += cp) {
       const int64_t f = f0 + c;
@@ -96,27 +115,25 @@ __global__ void __launch_bounds__(256) colstats_kernel(PackArgs a, int rows_per_
           sqy = fmaf(v, v, sqy);
         }
       }
-      if (rl_n > 1) {            // (block-uniform; the column loop then runs once)
-        part[0][tid] = cx;
-        part[1][tid] = cy;
-        __syncthreads();
-        if (rl == 0)
-          for (int k = c + cp; k < 256; k += cp) { cx += part[0][k]; cy += part[1][k]; }
-      }
-      if (rl == 0 && f < a.D) {
+      __syncthreads();           // the previous column pass has been read
+      part[0][tid] = cx;
+      part[1][tid] = cy;
+      __syncthreads();
+      if (rl == 0 && f < a.D) {  // the row lanes meet
+        for (int k = c + cp; k < kStatThreads; k += cp) { cx += part[0][k]; cy += part[1][k]; }
         if (q0 < nX) atomicAdd(&a.stats[2 + f], static_cast<double>(cx));
         if (q1 > nX) atomicAdd(&a.stats[2 + a.Dp + f], static_cast<double>(cy));
       }
     }
-    const float tx = block_sum_256(sqx, red);
-    const float ty = block_sum_256(sqy, red);
+    const float tx = block_sum_1024(sqx, red);
+    const float ty = block_sum_1024(sqy, red);
     if (tid == 0) {
       if (tx != 0.f) atomicAdd(&a.stats[0], static_cast<double>(tx));
       if (ty != 0.f) atomicAdd(&a.stats[1], static_cast<double>(ty));
     }
   }
   if (a.cmax && q0 < qx1) {
-    const int c = tid & (cpu - 1), rl = tid / cpu, rl_n = 256 / cpu;
+    const int c = tid & (cpu - 1), rl = tid / cpu, rl_n = kStatThreads / cpu;
     for (int64_t d0 = 0; d0 < a.D_u; d0 += cpu) {
       const int64_t d = d0 + c;
       unsigned long long best = 0ull;
@@ -127,25 +144,27 @@ __global__ void __launch_bounds__(256) colstats_kernel(PackArgs a, int rows_per_
           best = key > best ? key : best;
         }
       }
-      if (rl_n > 1) {
-        kpart[tid] = best;
-        __syncthreads();
-        if (rl == 0)
-          for (int k = c + cpu; k < 256; k += cpu) best = kpart[k] > best ? kpart[k] : best;
+      __syncthreads();
+      kpart[tid] = best;
+      __syncthreads();
+      if (rl == 0 && d < a.D_u) {
+        for (int k = c + cpu; k < kStatThreads; k += cpu) best = kpart[k] > best ? kpart[k] : best;
+        atomicMax(&a.cmax[d], best);
       }
-      if (rl == 0 && d < a.D_u) atomicMax(&a.cmax[d], best);
     }
   }
 }
 
 // ---- masked fast path (Y = U*X, Nx == Ny, D % 4 == 0, 16-byte aligned inputs): X and U are read ONCE per pass
 // for both halves of the stack, with 16-byte loads; the column maxima of U ride along.  cp = pow2_cols(D / 4).
-__global__ void __launch_bounds__(256) colstats_masked_kernel(PackArgs a, int rows_per_block, int cp) {
-  __shared__ float4 pcx[256], pcy[256];
-  __shared__ unsigned long long pkey[4][256];
-  __shared__ float red[8];
+__global__ void __launch_bounds__(kStatThreads) colstats_masked_kernel(PackArgs a, int rows_per_block, int cp) {
+  __shared__ __align__(16) unsigned char buf[2 * kStatThreads * 16];     // sums, then keys: 32 KiB
+  __shared__ float red[32];
+  float4* pcx = reinterpret_cast<float4*>(buf);
+  float4* pcy = pcx + kStatThreads;
+  unsigned long long* pkey = reinterpret_cast<unsigned long long*>(buf);   // [4][1024]
   const int tid = threadIdx.x;
-  const int c = tid & (cp - 1), rl = tid / cp, rl_n = 256 / cp;
+  const int c = tid & (cp - 1), rl = tid / cp, rl_n = kStatThreads / cp;
   const int64_t r0 = a.rb + static_cast<int64_t>(blockIdx.x) * rows_per_block;
   const int64_t r1 = min(r0 + rows_per_block, min(a.re, a.Nx));
   const int64_t D4 = a.D >> 2;
@@ -175,34 +194,41 @@ __global__ void __launch_bounds__(256) colstats_masked_kernel(PackArgs a, int ro
         }
       }
     }
-    if (rl_n > 1) {              // (block-uniform; the column loop then runs once)
-      pcx[tid] = cx; pcy[tid] = cy;
-      pkey[0][tid] = m0; pkey[1][tid] = m1; pkey[2][tid] = m2; pkey[3][tid] = m3;
-      __syncthreads();
-      if (rl == 0)
-        for (int k = c + cp; k < 256; k += cp) {
-          const float4 x = pcx[k], y = pcy[k];
-          cx.x += x.x; cx.y += x.y; cx.z += x.z; cx.w += x.w;
-          cy.x += y.x; cy.y += y.y; cy.z += y.z; cy.w += y.w;
-          m0 = pkey[0][k] > m0 ? pkey[0][k] : m0; m1 = pkey[1][k] > m1 ? pkey[1][k] : m1;
-          m2 = pkey[2][k] > m2 ? pkey[2][k] : m2; m3 = pkey[3][k] > m3 ? pkey[3][k] : m3;
-        }
-    }
-    if (rl == 0 && f4 < D4) {
+    const bool owner = rl == 0 && f4 < D4;
+    __syncthreads();             // the previous column pass has been read
+    pcx[tid] = cx; pcy[tid] = cy;
+    __syncthreads();
+    if (owner) {                 // the row lanes meet
+      for (int k = c + cp; k < kStatThreads; k += cp) {
+        const float4 x = pcx[k], y = pcy[k];
+        cx.x += x.x; cx.y += x.y; cx.z += x.z; cx.w += x.w;
+        cy.x += y.x; cy.y += y.y; cy.z += y.z; cy.w += y.w;
+      }
       double* sx = a.stats + 2 + 4 * f4;
       double* sy = a.stats + 2 + a.Dp + 4 * f4;
       atomicAdd(sx + 0, static_cast<double>(cx.x)); atomicAdd(sx + 1, static_cast<double>(cx.y));
       atomicAdd(sx + 2, static_cast<double>(cx.z)); atomicAdd(sx + 3, static_cast<double>(cx.w));
       atomicAdd(sy + 0, static_cast<double>(cy.x)); atomicAdd(sy + 1, static_cast<double>(cy.y));
       atomicAdd(sy + 2, static_cast<double>(cy.z)); atomicAdd(sy + 3, static_cast<double>(cy.w));
-      if (a.cmax) {
+    }
+    if (a.cmax) {                // (block-uniform)
+      __syncthreads();           // the sums have been read: the buffer now carries the keys
+      pkey[tid] = m0; pkey[kStatThreads + tid] = m1; pkey[2 * kStatThreads + tid] = m2; pkey[3 * kStatThreads + tid] = m3;
+      __syncthreads();
+      if (owner) {
+        for (int k = c + cp; k < kStatThreads; k += cp) {
+          m0 = pkey[k] > m0 ? pkey[k] : m0;
+          m1 = pkey[kStatThreads + k] > m1 ? pkey[kStatThreads + k] : m1;
+          m2 = pkey[2 * kStatThreads + k] > m2 ? pkey[2 * kStatThreads + k] : m2;
+          m3 = pkey[3 * kStatThreads + k] > m3 ? pkey[3 * kStatThreads + k] : m3;
+        }
         atomicMax(a.cmax + 4 * f4 + 0, m0); atomicMax(a.cmax + 4 * f4 + 1, m1);
         atomicMax(a.cmax + 4 * f4 + 2, m2); atomicMax(a.cmax + 4 * f4 + 3, m3);
       }
     }
   }
-  const float tx = block_sum_256(sqx, red);
-  const float ty = block_sum_256(sqy, red);
+  const float tx = block_sum_1024(sqx, red);
+  const float ty = block_sum_1024(sqy, red);
   if (tid == 0) {
     atomicAdd(&a.stats[0], static_cast<double>(tx));
     atomicAdd(&a.stats[1], static_cast<double>(ty));
@@ -493,19 +519,19 @@ int run_stats(const vgan_b200_layout_t& L, void* ws, const float* X, const float
   if (nY < 0) nY = 0;
   const int64_t rows = nX + nY;
   if (rows <= 0) return VGAN_B200_OK;       // an empty shard only takes part in the exchanges
-  // rows per block: 8 (masked: 16-byte loads) or 4 (generic) strides of the row lanes, doubled until at most 1024 blocks
-  // (every block ends in 2-12 double atomics per column)
+  // at most 64 (small problems) or 128 blocks: every block ends in 2 + 2-3 D atomics on the same addresses
   if (masked_fast(a)) {
     const int cp = pow2_cols(L.D >> 2);
-    int64_t rpb = (256 / cp) * 8;
-    while ((nX + rpb - 1) / rpb > 1024) rpb *= 2;
-    colstats_masked_kernel<<<static_cast<unsigned>((nX + rpb - 1) / rpb), 256, 0, st>>>(a, static_cast<int>(rpb), cp);
+    const int64_t rpb = stat_rows_per_block(nX, kStatThreads / cp, nX < 16384 ? 64 : 128);
+    colstats_masked_kernel<<<static_cast<unsigned>((nX + rpb - 1) / rpb), kStatThreads, 0, st>>>(
+        a, static_cast<int>(rpb), cp);
     count_launch();
   } else {
     const int cp = pow2_cols(L.D), cpu = pow2_cols(L.D_u > 0 ? L.D_u : 1);
-    int64_t rpb = (256 / cp) * 4;
-    while ((rows + rpb - 1) / rpb > 1024) rpb *= 2;
-    colstats_kernel<<<static_cast<unsigned>((rows + rpb - 1) / rpb), 256, 0, st>>>(a, static_cast<int>(rpb), cp, cpu);
+    const int rl_max = kStatThreads / (cp < cpu ? cp : cpu);
+    const int64_t rpb = stat_rows_per_block(rows, rl_max, rows < 16384 ? 64 : 128);
+    colstats_kernel<<<static_cast<unsigned>((rows + rpb - 1) / rpb), kStatThreads, 0, st>>>(a, static_cast<int>(rpb),
+                                                                                           cp, cpu);
     count_launch();
   }
   VG_CUDA_CHECK(cudaGetLastError());
