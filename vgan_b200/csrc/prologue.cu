@@ -250,21 +250,21 @@ struct ScaleArgs {
   float* misc;
 };
 
-__device__ __forceinline__ double block_sum_256d(double v, double* red) {
-  red[threadIdx.x] = v;
+__device__ __forceinline__ double block_sum_256d(double v, double* red) {   // red[8]; result valid in every thread
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  __syncthreads();               // the previous sum has been read
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
   __syncthreads();
-  for (int s = 128; s > 0; s >>= 1) {
-    if (threadIdx.x < s) red[threadIdx.x] += red[threadIdx.x + s];
-    __syncthreads();
-  }
-  const double t = red[0];
-  __syncthreads();
-  return t;   // valid in every thread
+  double t = 0.0;
+#pragma unroll
+  for (int w = 0; w < 8; ++w) t += red[w];
+  return t;
 }
 
 // bandwidth = sum_ij |zi-zj|^2 / (n^2-n) = (2n sum|z|^2 - 2 |sum z|^2) / (n^2-n)   (Mmd_loss_constrained.py:16-22)
 __global__ void __launch_bounds__(256) scales_kernel(ScaleArgs a) {
-  __shared__ double red[256];
+  __shared__ double red[8];
   __shared__ float sh[16];
   const double* csx = a.stats + 2;
   const double* csy = a.stats + 2 + a.Dp;
