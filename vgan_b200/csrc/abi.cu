@@ -254,6 +254,8 @@ static int run_tc(vgan_b200_ctx* ctx, const vgan_b200_layout_t& L, void* ws, con
   const int ladder = (flags & VGAN_B200_LADDER) ? 1 : 0;
   p.cs = p.nslices < 4 ? p.nslices : 4;
   p.ngroups = (p.nslices + p.cs - 1) / p.cs;
+  // (D_p = 256 stays on mmd_tc.cu: on the CTA-pair kernel, as clusters of one pair, it measured 11.3 against 9.7 ms
+  // at N = 65536 and 217 against 82 us at N = 4096 — profiles/r2n7_pair_at_256.txt)
   const bool multi_slice = p.pv && p.nslices >= 2;
   CUtensorMap map, mapB, mapV, mapB64, mapV64, mapB256;
   if (int e = get_tmap_bf16_2d(ctx, &map, p.zq, rows, width)) return e;

@@ -44,12 +44,13 @@ constexpr int kWarpTma = kNumEpiWarps, kWarpMma = kNumEpiWarps + 1, kWarpNorms =
               kWarpAlloc = kNumEpiWarps + 3;
 constexpr int kSmemLimit = 232448;
 constexpr int kEpiGroupThreads = kNumEpiThreads / 2;   // two epilogue groups of 8 warps alternate over the column tiles
+constexpr int kNjBufs = 4;   // column-norm buffers: the norms of tile n + 2 (same epilogue group) load while tile n is computed
 constexpr int kLag = 3;   // the Gram stream runs this many column tiles ahead of the gradient GEMM (see the MMA warp)
 
 struct __align__(8) TcBarriers {
   uint64_t ring_full[kStagesMax], ring_empty[kStagesMax];
   uint64_t s_full[2], s_empty[2];
-  uint64_t nj_full[2], nj_empty[2];
+  uint64_t nj_full[kNjBufs], nj_empty[kNjBufs];
   uint64_t p_full[2], p_empty[2];
   uint64_t o_full, zi_full;
   uint32_t tmem_base;
@@ -63,7 +64,7 @@ static_assert(sizeof(TcBarriers) <= 1024, "barrier block");
 // (three passes of the plain kernel recomputed the Gram and the whole epilogue three times).  Four P buffers
 // instead of two.
 //
-// Shared-memory geometry (bytes): [barriers 1 KiB][column norms 1 KiB][P buffers][Z_I resident][ring stages].
+// Shared-memory geometry (bytes): [barriers 1 KiB][column norms 2 KiB][P buffers][Z_I resident][ring stages].
 // The row operand is resident whenever it fits beside the P buffers and at least two ring stages: always on the plain
 // bf16 path (<= 4 chunks), and with split operands at D_p = 64 (hi and lo chunk: the VGAN encodings).  Otherwise
 // (split, D_p >= 128) the row operand travels through the ring with the column operand as before.
@@ -78,7 +79,7 @@ __host__ __device__ inline TcGeom tc_geom(bool split, int kchunks) {
   const int pbufs = split ? 4 : 2;
   g.res = split ? (kchunks == 1) : (kchunks <= kSliceMax / kChunk);   // (wider: forward-only calls, no gradient GEMM)
   g.zi_chunks = g.res ? (split ? 2 * kchunks : kchunks) : 0;
-  g.off_p = 2048;
+  g.off_p = 1024 + kNjBufs * kTile * 4;
   g.off_zi = g.off_p + pbufs * kPBytes;
   g.off_ring = g.off_zi + g.zi_chunks * kChunkBytes;
   int st = (kSmemLimit - g.off_ring) / kStageBytes;
@@ -167,13 +168,14 @@ __device__ __forceinline__ void epilogue_tiles(const TcParams& p, const Unit& u,
   const int n_tiles = u.j_end - u.j_begin;
   const int b = grp;
   const uint32_t taddr = tmem + lane_addr + b * kTile + hcol * 64;
-  const float* njp = nj_smem + b * kTile + hcol * 64;
   uint8_t* p_row = p_smem + b * kPBytes + hcol * kChunkBytes + row * 128;
   for (int n = grp; n < n_tiles; n += 2) {
     const int jt = u.j_begin + n;
     const uint32_t par = (n >> 1) & 1;
     const bool col_is_x = jt < p.tiles_x;
-    mbar_wait(&bar->nj_full[b], par);
+    const int nb = n & (kNjBufs - 1);
+    const float* njp = nj_smem + nb * kTile + hcol * 64;
+    mbar_wait(&bar->nj_full[nb], (n / kNjBufs) & 1);
     mbar_wait(&bar->s_full[b], par);
     tc_fence_after();
     float ksum = 0.f;
@@ -204,7 +206,7 @@ __device__ __forceinline__ void epilogue_tiles(const TcParams& p, const Unit& u,
         epi_core_32<LADDER, SPLIT ? kPBoth : kPHi>(v, njp + 32, ni, m2c0, cf, ratio, p.n_scales, ksum, rsum, pk, cw0,
                                                    pk_lo);
       }
-      mbar_arrive(&bar->nj_empty[b]);
+      mbar_arrive(&bar->nj_empty[nb]);
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         *reinterpret_cast<uint4*>(p_row + (((4 + i) ^ (row & 7)) << 4)) = pk[i];
@@ -223,7 +225,7 @@ __device__ __forceinline__ void epilogue_tiles(const TcParams& p, const Unit& u,
       tc_fence_before();
       mbar_arrive(&bar->s_empty[b]);
       epi_k_32<LADDER>(v, njp + 32, ni, m2c0, ratio, p.n_scales, ksum);
-      mbar_arrive(&bar->nj_empty[b]);
+      mbar_arrive(&bar->nj_empty[nb]);
       const float fac = (u.sym && jt != u.ti) ? 2.f : 1.f;
       if (col_is_x) acc_x = fmaf(ksum, fac, acc_x); else acc_y += ksum;
     }
@@ -259,10 +261,12 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__
     for (int b = 0; b < 2; ++b) {
       mbar_init(&bar->s_full[b], 1);
       mbar_init(&bar->s_empty[b], kEpiGroupThreads);
-      mbar_init(&bar->nj_full[b], 1);
-      mbar_init(&bar->nj_empty[b], kEpiGroupThreads);
       mbar_init(&bar->p_full[b], kEpiGroupThreads);
       mbar_init(&bar->p_empty[b], 1);
+    }
+    for (int b = 0; b < kNjBufs; ++b) {
+      mbar_init(&bar->nj_full[b], 1);
+      mbar_init(&bar->nj_empty[b], kEpiGroupThreads);
     }
     mbar_init(&bar->o_full, 1);
     mbar_init(&bar->zi_full, 1);
@@ -363,8 +367,8 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__
     if (lane == 0) {
       for (int n = 0; n < n_tiles; ++n) {
         const int jt = u.j_begin + n;
-        const int b = n & 1;
-        mbar_wait(&bar->nj_empty[b], ((n >> 1) & 1) ^ 1);   // epilogue done with nj[b]
+        const int b = n & (kNjBufs - 1);
+        mbar_wait(&bar->nj_empty[b], ((n / kNjBufs) & 1) ^ 1);   // epilogue done with nj[b]
         mbar_arrive_expect_tx(&bar->nj_full[b], kTile * 4);
         bulk_load_1d(nj_smem + b * kTile, p.nrms + static_cast<int64_t>(jt) * kTile, kTile * 4,
                      &bar->nj_full[b]);
@@ -554,9 +558,9 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__
       rs_smem[g * kTile + row] = rsum;
       asm volatile("bar.sync 1, %0;" ::"n"(kNumEpiThreads) : "memory");
       const float rtot = rs_smem[row] + rs_smem[kTile + row] + rs_smem[2 * kTile + row] + rs_smem[3 * kTile + row];
-      if (g < 2)                                        // two column halves of the slice, as in the other kernels
-        write_grad_rows(p, tmem_o, lane_addr, g, row, u.ti, u.row_is_x, u.slice, slice_chunks, rtot,
-                        p.col_split > 1, u.first != 0);
+      if (warp < 8)       // O through the ring (dead: every stage was consumed by an MMA that has completed)
+        write_grad_rows(p, tmem_o, reinterpret_cast<float*>(ring), reinterpret_cast<float*>(p_smem + 4096), u.ti,
+                        u.row_is_x, u.slice, slice_chunks, rtot, p.col_split > 1, u.first != 0);
     }
   }
 

@@ -223,7 +223,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt_begin));
   // resident now: the host makes the S_xx launch wait until every persistent CTA has counted itself in
   if (p.started && threadIdx.x == 0) atomicAdd(p.started, 1u);
-  long long tm_tail = 0;
+  long long tm_tail = 0, tm_t1 = 0, tm_t2 = 0, tm_t3 = 0;   // tail: barrier #1, row-sum exchange + #2, gradient rows
   float* rsx = reinterpret_cast<float*>(smem + kQSmemP);       // [CS][128] row-sum exchange, reuses P slot 0
 
   if (warp >= 8) {
@@ -579,6 +579,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
     const long long tq_tail = VG_CLK();
     tc_fence_before();
     cluster_sync_all();      // #1: no CTA of the cluster reads a P slot any more
+    const long long tq_s1 = VG_CLK();
     if (warp < 4) {
       const int row = warp * 32 + lane;
       const float tot = nj_smem[row] + nj_smem[kTile + row];     // both column halves of this CTA's tiles
@@ -586,19 +587,22 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
       for (int d = 0; d < CS; ++d) st_cluster_f32(mapa_u32(a, static_cast<uint32_t>(2 * d + hh)), tot);
     }
     cluster_sync_all();      // #2: all partial row sums have arrived
+    const long long tq_s2 = VG_CLK();
     if (warp < 8) {
-      const int q = warp & 3, g = warp >> 2;
-      const int row = q * 32 + lane;
+      const int row = (warp & 3) * 32 + lane;
       float rtot = 0.f;
       for (int d = 0; d < CS; ++d) rtot += rsx[d * kTile + row];
       tc_fence_after();
-      if (!dup)
-        write_grad_rows(p, tmem_o, static_cast<uint32_t>(q * 32) << 16, g, row, ti, row_is_x, slice, slice_chunks,
-                        rtot, partial, r0 == 0);
+      if (!dup)           // O through P slots 1 and 2 (dead since cluster barrier #1; slot 0 holds the row-sum exchange)
+        write_grad_rows(p, tmem_o, reinterpret_cast<float*>(smem + kQSmemP + kQPBytes),
+                        reinterpret_cast<float*>(smem + kQSmemP + 8192), ti, row_is_x, slice, slice_chunks, rtot, partial,
+                        r0 == 0);
     }
+    const long long tq_w = VG_CLK();
     tc_fence_before();
     cluster_sync_all();      // #3: O, the norm buffers and P slot 0 may be reused by the next range
     tm_tail += VG_CLK() - tq_tail;
+    tm_t1 += tq_s1 - tq_tail; tm_t2 += tq_s2 - tq_s1; tm_t3 += tq_w - tq_s2;
     }
   }
 
@@ -616,14 +620,17 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
       asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt_end));
       d[13] = static_cast<float>(gt_end - gt_begin);
     }
-    if (warp == 0) d[14] = static_cast<float>(tm_tail);
+    if (warp == 0) {
+      d[14] = static_cast<float>(tm_tail);
+      d[16] = static_cast<float>(tm_t1); d[17] = static_cast<float>(tm_t2); d[18] = static_cast<float>(tm_t3);
+    }
   }
   if (p.timeline && threadIdx.x == 0) {
     atomicMin(&p.timeline[0], gt_begin);
     atomicMax(&p.timeline[1], global_timer_ns());
   }
 #else
-  (void)tm0; (void)tm1; (void)tm2; (void)tm3; (void)tm_tail; (void)t_begin; (void)gt_begin;
+  (void)tm0; (void)tm1; (void)tm2; (void)tm3; (void)tm_tail; (void)tm_t1; (void)tm_t2; (void)tm_t3; (void)t_begin; (void)gt_begin;
 #endif
   if (warp == 11) tmem_dealloc_2cta(tmem, 512);
 }

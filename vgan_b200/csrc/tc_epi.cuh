@@ -182,122 +182,164 @@ __device__ __forceinline__ float warp_transpose_sum(float (&v)[32], int lane) {
 // O' and rtot' come from P' = c_j (w_ij - w0) and A, B (scales_kernel) are the closed-form common-mode remainder
 // sum_j c_j w0 (z_j - z_i).  The expression is linear in (O', rtot'): a unit cut into column ranges adds the ranges'
 // results (accumulate), and only the range that starts at column round 0 (`first_range`) adds A and B.
-// Thread = (row, column half g); O columns of the slice live at tmem_o.  Column sums of the Y rows written go to
-// p.colsum (the D-vector of the step: colsum_i dL/dU[i,:] on the masked path).
-__device__ __forceinline__ void write_grad_rows(const TcParams& p, uint32_t tmem_o, uint32_t lane_addr, int g,
-                                                int row, int ti, int row_is_x, int slice, int slice_chunks,
-                                                float rtot, bool accumulate, bool first_range) {
-  const int lane = threadIdx.x & 31;
+// Column sums of the Y rows written go to p.colsum (the D-vector of the step: colsum_i dL/dU[i,:] on the masked path).
+//
+// Called by 256 threads = warps 0-7 of the CTA (warp % 4 = TMEM lane quadrant), with their own named barrier.
+// TMEM hands a thread ONE ROW of O; read that way from global memory (round 1: a thread walked its row of X, U, the
+// multiplier and the output in 16-byte steps) a warp touches 32 rows per instruction — the gradient rows of one work
+// range took 68 000 cycles in the pair kernel, 37 % of the kernel at N = 4096 (tools/gpu_cluster_timers.py).  Now O
+// goes through shared memory, 128 columns at a time (`stage`: [128 rows][128 columns] fp32, 16-byte chunks XOR-swizzled
+// by the row so that both the row-wise writes and the row-contiguous reads are conflict-free), and a warp then handles
+// one row at a time with its lanes along the features: every global access is a contiguous 512-byte segment, the
+// per-feature constants stay in registers, and the column sums accumulate per lane (no warp transposes).
+//   stage: 64 KiB, aux: (1 + 8) x 128 floats; both dead operand memory of the caller.  rtot: row sum of P' of the
+//   calling thread's row (row = (warp % 4) * 32 + lane).
+__device__ __forceinline__ void write_grad_rows(const TcParams& p, uint32_t tmem_o, float* stage, float* aux, int ti,
+                                                int row_is_x, int slice, int slice_chunks, float rtot,
+                                                bool accumulate, bool first_range) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int q = warp & 3, g = warp >> 2;
+  const int row = q * 32 + lane;
+  const uint32_t lane_addr = static_cast<uint32_t>(q * 32) << 16;
   const int slice_w = slice_chunks * kChunk;
-  const int64_t region_row = static_cast<int64_t>(row_is_x ? ti : ti - p.tiles_x) * kTile + row;
+  const int64_t tile_row0 = static_cast<int64_t>(row_is_x ? ti : ti - p.tiles_x) * kTile;
   const int64_t n_region = row_is_x ? p.Nx : p.Ny;
-  const bool row_ok = region_row < n_region && region_row >= p.row_begin && region_row < p.row_end;
   const float ci4 = 4.f * (row_is_x ? 1.f / static_cast<float>(p.Nx) : -1.f / static_cast<float>(p.Ny));
-  float* out = (row_is_x ? p.dX : p.dY) + (region_row - p.row_begin) * p.D;
-  const float* mul = (!row_is_x && p.dY_mul) ? p.dY_mul + (region_row - p.row_begin) * p.D : nullptr;
-  // unrounded z_i = input row - centring mean (rows outside the range are never dereferenced: the callers of a
-  // multi-GPU job pass pointers that are only valid for their own rows)
-  const float* xrow = p.Xf + region_row * p.D;
-  const float* yrow = p.Yf ? p.Yf + region_row * p.D : nullptr;
-  const float* urow = p.Uf ? p.Uf + region_row * p.D : nullptr;
-  const bool zvec = (p.D & 3) == 0 && (reinterpret_cast<uintptr_t>(p.Xf) & 15) == 0 &&
-                    (!p.Yf || (reinterpret_cast<uintptr_t>(p.Yf) & 15) == 0) &&
-                    (!p.Uf || (reinterpret_cast<uintptr_t>(p.Uf) & 15) == 0);
-  if (p.pass_flags & kPassNoRowsum) rtot = 0.f;
+  float* out_base = row_is_x ? p.dX : p.dY;
+  const float* mul_base = (!row_is_x && p.dY_mul) ? p.dY_mul : nullptr;
   const bool cmode = first_range && !(p.pass_flags & kPassNoRowsum);
-  if (cmode) rtot += p.par[kParB + (row_is_x ? 0 : 1)];
   const float* cmv = p.cm + (row_is_x ? 0 : p.Dp);
   accumulate = accumulate || (p.pass_flags & kPassAccumulate);
   const int f_slice = slice * p.slice_chunks * kChunk;
-  const bool vec_ok = (p.D & 3) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0 &&
-                      (!mul || (reinterpret_cast<uintptr_t>(mul) & 15) == 0);
-  const bool want_colsum = p.colsum != nullptr && !row_is_x;       // warp-uniform
-  for (int cc = 0; cc < slice_chunks; ++cc) {
-    const int col = g * (slice_w / 2) + cc * 32;
-    uint32_t v[32];
-    tmem_ld_32x32(tmem_o + lane_addr + col, v);
-    tmem_ld_wait();
-    float cs[32];
+  // 16-byte accesses: rows are 16-byte aligned when D % 4 == 0 and the bases are
+  const bool vec = (p.D & 3) == 0 && (reinterpret_cast<uintptr_t>(p.Xf) & 15) == 0 &&
+                   (!p.Yf || (reinterpret_cast<uintptr_t>(p.Yf) & 15) == 0) &&
+                   (!p.Uf || (reinterpret_cast<uintptr_t>(p.Uf) & 15) == 0) &&
+                   (reinterpret_cast<uintptr_t>(out_base) & 15) == 0 &&
+                   (!mul_base || (reinterpret_cast<uintptr_t>(mul_base) & 15) == 0);
+  const bool want_colsum = p.colsum != nullptr && !row_is_x;
+  float* rt = aux;                    // [128] row totals (with B on the first range)
+  float* csp = aux + kTile;           // [8 warps][128] column-sum partials
+  if (g == 0) {
+    float t = (p.pass_flags & kPassNoRowsum) ? 0.f : rtot;
+    if (cmode) t += p.par[kParB + (row_is_x ? 0 : 1)];
+    rt[row] = t;
+  }
+  float4* stage4 = reinterpret_cast<float4*>(stage);
+  for (int c0 = 0; c0 < slice_w; c0 += 128) {
+    // ---- phase A: this thread's row of O, columns c0 + 64 g + [0, 64), TMEM -> swizzled shared memory
 #pragma unroll
-    for (int e = 0; e < 32; ++e) cs[e] = 0.f;
-    if (row_ok) {
+    for (int h = 0; h < 2; ++h) {
+      const int col = c0 + g * 64 + h * 32;
+      if (col < slice_w) {              // (warp-uniform)
+        uint32_t v[32];
+        tmem_ld_32x32(tmem_o + lane_addr + col, v);
+        tmem_ld_wait();
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        const int f0 = f_slice + col + c * 8;
-        float zv[8];
-        if (zvec && f0 + 8 <= p.D) {
-          float4 a0, a1;
-          if (row_is_x) {
-            a0 = *reinterpret_cast<const float4*>(xrow + f0); a1 = *reinterpret_cast<const float4*>(xrow + f0 + 4);
-          } else if (yrow) {
-            a0 = *reinterpret_cast<const float4*>(yrow + f0); a1 = *reinterpret_cast<const float4*>(yrow + f0 + 4);
-          } else {
-            const float4 x0 = *reinterpret_cast<const float4*>(xrow + f0), x1 = *reinterpret_cast<const float4*>(xrow + f0 + 4);
-            const float4 u0 = *reinterpret_cast<const float4*>(urow + f0), u1 = *reinterpret_cast<const float4*>(urow + f0 + 4);
-            a0 = make_float4(u0.x * x0.x, u0.y * x0.y, u0.z * x0.z, u0.w * x0.w);
-            a1 = make_float4(u1.x * x1.x, u1.y * x1.y, u1.z * x1.z, u1.w * x1.w);
-          }
-          const float4 m0 = *reinterpret_cast<const float4*>(p.mean + f0), m1 = *reinterpret_cast<const float4*>(p.mean + f0 + 4);
-          zv[0] = a0.x - m0.x; zv[1] = a0.y - m0.y; zv[2] = a0.z - m0.z; zv[3] = a0.w - m0.w;
-          zv[4] = a1.x - m1.x; zv[5] = a1.y - m1.y; zv[6] = a1.z - m1.z; zv[7] = a1.w - m1.w;
-        } else {
-#pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            const int f = f0 + e;
-            float raw = 0.f, mu = 0.f;
-            if (f < p.D) {
-              raw = row_is_x ? xrow[f] : (yrow ? yrow[f] : urow[f] * xrow[f]);
-              mu = p.mean[f];
-            }
-            zv[e] = raw - mu;
-          }
-        }
-        float av[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-        if (cmode) {
-          const float4 a0 = *reinterpret_cast<const float4*>(cmv + f0), a1 = *reinterpret_cast<const float4*>(cmv + f0 + 4);
-          av[0] = a0.x; av[1] = a0.y; av[2] = a0.z; av[3] = a0.w; av[4] = a1.x; av[5] = a1.y; av[6] = a1.z; av[7] = a1.w;
-        }
-        float gv[8];
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          gv[e] = ci4 * ((__uint_as_float(v[c * 8 + e]) + av[e]) - rtot * zv[e]);
-        }
-        if (vec_ok && f0 + 8 <= p.D) {
-          // 16-byte accesses (rows are 16-byte aligned when D % 4 == 0)
-          if (mul) {
-            const float4 m0 = *reinterpret_cast<const float4*>(mul + f0), m1 = *reinterpret_cast<const float4*>(mul + f0 + 4);
-            gv[0] *= m0.x; gv[1] *= m0.y; gv[2] *= m0.z; gv[3] *= m0.w;
-            gv[4] *= m1.x; gv[5] *= m1.y; gv[6] *= m1.z; gv[7] *= m1.w;
-          }
-          if (accumulate) {     // unit shared between CTAs (column ranges / stream-K cut) or a BF16X3 pass: red.v4.f32
-            atomicAdd(reinterpret_cast<float4*>(out + f0), make_float4(gv[0], gv[1], gv[2], gv[3]));
-            atomicAdd(reinterpret_cast<float4*>(out + f0 + 4), make_float4(gv[4], gv[5], gv[6], gv[7]));
-          } else {
-            *reinterpret_cast<float4*>(out + f0) = make_float4(gv[0], gv[1], gv[2], gv[3]);
-            *reinterpret_cast<float4*>(out + f0 + 4) = make_float4(gv[4], gv[5], gv[6], gv[7]);
-          }
-#pragma unroll
-          for (int e = 0; e < 8; ++e) cs[c * 8 + e] = gv[e];
-        } else {
-#pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            const int f = f0 + e;
-            if (f < p.D) {
-              float gval = gv[e];
-              if (mul) gval *= mul[f];
-              if (accumulate) atomicAdd(out + f, gval);   // unit shared between clusters (stream-K cut) / BF16X3 pass
-              else out[f] = gval;
-              cs[c * 8 + e] = gval;
-            }
-          }
+        for (int j = 0; j < 8; ++j) {
+          const int chunk = g * 16 + h * 8 + j;
+          stage4[row * 32 + (chunk ^ (row & 31))] =
+              make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]),
+                          __uint_as_float(v[4 * j + 3]));
         }
       }
     }
-    if (want_colsum) {
-      const float tot = warp_transpose_sum(cs, lane);
-      const int f = f_slice + col + lane;
-      if (f < p.D) atomicAdd(p.colsum + f, static_cast<double>(tot));
+    asm volatile("bar.sync 2, 256;" ::: "memory");
+    // ---- phase B: warp w takes rows w, w + 8, ...; lane l the features f0 .. f0 + 3 of every row
+    const int f0 = f_slice + c0 + 4 * lane;
+    const bool lane_on = c0 + 4 * lane < slice_w && f0 < p.D;
+    const bool lane_vec = lane_on && vec && f0 + 4 <= p.D;
+    float mean4[4] = {0.f, 0.f, 0.f, 0.f}, av4[4] = {0.f, 0.f, 0.f, 0.f}, cs[4] = {0.f, 0.f, 0.f, 0.f};
+    if (lane_on) {
+#pragma unroll
+      for (int e = 0; e < 4; ++e)
+        if (f0 + e < p.D) {
+          mean4[e] = p.mean[f0 + e];
+          if (cmode) av4[e] = cmv[f0 + e];
+        }
     }
+    if (lane_vec) {
+      // four rows per step, every load of the step issued before its first store (a row at a time the loop ran at
+      // one memory latency per row: 32 rows x ~1 500 cycles per range)
+      for (int rr = 0; rr < kTile / 8; rr += 4) {
+        float4 o[4], a[4], m[4];
+        bool ok[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const int r = (rr + k) * 8 + warp;
+          const int64_t region_row = tile_row0 + r;
+          // (rows outside the range are never dereferenced: the callers of a multi-GPU job pass pointers that are
+          // only valid for their own rows)
+          ok[k] = region_row < n_region && region_row >= p.row_begin && region_row < p.row_end;   // warp-uniform
+          o[k] = a[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+          m[k] = make_float4(1.f, 1.f, 1.f, 1.f);
+          if (ok[k]) {
+            const int64_t in_off = region_row * p.D + f0;
+            o[k] = stage4[r * 32 + (lane ^ (r & 31))];
+            if (row_is_x) {
+              a[k] = __ldg(reinterpret_cast<const float4*>(p.Xf + in_off));
+            } else if (p.Yf) {
+              a[k] = __ldg(reinterpret_cast<const float4*>(p.Yf + in_off));
+            } else {
+              const float4 x = __ldg(reinterpret_cast<const float4*>(p.Xf + in_off));
+              const float4 u = __ldg(reinterpret_cast<const float4*>(p.Uf + in_off));
+              a[k] = make_float4(u.x * x.x, u.y * x.y, u.z * x.z, u.w * x.w);
+            }
+            if (mul_base) m[k] = __ldg(reinterpret_cast<const float4*>(mul_base + (region_row - p.row_begin) * p.D + f0));
+          }
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          if (!ok[k]) continue;
+          const int r = (rr + k) * 8 + warp;
+          const float rtr = rt[r];
+          // unrounded z_i = input row - centring mean
+          float4 gv;
+          gv.x = ci4 * ((o[k].x + av4[0]) - rtr * (a[k].x - mean4[0])) * m[k].x;
+          gv.y = ci4 * ((o[k].y + av4[1]) - rtr * (a[k].y - mean4[1])) * m[k].y;
+          gv.z = ci4 * ((o[k].z + av4[2]) - rtr * (a[k].z - mean4[2])) * m[k].z;
+          gv.w = ci4 * ((o[k].w + av4[3]) - rtr * (a[k].w - mean4[3])) * m[k].w;
+          cs[0] += gv.x; cs[1] += gv.y; cs[2] += gv.z; cs[3] += gv.w;
+          float4* out = reinterpret_cast<float4*>(out_base + (tile_row0 + r - p.row_begin) * p.D + f0);
+          if (accumulate) atomicAdd(out, gv);     // unit shared between CTAs (column ranges / stream-K cut) or a BF16X3 pass
+          else *out = gv;
+        }
+      }
+    } else if (lane_on) {
+      for (int rr = 0; rr < kTile / 8; ++rr) {
+        const int r = rr * 8 + warp;
+        const int64_t region_row = tile_row0 + r;
+        if (!(region_row < n_region && region_row >= p.row_begin && region_row < p.row_end)) continue;
+        const float4 o = stage4[r * 32 + (lane ^ (r & 31))];
+        const float ov[4] = {o.x, o.y, o.z, o.w};
+        const float rtr = rt[r];
+        const int64_t in_off = region_row * p.D + f0;
+        const int64_t out_off = (region_row - p.row_begin) * p.D + f0;
+#pragma unroll
+        for (int e = 0; e < 4; ++e)
+          if (f0 + e < p.D) {
+            const float raw = row_is_x ? p.Xf[in_off + e] : (p.Yf ? p.Yf[in_off + e] : p.Uf[in_off + e] * p.Xf[in_off + e]);
+            float gval = ci4 * ((ov[e] + av4[e]) - rtr * (raw - mean4[e]));
+            if (mul_base) gval *= mul_base[out_off + e];
+            cs[e] += gval;
+            if (accumulate) atomicAdd(out_base + out_off + e, gval);
+            else out_base[out_off + e] = gval;
+          }
+      }
+    }
+    if (want_colsum) {      // (CTA-uniform)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) csp[warp * kTile + 4 * lane + e] = cs[e];
+      asm volatile("bar.sync 2, 256;" ::: "memory");
+      if (threadIdx.x < kTile) {
+        float t = 0.f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) t += csp[w * kTile + threadIdx.x];
+        const int f = f_slice + c0 + static_cast<int>(threadIdx.x);
+        if (c0 + static_cast<int>(threadIdx.x) < slice_w && f < p.D) atomicAdd(p.colsum + f, static_cast<double>(t));
+      }
+    }
+    asm volatile("bar.sync 2, 256;" ::: "memory");      // the stage (and the partials) may be rewritten
   }
 }
 
