@@ -37,6 +37,7 @@ print(f"{groups} groups, cycles per round (4 tiles), {R:.0f} rounds per group:")
 print("  (raw, cycles per group) kernel total %.0f  tail %.0f  gram waits %.0f + %.0f  epilogue wait_s_full %.0f compute %.0f" % (
     lead[:, 12].mean(), allc[:, 14].mean(), lead[:, 0].mean(), lead[:, 1].mean(), allc[:, 4].mean(), allc[:, 5].mean()))
 print("  tail parts (cycles per group): barrier #1 %.0f  row sums + barrier #2 %.0f  gradient rows %.0f" % tuple(allc[:, i].mean() for i in (16, 17, 18)))
+print("  gradient rows (cycles per group): TMEM -> shared %.0f  rows %.0f  column sums %.0f" % tuple(allc[:, i].mean() for i in (20, 21, 22)))
 print("  Gram warp: wait_g_ring %.0f  wait_s_empty %.0f   kernel total %.0f" % (lead[:, 0].mean() / R, lead[:, 1].mean() / R, lead[:, 12].mean() / R))
 print("  PV warp:   wait_p %.0f  wait_v_ring %.0f" % (lead[:, 10].mean() / R, lead[:, 11].mean() / R))
 print("  SM clock %.0f MHz ; tail (syncs + gradient rows) %.0f cycles per round" % (1e3 * lead[:, 12].mean() / lead[:, 13].mean(), allc[:, 14].mean() / R))

@@ -528,6 +528,7 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__
     if (u.pv) epilogue_tiles<LADDER, SPLIT, true>(p, u, bar, p_smem, nj_smem, tmem, warp, lane, acc_x, acc_y, rsum);
     else epilogue_tiles<LADDER, SPLIT, false>(p, u, bar, p_smem, nj_smem, tmem, warp, lane, acc_x, acc_y, rsum);
 
+    if (u.pv && warp < 8) prefetch_grad_rows(p, u.ti, u.row_is_x, u.slice, slice_chunks);   // inputs of the gradient rows -> L2
     // ---- block sums
     acc_x = warp_sum(acc_x);
     acc_y = warp_sum(acc_y);

@@ -555,6 +555,7 @@ mmd2_tc_pair_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_const
         park(k + 1, pk1);
       }
     }
+    if (!dup) prefetch_grad_rows(p, ti, row_is_x, slice, slice_chunks);    // inputs of the gradient rows -> L2
     // ---- partial sums of this CTA's tiles
     acc_x = warp_sum(acc_x);
     acc_y = warp_sum(acc_y);

@@ -178,6 +178,32 @@ __device__ __forceinline__ float warp_transpose_sum(float (&v)[32], int lane) {
   return v[0];
 }
 
+// L2 prefetch of what write_grad_rows will read from global memory (the fp32 input rows of the unit's row tile, its
+// slice of the features): 256 threads, thread = (row, half of the slice's 128-byte lines).  Issued when the epilogue has
+// finished its last tile, so the lines arrive while the last gradient GEMMs drain; read cold under the full L2 / HBM
+// load of the other CTAs the gradient rows cost 36 000 - 53 000 cycles per work range in the pair kernel (a handful of
+// dependent DRAM round trips of several thousand cycles each, tools/gpu_cluster_timers.py).
+__device__ __forceinline__ void prefetch_grad_rows(const TcParams& p, int ti, int row_is_x, int slice, int slice_chunks) {
+  const int t = threadIdx.x & 255;
+  const int r = t & (kTile - 1), half = t >> 7;
+  const int64_t region_row = static_cast<int64_t>(row_is_x ? ti : ti - p.tiles_x) * kTile + r;
+  const int64_t n_region = row_is_x ? p.Nx : p.Ny;
+  if (!(region_row < n_region && region_row >= p.row_begin && region_row < p.row_end)) return;
+  const int f_slice = slice * p.slice_chunks * kChunk;
+  const int lines = slice_chunks * kChunk / 32;          // 128-byte lines of the slice per row
+  const float* a0 = row_is_x ? p.Xf : (p.Yf ? p.Yf : p.Uf);
+  const float* a1 = (!row_is_x && !p.Yf) ? p.Xf : nullptr;                  // masked rows: U and X
+  const float* a2 = (!row_is_x && p.dY_mul && p.dY_mul != a1 + p.row_begin * p.D) ? p.dY_mul - p.row_begin * p.D : nullptr;
+  for (int l = half; l < lines; l += 2) {
+    const int64_t f = f_slice + l * 32;
+    if (f >= p.D) break;
+    const int64_t off = region_row * p.D + f;
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(a0 + off));
+    if (a1) asm volatile("prefetch.global.L2 [%0];" ::"l"(a1 + off));
+    if (a2) asm volatile("prefetch.global.L2 [%0];" ::"l"(a2 + off));
+  }
+}
+
 // dZ rows of one unit: out[row, f] = 4 c_i (O'[row, f] + A[f] - (rtot' + B) z[row, f]) (x mul), f in the slice, where
 // O' and rtot' come from P' = c_j (w_ij - w0) and A, B (scales_kernel) are the closed-form common-mode remainder
 // sum_j c_j w0 (z_j - z_i).  The expression is linear in (O', rtot'): a unit cut into column ranges adds the ranges'
@@ -226,7 +252,14 @@ __device__ __forceinline__ void write_grad_rows(const TcParams& p, uint32_t tmem
     rt[row] = t;
   }
   float4* stage4 = reinterpret_cast<float4*>(stage);
+#if defined(VGAN_B200_DEBUG) && defined(VGAN_B200_TIMERS)
+#define VG_WG_CLK() clock64()
+  long long wg_a = 0, wg_b = 0, wg_c = 0;
+#else
+#define VG_WG_CLK() 0ll
+#endif
   for (int c0 = 0; c0 < slice_w; c0 += 128) {
+    const long long wg_t0 = VG_WG_CLK();
     // ---- phase A: this thread's row of O, columns c0 + 64 g + [0, 64), TMEM -> swizzled shared memory
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
@@ -245,6 +278,7 @@ __device__ __forceinline__ void write_grad_rows(const TcParams& p, uint32_t tmem
       }
     }
     asm volatile("bar.sync 2, 256;" ::: "memory");
+    const long long wg_t1 = VG_WG_CLK();
     // ---- phase B: warp w takes rows w, w + 8, ...; lane l the features f0 .. f0 + 3 of every row
     const int f0 = f_slice + c0 + 4 * lane;
     const bool lane_on = c0 + 4 * lane < slice_w && f0 < p.D;
@@ -259,46 +293,45 @@ __device__ __forceinline__ void write_grad_rows(const TcParams& p, uint32_t tmem
         }
     }
     if (lane_vec) {
-      // four rows per step, every load of the step issued before its first store (a row at a time the loop ran at
-      // one memory latency per row: 32 rows x ~1 500 cycles per range)
+      // four rows per step, every global load of the step issued before its first use (a row at a time the loop ran
+      // at one memory latency per row).  Registers decide whether the loads really go out together: the multiplier of
+      // the masked path IS the X row (dL/dU = dL/dY * X), so it is not loaded twice, and O comes from shared memory
+      // only when it is used.
+      const float* pa = row_is_x ? p.Xf : (p.Yf ? p.Yf : p.Xf);            // primary input row
+      const float* pb = (!row_is_x && !p.Yf) ? p.Uf : nullptr;               // masked rows: z = U * X - mean
+      const bool mul_is_pa = mul_base && pb && mul_base == p.Xf + p.row_begin * p.D;
+      const float* pm = (mul_base && !mul_is_pa) ? mul_base - p.row_begin * p.D : nullptr;
       for (int rr = 0; rr < kTile / 8; rr += 4) {
-        float4 o[4], a[4], m[4];
+        float4 va[4], vb[4], vm[4];
         bool ok[4];
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-          const int r = (rr + k) * 8 + warp;
-          const int64_t region_row = tile_row0 + r;
+          const int64_t region_row = tile_row0 + (rr + k) * 8 + warp;
           // (rows outside the range are never dereferenced: the callers of a multi-GPU job pass pointers that are
           // only valid for their own rows)
           ok[k] = region_row < n_region && region_row >= p.row_begin && region_row < p.row_end;   // warp-uniform
-          o[k] = a[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-          m[k] = make_float4(1.f, 1.f, 1.f, 1.f);
+          va[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+          vb[k] = vm[k] = make_float4(1.f, 1.f, 1.f, 1.f);
           if (ok[k]) {
-            const int64_t in_off = region_row * p.D + f0;
-            o[k] = stage4[r * 32 + (lane ^ (r & 31))];
-            if (row_is_x) {
-              a[k] = __ldg(reinterpret_cast<const float4*>(p.Xf + in_off));
-            } else if (p.Yf) {
-              a[k] = __ldg(reinterpret_cast<const float4*>(p.Yf + in_off));
-            } else {
-              const float4 x = __ldg(reinterpret_cast<const float4*>(p.Xf + in_off));
-              const float4 u = __ldg(reinterpret_cast<const float4*>(p.Uf + in_off));
-              a[k] = make_float4(u.x * x.x, u.y * x.y, u.z * x.z, u.w * x.w);
-            }
-            if (mul_base) m[k] = __ldg(reinterpret_cast<const float4*>(mul_base + (region_row - p.row_begin) * p.D + f0));
+            const int64_t off = region_row * p.D + f0;
+            va[k] = __ldg(reinterpret_cast<const float4*>(pa + off));
+            if (pb) vb[k] = __ldg(reinterpret_cast<const float4*>(pb + off));
+            if (pm) vm[k] = __ldg(reinterpret_cast<const float4*>(pm + off));
           }
         }
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
           if (!ok[k]) continue;
           const int r = (rr + k) * 8 + warp;
+          const float4 o = stage4[r * 32 + (lane ^ (r & 31))];
           const float rtr = rt[r];
+          const float4 m = mul_is_pa ? va[k] : vm[k];
           // unrounded z_i = input row - centring mean
           float4 gv;
-          gv.x = ci4 * ((o[k].x + av4[0]) - rtr * (a[k].x - mean4[0])) * m[k].x;
-          gv.y = ci4 * ((o[k].y + av4[1]) - rtr * (a[k].y - mean4[1])) * m[k].y;
-          gv.z = ci4 * ((o[k].z + av4[2]) - rtr * (a[k].z - mean4[2])) * m[k].z;
-          gv.w = ci4 * ((o[k].w + av4[3]) - rtr * (a[k].w - mean4[3])) * m[k].w;
+          gv.x = ci4 * ((o.x + av4[0]) - rtr * (va[k].x * vb[k].x - mean4[0])) * m.x;
+          gv.y = ci4 * ((o.y + av4[1]) - rtr * (va[k].y * vb[k].y - mean4[1])) * m.y;
+          gv.z = ci4 * ((o.z + av4[2]) - rtr * (va[k].z * vb[k].z - mean4[2])) * m.z;
+          gv.w = ci4 * ((o.w + av4[3]) - rtr * (va[k].w * vb[k].w - mean4[3])) * m.w;
           cs[0] += gv.x; cs[1] += gv.y; cs[2] += gv.z; cs[3] += gv.w;
           float4* out = reinterpret_cast<float4*>(out_base + (tile_row0 + r - p.row_begin) * p.D + f0);
           if (accumulate) atomicAdd(out, gv);     // unit shared between CTAs (column ranges / stream-K cut) or a BF16X3 pass
@@ -327,6 +360,7 @@ __device__ __forceinline__ void write_grad_rows(const TcParams& p, uint32_t tmem
           }
       }
     }
+    const long long wg_t2 = VG_WG_CLK();
     if (want_colsum) {      // (CTA-uniform)
 #pragma unroll
       for (int e = 0; e < 4; ++e) csp[warp * kTile + 4 * lane + e] = cs[e];
@@ -340,7 +374,18 @@ __device__ __forceinline__ void write_grad_rows(const TcParams& p, uint32_t tmem
       }
     }
     asm volatile("bar.sync 2, 256;" ::: "memory");      // the stage (and the partials) may be rewritten
+#if defined(VGAN_B200_DEBUG) && defined(VGAN_B200_TIMERS)
+    wg_a += wg_t1 - wg_t0; wg_b += wg_t2 - wg_t1; wg_c += clock64() - wg_t2;
+#else
+    (void)wg_t0; (void)wg_t1; (void)wg_t2;
+#endif
   }
+#if defined(VGAN_B200_DEBUG) && defined(VGAN_B200_TIMERS)
+  if (p.dbg && threadIdx.x == 0) {
+    float* d = p.dbg + static_cast<int64_t>(blockIdx.x) * p.dbg_stride;
+    d[20] += static_cast<float>(wg_a); d[21] += static_cast<float>(wg_b); d[22] += static_cast<float>(wg_c);
+  }
+#endif
 }
 
 }  // namespace vg
