@@ -59,9 +59,17 @@ enum {
   VGAN_B200_CENTER    = 2,      /* subtract the stacked column mean (distance invariant) */
   VGAN_B200_NEED_DX   = 4,      /* also produce dL/dX (VGAN.fit, vgan.py:283)           */
   VGAN_B200_LADDER    = 8,      /* scales are s, s/2, s/4, s/8, s/16: 1 ex2 + 4 squarings */
-  VGAN_B200_BF16X3    = 64      /* with PREC_BF16: fp32-class results on the tensor cores.  Every operand value is split
+  VGAN_B200_BF16X3    = 64,     /* with PREC_BF16: fp32-class results on the tensor cores.  Every operand value is split
                                    z = hi + lo (two bf16), the Gram is hi.hi + hi.lo + lo.hi in ONE K = 3 D GEMM, the
-                                   gradient GEMM runs three passes (P_hi V_hi, P_hi V_lo, P_lo V_hi) */
+                                   gradient GEMM adds its three parts P_hi V_hi + P_hi V_lo + P_lo V_hi (one pass for
+                                   D <= 256, two above) */
+  VGAN_B200_ONES      = 65536   /* OUTPUT of vgan_b200_workspace_layout in layout.flags, ignored on input: the stored rows
+                                   carry three constant features 1.0 in the zero padding behind the D real ones (set
+                                   when the padding has room and the D <= 256 kernel keeps the row operand in shared
+                                   memory).  Distances do not change (off_nrm / off_nrms include the +3); the kernel
+                                   puts the row norms into those columns of its row operand and reads the row sums of
+                                   P from the matching column of O, which takes two packed FP32 operations per column
+                                   pair out of the epilogue. */
 };
 
 typedef struct vgan_b200_ctx vgan_b200_ctx;    /* opaque */

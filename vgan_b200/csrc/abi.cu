@@ -115,12 +115,18 @@ static int fill_layout(int64_t Nx, int64_t Ny, int64_t D, int64_t D_u, int n_sca
   }
   memset(L, 0, sizeof(*L));
   L->Nx = Nx; L->Ny = Ny; L->D = D; L->D_u = D_u;
-  L->flags = flags; L->n_scales = n_scales;
+  L->flags = flags & ~VGAN_B200_ONES; L->n_scales = n_scales;
   const bool fp32 = (flags & VGAN_B200_PREC_MASK) == VGAN_B200_PREC_FP32;
   L->Dp = (D + kChunk - 1) / kChunk * kChunk;
   // bf16, more than one feature slice: an even chunk count, so that every slice is 2 or 4 chunks wide and the
   // CTA-pair kernel (each CTA of a pair holds half a slice) serves every width; at most one extra zero chunk
   if (!fp32 && L->Dp > kSliceMax) L->Dp = (D + 2 * kChunk - 1) / (2 * kChunk) * (2 * kChunk);
+  // three constant-1 features in the padding (see VGAN_B200_ONES): only where mmd_tc.cu keeps the row operand resident
+  // (plain bf16 up to D_p = 256; split operands at D_p = 64) and the padding has room for them
+  {
+    const bool split_ops = !fp32 && (flags & VGAN_B200_BF16X3);
+    if (!fp32 && D + 3 <= L->Dp && L->Dp <= kSliceMax && (!split_ops || L->Dp == kChunk)) L->flags |= VGAN_B200_ONES;
+  }
   L->Nxp = (Nx + kTile - 1) / kTile * kTile;
   L->Nyp = (Ny + kTile - 1) / kTile * kTile;
   const size_t rows = static_cast<size_t>(L->Nxp + L->Nyp);
@@ -224,10 +230,12 @@ static int run_tc(vgan_b200_ctx* ctx, const vgan_b200_layout_t& L, void* ws, con
   p.n_scales = L.n_scales;
   p.max_clusters = ctx->cluster_limit;
   p.v_parts = 1;
+  p.ones = (flags & VGAN_B200_ONES) ? 3 : 0;
   p.Nx = Nx; p.Ny = Ny; p.D = D; p.Dp = L.Dp;
   p.row_begin = row_begin; p.row_end = row_end;
   p.zq = reinterpret_cast<const __nv_bfloat16*>(base + L.off_zq);
   p.nrms = reinterpret_cast<const float*>(base + L.off_nrms);
+  p.nrm = reinterpret_cast<const float*>(base + L.off_nrm);
   p.par = reinterpret_cast<const float*>(base + L.off_par);
   p.cm = reinterpret_cast<const float*>(base + L.off_cm);
   p.sums = reinterpret_cast<double*>(base + L.off_sums);

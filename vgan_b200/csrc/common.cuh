@@ -52,6 +52,7 @@ struct TcParams {
   int gy_begin, gy_end;       // Y row tiles of this shard
   int xx_part, xx_nparts;     // S_xx-only units: X tiles t with t % nparts == part
   int n_xx_units;
+  int ones;                   // 3: the stored rows carry three features 1.0 behind the D real ones (VGAN_B200_ONES)
   int col_split, xx_chunk;    // mmd_tc.cu (set by its launcher): column ranges per gradient unit, tiles per S_xx chunk
   int pv;                     // 1: run the gradient GEMM and write dX/dY
   int n_scales;
@@ -68,6 +69,7 @@ struct TcParams {
   const float* Yf;
   const float* mean;
   const float* nrms;          // scaled norms
+  const float* nrm;           // unscaled norms |z_i|^2 of the stored rows
   const float* par;           // parameter block
   const float* cm;            // [2][Dp] common-mode gradient vectors A_x, A_y
   double* sums;

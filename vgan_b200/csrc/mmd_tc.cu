@@ -52,7 +52,7 @@ struct __align__(8) TcBarriers {
   uint64_t s_full[2], s_empty[2];
   uint64_t nj_full[kNjBufs], nj_empty[kNjBufs];
   uint64_t p_full[2], p_empty[2];
-  uint64_t o_full, zi_full;
+  uint64_t o_full, zi_full, zi_ready;
   uint32_t tmem_base;
   float red[kNumEpiWarps][2];
 };
@@ -147,7 +147,7 @@ __device__ __forceinline__ Unit decode_unit(const TcParams& p) {
 // in its barrier waits, tcgen05.ld latency and the fence behind its P stores, the other one computes (measured against
 // all 16 warps sharing every tile, same box: N = 16384, D = 128 506 -> 454 us, N = 65536, D = 64 7.65 -> 6.72 ms).
 // PV = false: kernel sums only (S_xx chunks, forward-only calls).
-template <bool LADDER, bool SPLIT, bool PV>
+template <bool LADDER, bool SPLIT, bool PV, bool ONES>
 __device__ __forceinline__ void epilogue_tiles(const TcParams& p, const Unit& u, TcBarriers* bar, uint8_t* p_smem,
                                                const float* nj_smem, uint32_t tmem, int warp, int lane, float& acc_x,
                                                float& acc_y, float& rsum) {
@@ -155,7 +155,7 @@ __device__ __forceinline__ void epilogue_tiles(const TcParams& p, const Unit& u,
   const int row = q * 32 + lane;
   const uint32_t lane_addr = static_cast<uint32_t>(q * 32) << 16;
   const float m2c0 = p.par[1];
-  const float ni = p.nrms[static_cast<int64_t>(u.ti) * kTile + row];
+  const float ni = ONES ? 0.f : p.nrms[static_cast<int64_t>(u.ti) * kTile + row];   // (ONES: inside the Gram)
   float coef_x[VGAN_B200_MAX_SCALES], coef_y[VGAN_B200_MAX_SCALES], ratio[VGAN_B200_MAX_SCALES];
 #pragma unroll
   for (int m = 0; m < VGAN_B200_MAX_SCALES; ++m) {
@@ -189,7 +189,7 @@ __device__ __forceinline__ void epilogue_tiles(const TcParams& p, const Unit& u,
         uint32_t v[32];
         tmem_ld_32x32(taddr, v);
         tmem_ld_wait();
-        epi_core_32<LADDER, SPLIT ? kPBoth : kPHi>(v, njp, ni, m2c0, cf, ratio, p.n_scales, ksum, rsum, pk, cw0, pk_lo);
+        epi_core_32<LADDER, SPLIT ? kPBoth : kPHi, ONES>(v, njp, ni, m2c0, cf, ratio, p.n_scales, ksum, rsum, pk, cw0, pk_lo);
       }
       mbar_wait(&bar->p_empty[b], par ^ 1);              // PV(n-2) done with P[b]
 #pragma unroll
@@ -203,7 +203,7 @@ __device__ __forceinline__ void epilogue_tiles(const TcParams& p, const Unit& u,
         tmem_ld_wait();
         tc_fence_before();
         mbar_arrive(&bar->s_empty[b]);     // all of S[b] is in registers: the Gram two tiles on may overwrite it
-        epi_core_32<LADDER, SPLIT ? kPBoth : kPHi>(v, njp + 32, ni, m2c0, cf, ratio, p.n_scales, ksum, rsum, pk, cw0,
+        epi_core_32<LADDER, SPLIT ? kPBoth : kPHi, ONES>(v, njp + 32, ni, m2c0, cf, ratio, p.n_scales, ksum, rsum, pk, cw0,
                                                    pk_lo);
       }
       mbar_arrive(&bar->nj_empty[nb]);
@@ -219,12 +219,12 @@ __device__ __forceinline__ void epilogue_tiles(const TcParams& p, const Unit& u,
       uint32_t v[32];
       tmem_ld_32x32(taddr, v);
       tmem_ld_wait();
-      epi_k_32<LADDER>(v, njp, ni, m2c0, ratio, p.n_scales, ksum);
+      epi_k_32<LADDER, ONES>(v, njp, ni, m2c0, ratio, p.n_scales, ksum);
       tmem_ld_32x32(taddr + 32, v);
       tmem_ld_wait();
       tc_fence_before();
       mbar_arrive(&bar->s_empty[b]);
-      epi_k_32<LADDER>(v, njp + 32, ni, m2c0, ratio, p.n_scales, ksum);
+      epi_k_32<LADDER, ONES>(v, njp + 32, ni, m2c0, ratio, p.n_scales, ksum);
       mbar_arrive(&bar->nj_empty[nb]);
       const float fac = (u.sym && jt != u.ti) ? 2.f : 1.f;
       if (col_is_x) acc_x = fmaf(ksum, fac, acc_x); else acc_y += ksum;
@@ -270,6 +270,7 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__
     }
     mbar_init(&bar->o_full, 1);
     mbar_init(&bar->zi_full, 1);
+    mbar_init(&bar->zi_ready, kTile);
     fence_barrier_init();
   }
   if (warp == kWarpAlloc) {
@@ -393,7 +394,7 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__
     const int pv_stages = (slice_chunks + 1) >> 1;
     uint32_t s = 0, ph = 0;
     if (geo.res) {
-      mbar_wait(&bar->zi_full, 0);
+      mbar_wait(p.ones ? &bar->zi_ready : &bar->zi_full, 0);     // (ones: the row norms have been written into Z_I)
       tc_fence_after();
     }
     // 4 k-steps of 16 over one 64-feature chunk pair
@@ -525,8 +526,36 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__
     const uint32_t lane_addr = static_cast<uint32_t>(q * 32) << 16;
     float acc_x = 0.f, acc_y = 0.f;   // sum of k over X / Y columns (weighted by symmetry)
     float rsum = 0.f;                 // sum_j P_ij over this thread's column quarter
-    if (u.pv) epilogue_tiles<LADDER, SPLIT, true>(p, u, bar, p_smem, nj_smem, tmem, warp, lane, acc_x, acc_y, rsum);
-    else epilogue_tiles<LADDER, SPLIT, false>(p, u, bar, p_smem, nj_smem, tmem, warp, lane, acc_x, acc_y, rsum);
+    const bool ones = p.ones != 0 && geo.res;
+    if (ones && warp < 4) {
+      // VGAN_B200_ONES: columns D .. D + 2 of the resident row operand (1.0 in every stored row) become the three bf16
+      // pieces of -(|z_i|^2 - 6) / 2 (the norm includes the three ones; the column operand keeps its ones), so that
+      //   S' = z_i.z_j - (|z_i|^2 - 6) / 2   and   u = -2 c0 S' + c0 |z_j|^2 = c0 d2
+      // with no row norm in the epilogue.  Split operands: the hi chunk is patched, the lo chunk is 0 there.
+      mbar_wait(&bar->zi_full, 0);
+      const float a = -0.5f * (p.nrm[static_cast<int64_t>(u.ti) * kTile + row] - 6.f);
+      const __nv_bfloat16 h0 = __float2bfloat16_rn(a);
+      const float r1 = a - __bfloat162float(h0);
+      const __nv_bfloat16 h1 = __float2bfloat16_rn(r1);
+      const __nv_bfloat16 h2 = __float2bfloat16_rn(r1 - __bfloat162float(h1));
+      const __nv_bfloat16 piece[3] = {h0, h1, h2};
+#pragma unroll
+      for (int e = 0; e < 3; ++e) {
+        const int col = static_cast<int>(p.D) + e;
+        const int kc = col >> 6, cc = col & 63;                      // chunk, column inside the 128-byte swizzle row
+        *reinterpret_cast<__nv_bfloat16*>(zi_smem + kc * kChunkBytes + row * 128 + (((cc >> 3) ^ (row & 7)) << 4) +
+                                          (cc & 7) * 2) = piece[e];
+      }
+      fence_proxy_async_smem();
+      mbar_arrive(&bar->zi_ready);
+    }
+    if (ones) {
+      if (u.pv) epilogue_tiles<LADDER, SPLIT, true, true>(p, u, bar, p_smem, nj_smem, tmem, warp, lane, acc_x, acc_y, rsum);
+      else epilogue_tiles<LADDER, SPLIT, false, true>(p, u, bar, p_smem, nj_smem, tmem, warp, lane, acc_x, acc_y, rsum);
+    } else {
+      if (u.pv) epilogue_tiles<LADDER, SPLIT, true, false>(p, u, bar, p_smem, nj_smem, tmem, warp, lane, acc_x, acc_y, rsum);
+      else epilogue_tiles<LADDER, SPLIT, false, false>(p, u, bar, p_smem, nj_smem, tmem, warp, lane, acc_x, acc_y, rsum);
+    }
 
     if (u.pv && warp < 8) prefetch_grad_rows(p, u.ti, u.row_is_x, u.slice, slice_chunks);   // inputs of the gradient rows -> L2
     // ---- block sums
@@ -558,7 +587,11 @@ mmd2_tc_kernel(const __grid_constant__ CUtensorMap zmap, const __grid_constant__
       float* rs_smem = reinterpret_cast<float*>(p_smem);   // [4 column quarters][128 rows] row sums of P
       rs_smem[g * kTile + row] = rsum;
       asm volatile("bar.sync 1, %0;" ::"n"(kNumEpiThreads) : "memory");
-      const float rtot = rs_smem[row] + rs_smem[kTile + row] + rs_smem[2 * kTile + row] + rs_smem[3 * kTile + row];
+      float rtot = rs_smem[row] + rs_smem[kTile + row] + rs_smem[2 * kTile + row] + rs_smem[3 * kTile + row];
+      if (ones && warp < 8) {       // the row sums of the ROUNDED P' (all three parts with split operands): column D of O
+        rtot = __uint_as_float(tmem_ld_32x32_x1(tmem_o + lane_addr + static_cast<uint32_t>(p.D)));
+        tmem_ld_wait();
+      }
       if (warp < 8)       // O through the ring (dead: every stage was consumed by an MMA that has completed)
         write_grad_rows(p, tmem_o, reinterpret_cast<float*>(ring), reinterpret_cast<float*>(p_smem + 4096), u.ti,
                         u.row_is_x, u.slice, slice_chunks, rtot, p.col_split > 1, u.first != 0);

@@ -16,7 +16,7 @@ struct PackArgs {
   const float* Y;
   int64_t Nx, Ny, D, Dp, Nxp, Nyp, D_u;
   int64_t rb, re;   // row range of X and of Y handled by this call
-  int center, fp32, split;
+  int center, fp32, split, ones;   // ones: constant-1 features at columns D .. D + ones - 1 of every valid row
   __nv_bfloat16* zq;
   __nv_bfloat16* zb;    // split operands (BF16X3): zq = row operand [hi | hi | lo], zb = column operand [hi | lo | hi],
                         // both [rows, 3 Dp]: sum_k zq[i,k] zb[j,k] = hi_i.hi_j + hi_i.lo_j + lo_i.hi_j
@@ -238,7 +238,7 @@ __global__ void __launch_bounds__(kStatThreads) colstats_masked_kernel(PackArgs 
 // ------------------------------------------------------------------ scales
 struct ScaleArgs {
   float mults[VGAN_B200_MAX_SCALES];
-  int n_scales, frozen, center, common_mode;
+  int n_scales, frozen, center, common_mode, ones;
   int64_t Nx, Ny, D, Dp, Nxp, Nyp, D_u;
   float weight;
   const double* stats;
@@ -335,7 +335,9 @@ __global__ void __launch_bounds__(256) scales_kernel(ScaleArgs a) {
     for (int r = 0; r < 2; ++r) {
       par[kParCw0 + 2 * r + 0] = cx * w0[r][0];
       par[kParCw0 + 2 * r + 1] = cy * w0[r][1];
-      par[kParB + r] = (w0[r][0] - w0[r][1]) + cx * w0[r][0] * npx + cy * w0[r][1] * npy;
+      // the row sums the kernel forms in FP32 include the padding columns (P' = -c_j w0 there); read from the ones
+      // column of O (VGAN_B200_ONES) they do not
+      par[kParB + r] = (w0[r][0] - w0[r][1]) + (a.ones ? 0.f : cx * w0[r][0] * npx + cy * w0[r][1] * npy);
     }
     sh[0] = w0[0][0]; sh[1] = w0[0][1]; sh[2] = w0[1][0]; sh[3] = w0[1][1];
   }
@@ -386,6 +388,8 @@ __global__ void __launch_bounds__(256) pack_kernel(PackArgs a, int64_t x0, int64
       const float raw = in_x ? a.X[local * a.D + f]
                              : (a.Y ? a.Y[local * a.D + f] : a.U[local * a.D + f] * a.X[local * a.D + f]);
       z = raw - a.mean[f];
+    } else if (valid && f < a.D + a.ones) {
+      z = 1.f;                       // VGAN_B200_ONES (split: hi = 1, lo = 0)
     }
     if (a.fp32) {
       a.zf[r * a.Dp + f] = z;
@@ -444,6 +448,9 @@ __global__ void __launch_bounds__(256) pack_masked_kernel(PackArgs a, int64_t r0
       const float4 m = *reinterpret_cast<const float4*>(a.mean + 4 * f4);
       ox = pack4_bf16(x.x - m.x, x.y - m.y, x.z - m.z, x.w - m.w, nx);
       oy = pack4_bf16(u.x * x.x - m.x, u.y * x.y - m.y, u.z * x.z - m.z, u.w * x.w - m.w, ny);
+    } else if (valid && a.ones && f4 == D4) {
+      ox = pack4_bf16(1.f, 1.f, 1.f, 0.f, nx);      // VGAN_B200_ONES: D % 4 == 0 here, the three ones fill this group
+      oy = pack4_bf16(1.f, 1.f, 1.f, 0.f, ny);
     }
     zx[f4] = ox;
     zy[f4] = oy;
@@ -493,6 +500,7 @@ static PackArgs make_pack_args(const vgan_b200_layout_t& L, void* ws, const floa
   a.center = (L.flags & VGAN_B200_CENTER) ? 1 : 0;
   a.fp32 = (L.flags & VGAN_B200_PREC_MASK) == VGAN_B200_PREC_FP32;
   a.split = (!a.fp32 && (L.flags & VGAN_B200_BF16X3)) ? 1 : 0;
+  a.ones = (L.flags & VGAN_B200_ONES) ? 3 : 0;
   a.zq = reinterpret_cast<__nv_bfloat16*>(base + L.off_zq);
   a.zb = a.zq + static_cast<size_t>(L.Nxp + L.Nyp) * 3 * L.Dp;
   a.zf = reinterpret_cast<float*>(base + L.off_zf);
@@ -546,6 +554,7 @@ int run_scales(const vgan_b200_layout_t& L, void* ws, float* bandwidth, int froz
   a.n_scales = L.n_scales; a.frozen = frozen;
   a.center = (L.flags & VGAN_B200_CENTER) ? 1 : 0;
   a.common_mode = (L.flags & VGAN_B200_PREC_MASK) == VGAN_B200_PREC_BF16;   // the tcgen05 kernels (bf16, bf16x3)
+  a.ones = (L.flags & VGAN_B200_ONES) ? 3 : 0;
   a.Nx = L.Nx; a.Ny = L.Ny; a.D = L.D; a.Dp = L.Dp; a.Nxp = L.Nxp; a.Nyp = L.Nyp; a.D_u = L.D_u;
   a.weight = weight;
   a.stats = reinterpret_cast<const double*>(base + L.off_stats);

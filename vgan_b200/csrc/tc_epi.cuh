@@ -14,7 +14,10 @@ enum : int { kPHi = 0, kPLo = 1, kPBoth = 2 };
 //   k = t (1 + t (1 + t^2 (1 + t^4 (1 + t^8))))                    = t + t^2 + t^4 + t^8 + t^16
 //   w = t (c4 + t (c3 + t^2 (c2 + t^4 (c1 + t^8 c0)))) - c_j w0    = sum_m c_m t^(2^(4-m)) - c_j w0
 // (scale index 4 is the widest kernel, t itself; index 0 the narrowest, t^16)
-template <bool LADDER, int PMODE>
+// ONES (VGAN_B200_ONES): the Gram already carries -|z_i|^2 / 2 (three bf16 pieces in the ones columns of the resident row
+// operand), so u = fma(S, -2 c0, nj) without the row norm, and the row sum of P comes out of the ones column of O:
+// 14 packed ops per column pair.
+template <bool LADDER, int PMODE, bool ONES = false>
 __device__ __forceinline__ void epi_core_32(const uint32_t (&v)[32], const float* __restrict__ njp, float ni,
                                             float m2c0, const float (&cf)[VGAN_B200_MAX_SCALES],
                                             const float (&ratio)[VGAN_B200_MAX_SCALES], int n_scales,
@@ -38,7 +41,7 @@ __device__ __forceinline__ void epi_core_32(const uint32_t (&v)[32], const float
       for (int q = 0; q < 4; ++q) {
         const uint64_t s2 = f2_pack(__uint_as_float(v[c * 8 + 2 * q]), __uint_as_float(v[c * 8 + 2 * q + 1]));
         float u0, u1;
-        f2_unpack(f2_fma(s2, m2, f2_add(ni2, nj2[q])), u0, u1);
+        f2_unpack(ONES ? f2_fma(s2, m2, nj2[q]) : f2_fma(s2, m2, f2_add(ni2, nj2[q])), u0, u1);
         // no clamp at 0 here (the reference's cdist clamps): the norms are those of the values the tensor core
         // multiplies, so u of a coincident pair is 0 +- 1e-6 and t = 1 +- 1e-6 — far inside the 2e-3 / 1e-4 budgets,
         // and two FMNMX per column pair are saved; padding has u = +huge
@@ -46,7 +49,7 @@ __device__ __forceinline__ void epi_core_32(const uint32_t (&v)[32], const float
         const uint64_t t2 = f2_mul(t1, t1), t4 = f2_mul(t2, t2), t8 = f2_mul(t4, t4);
         ks2 = f2_fma(t1, f2_fma(t1, f2_fma(t2, f2_fma(t4, f2_add(t8, one), one), one), one), ks2);
         const uint64_t w2 = f2_fma(t1, f2_fma(t1, f2_fma(t2, f2_fma(t4, f2_fma(t8, c0, c1), c2), c3), c4), mcw);
-        rs2 = f2_add(rs2, w2);
+        if constexpr (!ONES) rs2 = f2_add(rs2, w2);
         float w0, w1;
         f2_unpack(w2, w0, w1);
         pw[q] = pack_bf16x2(w0, w1);
@@ -72,7 +75,7 @@ __device__ __forceinline__ void epi_core_32(const uint32_t (&v)[32], const float
     float w[8];
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
-      float uarg = fmaf(__uint_as_float(v[c * 8 + e]), m2c0, ni + njv[e]);
+      float uarg = fmaf(__uint_as_float(v[c * 8 + e]), m2c0, ONES ? njv[e] : ni + njv[e]);
       uarg = fmaxf(uarg, 0.f);
       float kk = 0.f, ww = -cw0;
       for (int m = 0; m < n_scales; ++m) {
@@ -109,7 +112,7 @@ __device__ __forceinline__ void epi_compute_32(const uint32_t (&v)[32], const fl
 }
 
 // Sum over 32 columns already in registers of k alone (units without a gradient GEMM): 10 packed ops per column pair
-template <bool LADDER>
+template <bool LADDER, bool ONES = false>
 __device__ __forceinline__ void epi_k_32(const uint32_t (&v)[32], const float* __restrict__ njp, float ni, float m2c0,
                                          const float (&ratio)[VGAN_B200_MAX_SCALES], int n_scales, float& ksum) {
   if constexpr (LADDER) {
@@ -123,7 +126,7 @@ __device__ __forceinline__ void epi_k_32(const uint32_t (&v)[32], const float* _
       for (int q = 0; q < 2; ++q) {
         const uint64_t s2 = f2_pack(__uint_as_float(v[c * 4 + 2 * q]), __uint_as_float(v[c * 4 + 2 * q + 1]));
         float u0, u1;
-        f2_unpack(f2_fma(s2, m2, f2_add(ni2, nj2[q])), u0, u1);
+        f2_unpack(ONES ? f2_fma(s2, m2, nj2[q]) : f2_fma(s2, m2, f2_add(ni2, nj2[q])), u0, u1);
         const uint64_t t1 = f2_pack(ex2_approx(-u0), ex2_approx(-u1));
         const uint64_t t2 = f2_mul(t1, t1), t4 = f2_mul(t2, t2), t8 = f2_mul(t4, t4);
         ks2 = f2_fma(t1, f2_fma(t1, f2_fma(t2, f2_fma(t4, f2_add(t8, one), one), one), one), ks2);
@@ -139,7 +142,7 @@ __device__ __forceinline__ void epi_k_32(const uint32_t (&v)[32], const float* _
       const float njv[4] = {nj4.x, nj4.y, nj4.z, nj4.w};
 #pragma unroll
       for (int e = 0; e < 4; ++e) {
-        float uarg = fmaf(__uint_as_float(v[c * 4 + e]), m2c0, ni + njv[e]);
+        float uarg = fmaf(__uint_as_float(v[c * 4 + e]), m2c0, ONES ? njv[e] : ni + njv[e]);
         uarg = fmaxf(uarg, 0.f);
         for (int m = 0; m < n_scales; ++m) ksum += ex2_approx(-uarg * ratio[m]);
       }
