@@ -170,7 +170,8 @@ def secondary_configs(dev, peak_tf):
     for a few steps on one GPU: ms per evaluation, the roofline that binds it and the fraction of it.
     tensor: 8 N^2 D flops / measured sustained bf16 peak.  epilogue: 2.5 N^2 kernel pairs per evaluation (N x 2N
     gradient rows + the upper triangle of X x X) / the measured pairs/s of the ladder epilogue's instruction mix
-    (2 ex2 + 17 packed fp32 per 2 pairs: MUFU and FP32 issue together, profiles/peaks_r2.json)."""
+    (2 ex2 + 17 packed fp32 per 2 pairs: MUFU and FP32 issue together, profiles/peaks_r2.json; that is the round-1
+    epilogue and stays the yardstick — the kernel now issues 14 to 16 packed operations per column pair)."""
     from vgan_b200 import MMDLossConstrained, RBF
     from vgan_b200.dist import sharded_masked_step
     pk = micro_peaks()

@@ -54,6 +54,17 @@ def test_layout_is_pure_host_logic():
     # everything vgan_b200_stats zeroes is one contiguous block
     assert L.off_colsum == L.off_sums + 32 and L.off_acc == L.off_sums
     assert L.off_acc + L.acc_bytes == L.off_misc + 64 and L.off_stats > L.off_colsum and L.off_cmax > L.off_stats
+    # VGAN_B200_ONES (output flag): three constant-1 features where the padding has room and mmd_tc.cu keeps the row
+    # operand resident — plain bf16 up to D_p = 256, split operands at D_p = 64; never on input, never for fp32 / D > 256
+    ONES = 65536
+    assert L.flags & ONES and not (L32.flags & ONES)
+    assert _lib.layout(64, 64, 61, 0, 5, _lib.PREC_BF16).flags & ONES
+    assert not (_lib.layout(64, 64, 62, 0, 5, _lib.PREC_BF16).flags & ONES)          # 62 + 3 > 64
+    assert not (_lib.layout(64, 64, 128, 0, 5, _lib.PREC_BF16 | ONES).flags & ONES)   # no padding; the input bit is ignored
+    assert _lib.layout(64, 64, 20, 0, 5, _lib.PREC_BF16 | _lib.BF16X3).flags & ONES
+    assert not (_lib.layout(64, 64, 100, 0, 5, _lib.PREC_BF16 | _lib.BF16X3).flags & ONES)   # split, D_p = 128: streamed
+    assert _lib.layout(64, 64, 250, 0, 5, _lib.PREC_BF16).flags & ONES
+    assert not (_lib.layout(64, 64, 300, 0, 5, _lib.PREC_BF16).flags & ONES)
     wide = _lib.layout(4096, 4096, 784, 784, 5, _lib.PREC_BF16 | _lib.LADDER)
     assert wide.Dp == 896 and wide.off_zq - wide.off_xchg == 256 * 128 * 1024
     with pytest.raises(RuntimeError):
