@@ -77,7 +77,8 @@ typedef struct vgan_b200_ctx vgan_b200_ctx;    /* opaque */
 /* Layout of the caller-provided workspace (all offsets in bytes from `ws`, which must be 1024-byte aligned).
  * Z is the stacked sample [X ; Y] (Mmd_loss_constrained.py:43): X rows at [0,Nx),
  * zero rows up to Nxp (multiple of 128), Y rows at [Nxp, Nxp+Ny), zero rows up to
- * Nxp+Nyp; Dp = D rounded up to 64 with zero columns (to 128 on the bf16 path when D > 256).
+ * Nxp+Nyp; Dp = D rounded up to 64 with zero columns (to 128 on the bf16 path when D > 256 and, plain bf16, for
+ * D = 62..64, where the extra chunk makes room for VGAN_B200_ONES).
  * The accumulator block [off_acc, off_acc + acc_bytes) is zeroed by vgan_b200_stats; on several GPUs the caller
  * reduces its parts between the calls (see vgan_b200_stats / _mmd2_fwd_bwd). */
 typedef struct {

@@ -59,7 +59,10 @@ def test_layout_is_pure_host_logic():
     ONES = 65536
     assert L.flags & ONES and not (L32.flags & ONES)
     assert _lib.layout(64, 64, 61, 0, 5, _lib.PREC_BF16).flags & ONES
-    assert not (_lib.layout(64, 64, 62, 0, 5, _lib.PREC_BF16).flags & ONES)          # 62 + 3 > 64
+    L62 = _lib.layout(64, 64, 62, 0, 5, _lib.PREC_BF16)                               # 62 + 3 > 64: one more chunk
+    assert L62.Dp == 128 and L62.flags & ONES
+    L62s = _lib.layout(64, 64, 62, 0, 5, _lib.PREC_BF16 | _lib.BF16X3)                # split operands: no room, no ones
+    assert L62s.Dp == 64 and not (L62s.flags & ONES)
     assert not (_lib.layout(64, 64, 128, 0, 5, _lib.PREC_BF16 | ONES).flags & ONES)   # no padding; the input bit is ignored
     assert _lib.layout(64, 64, 20, 0, 5, _lib.PREC_BF16 | _lib.BF16X3).flags & ONES
     assert not (_lib.layout(64, 64, 100, 0, 5, _lib.PREC_BF16 | _lib.BF16X3).flags & ONES)   # split, D_p = 128: streamed
