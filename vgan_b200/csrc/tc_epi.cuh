@@ -342,25 +342,48 @@ __device__ __forceinline__ void write_grad_rows(const TcParams& p, uint32_t tmem
         }
       }
     } else if (lane_on) {
-      for (int rr = 0; rr < kTile / 8; ++rr) {
-        const int r = rr * 8 + warp;
-        const int64_t region_row = tile_row0 + r;
-        if (!(region_row < n_region && region_row >= p.row_begin && region_row < p.row_end)) continue;
-        const float4 o = stage4[r * 32 + (lane ^ (r & 31))];
-        const float ov[4] = {o.x, o.y, o.z, o.w};
-        const float rtr = rt[r];
-        const int64_t in_off = region_row * p.D + f0;
-        const int64_t out_off = (region_row - p.row_begin) * p.D + f0;
+      // D % 4 != 0 (or misaligned bases): the same four rows per step with 4-byte accesses (rows are not 16-byte aligned)
+      const float* pa = row_is_x ? p.Xf : (p.Yf ? p.Yf : p.Xf);
+      const float* pb = (!row_is_x && !p.Yf) ? p.Uf : nullptr;
+      const bool mul_is_pa = mul_base && pb && mul_base == p.Xf + p.row_begin * p.D;
+      const float* pm = (mul_base && !mul_is_pa) ? mul_base - p.row_begin * p.D : nullptr;
+      const int ne = min(4, static_cast<int>(p.D) - f0);          // valid features of this lane (>= 1)
+      for (int rr = 0; rr < kTile / 8; rr += 4) {
+        float va[4][4], vb[4][4], vm[4][4];
+        bool ok[4];
 #pragma unroll
-        for (int e = 0; e < 4; ++e)
-          if (f0 + e < p.D) {
-            const float raw = row_is_x ? p.Xf[in_off + e] : (p.Yf ? p.Yf[in_off + e] : p.Uf[in_off + e] * p.Xf[in_off + e]);
-            float gval = ci4 * ((ov[e] + av4[e]) - rtr * (raw - mean4[e]));
-            if (mul_base) gval *= mul_base[out_off + e];
-            cs[e] += gval;
-            if (accumulate) atomicAdd(out_base + out_off + e, gval);
-            else out_base[out_off + e] = gval;
+        for (int k = 0; k < 4; ++k) {
+          const int64_t region_row = tile_row0 + (rr + k) * 8 + warp;
+          ok[k] = region_row < n_region && region_row >= p.row_begin && region_row < p.row_end;   // warp-uniform
+          const int64_t off = region_row * p.D + f0;
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            va[k][e] = 0.f; vb[k][e] = 1.f; vm[k][e] = 1.f;
+            if (ok[k] && e < ne) {
+              va[k][e] = __ldg(pa + off + e);
+              if (pb) vb[k][e] = __ldg(pb + off + e);
+              if (pm) vm[k][e] = __ldg(pm + off + e);
+            }
           }
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          if (!ok[k]) continue;
+          const int r = (rr + k) * 8 + warp;
+          const float4 o = stage4[r * 32 + (lane ^ (r & 31))];
+          const float ov[4] = {o.x, o.y, o.z, o.w};
+          const float rtr = rt[r];
+          float* out = out_base + (tile_row0 + r - p.row_begin) * p.D + f0;
+#pragma unroll
+          for (int e = 0; e < 4; ++e)
+            if (e < ne) {
+              const float gval = ci4 * ((ov[e] + av4[e]) - rtr * (va[k][e] * vb[k][e] - mean4[e])) *
+                                 (mul_is_pa ? va[k][e] : vm[k][e]);
+              cs[e] += gval;
+              if (accumulate) atomicAdd(out + e, gval);
+              else out[e] = gval;
+            }
+        }
       }
     }
     const long long wg_t2 = VG_WG_CLK();
