@@ -184,10 +184,30 @@ def secondary_configs(dev, peak_tf):
         X, U = X.to(dev), U.to(dev)
         f = MMDLossConstrained(WEIGHT, kernel=RBF(), precision=prec)
         ms = time_steps(lambda: sharded_masked_step(f, X, U, 0, 1, time_k1=False), steps, warmup)
+        graph_ms = None
+        if N <= 16384:
+            # the same evaluation replayed as a CUDA graph (what VGAN.fit does): no host launch gaps — at these sizes the
+            # per-call number above depends on the host as much as on the GPU
+            try:
+                side = torch.cuda.Stream()
+                side.wait_stream(torch.cuda.current_stream())
+                with torch.cuda.stream(side):
+                    sharded_masked_step(f, X, U, 0, 1, time_k1=False)
+                    side.synchronize()
+                    g = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(g, stream=side):
+                        keep = sharded_masked_step(f, X, U, 0, 1, time_k1=False)
+                torch.cuda.current_stream().wait_stream(side)
+                graph_ms = time_steps(g.replay, 3 * steps, warmup)
+                del g, keep
+            except Exception:
+                graph_ms = None
         t = ms * 1e-3
         tensor_frac = 8.0 * N * N * D / t / 1e12 / peak_tf
         rec = {"config": name, "N": N, "D": D, "precision": prec, "ms": ms, "evals_per_s": 1e3 / ms,
                "tensor_frac": tensor_frac}
+        if graph_ms is not None:
+            rec["graph_replay_ms"] = graph_ms
         if epi_peak:
             rec["epilogue_frac"] = 2.5 * N * N / t / epi_peak
             rec["mufu_frac"] = 2.0 * N * N / t / mufu_peak
