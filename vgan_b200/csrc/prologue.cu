@@ -42,17 +42,6 @@ __device__ __forceinline__ unsigned long long max_key(float v, int64_t row) {
          static_cast<unsigned long long>(0xffffffffu - static_cast<uint32_t>(row));
 }
 
-__device__ __forceinline__ float block_sum_256(float v, float* red) {
-  v = warp_sum(v);
-  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
-  __syncthreads();
-  float t = 0.f;
-  if (threadIdx.x == 0)
-    for (int w = 0; w < 8; ++w) t += red[w];
-  __syncthreads();
-  return t;   // valid in thread 0
-}
-
 // 2-D thread map of the statistics kernels (round 2: one thread per column walking 32-64 rows serially left 20 of 256
 // threads busy at D = 20 and cost 30 us for 40 KB).  1024 threads: column c = tid % cp of the pass (cp = power of two
 // <= 64 that covers the column items), row lane tid / cp (>= 16 of them); a thread strides the block's rows by the row

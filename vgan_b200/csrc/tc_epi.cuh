@@ -9,7 +9,7 @@ namespace vg {
 // split-operand form), or both tiles at once (single-pass split operands, mmd_tc.cu)
 enum : int { kPHi = 0, kPLo = 1, kPBoth = 2 };
 
-// Kernel values of 32 columns already in registers (see epi_half_tile for the math).
+// Kernel values of 32 columns already in registers (the math is spelled out below the function).
 // Ladder form, nested so that t^16 is never formed (3 squarings, 16 packed ops per column pair instead of 17):
 //   k = t (1 + t (1 + t^2 (1 + t^4 (1 + t^8))))                    = t + t^2 + t^4 + t^8 + t^16
 //   w = t (c4 + t (c3 + t^2 (c2 + t^4 (c1 + t^8 c0)))) - c_j w0    = sum_m c_m t^(2^(4-m)) - c_j w0
@@ -150,36 +150,10 @@ __device__ __forceinline__ void epi_k_32(const uint32_t (&v)[32], const float* _
   }
 }
 
-// One thread = one row of the tile.  Reads S[row, col0 .. col0+31] from TMEM, forms
+// The math of epi_core_32 (one thread = one row of the tile, 32 columns of S already in registers):
 //   u = c0*d2 = fma(S, -2c0, ni + nj),  t = 2^-u,  k = sum_m t^(2^q),  w = sum_m coef_m t^(2^q)
-// (ladder) or the general n_scales form, adds k to ksum and w to rsum, and returns the 32 values of
-// P = w as bf16 packed into 4 x uint4 (8 columns each, ascending).
-template <bool LADDER, int PMODE>
-__device__ __forceinline__ void epi_half_tile(uint32_t taddr, const float* __restrict__ njp, float ni,
-                                              float m2c0, const float (&cf)[VGAN_B200_MAX_SCALES],
-                                              const float (&ratio)[VGAN_B200_MAX_SCALES], int n_scales,
-                                              float& ksum, float& rsum, uint4 (&pk)[4], float cw0, uint4* pk_lo) {
-  uint32_t v[32];
-  tmem_ld_32x32(taddr, v);
-  tmem_ld_wait();
-  epi_core_32<LADDER, PMODE>(v, njp, ni, m2c0, cf, ratio, n_scales, ksum, rsum, pk, cw0, pk_lo);
-}
-
-// Column sums over the 32 lanes of a warp of 32 per-lane values: lane l returns sum over lanes of v[l].
-// Butterfly: each step halves the values a lane holds (16 + 8 + 4 + 2 + 1 = 31 shuffles).
-__device__ __forceinline__ float warp_transpose_sum(float (&v)[32], int lane) {
-#pragma unroll
-  for (int s = 16; s >= 1; s >>= 1) {
-    const bool up = (lane & s) != 0;
-#pragma unroll
-    for (int i = 0; i < s; ++i) {
-      const float send = up ? v[i] : v[i + s];
-      const float keep = up ? v[i + s] : v[i];
-      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, s);
-    }
-  }
-  return v[0];
-}
+// (ladder) or the general n_scales form; k is added to ksum, w to rsum, and the 32 values of P = w come back as bf16
+// packed into 4 x uint4 (8 columns each, ascending).
 
 // L2 prefetch of what write_grad_rows will read from global memory (the fp32 input rows of the unit's row tile, its
 // slice of the features): 256 threads, thread = (row, half of the slice's 128-byte lines).  Issued when the epilogue has
